@@ -1,0 +1,202 @@
+/*
+ * vox_cuda.h - C ABI of the B200 (sm_100a) CUDA backend for voxtral.c
+ *
+ * This header is the drop-in boundary.  It plays the role voxtral_metal.h plays
+ * for the reference's Apple backend (/root/reference/voxtral_metal.h:20-282):
+ * plain C, pointers and sizes only, callable from one host thread per GPU.
+ * Every entry point names the reference interface it stands in for.
+ *
+ * Ownership model (differs from Metal's unified memory on purpose): weights are
+ * uploaded ONCE from the mmap'd safetensors pointers into HBM
+ * (vox_cuda_model_create), and every per-stream tensor - decoder KV ring,
+ * encoder KV ring, conv-stem tails, adapter-token buffer - lives in a device
+ * resident vox_cuda_state_t.  The host keeps only integers (lengths, offsets).
+ *
+ * Error convention follows the reference (/root/reference/voxtral.c:149,158):
+ * a negative / NULL return plus one line on stderr; vox_cuda_last_error()
+ * returns the same text.  There is no CPU fallback anywhere behind this ABI.
+ */
+#ifndef VOX_CUDA_H
+#define VOX_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Model constants - identical to /root/reference/voxtral.h:19-50. */
+#define VOX_CUDA_MEL_BINS      128
+#define VOX_CUDA_ENC_DIM       1280
+#define VOX_CUDA_ENC_LAYERS    32
+#define VOX_CUDA_ENC_HEADS     32
+#define VOX_CUDA_ENC_HEAD_DIM  64
+#define VOX_CUDA_ENC_HIDDEN    5120
+#define VOX_CUDA_ENC_WINDOW    750
+#define VOX_CUDA_DEC_DIM       3072
+#define VOX_CUDA_DEC_LAYERS    26
+#define VOX_CUDA_DEC_HEADS     32
+#define VOX_CUDA_DEC_KV_HEADS  8
+#define VOX_CUDA_DEC_HEAD_DIM  128
+#define VOX_CUDA_DEC_HIDDEN    9216
+#define VOX_CUDA_DEC_WINDOW    8192
+#define VOX_CUDA_VOCAB         131072
+#define VOX_CUDA_MAX_ALT       4
+
+/* ------------------------------------------------------------------------
+ * Weight table: host pointers exactly as the reference loaders leave them
+ * (bf16 matrices = pointers into the mmap, small tensors = malloc'd f32);
+ * /root/reference/voxtral.h:56-182, loaders voxtral_encoder.c:58-146,
+ * voxtral_decoder.c:57-145, voxtral.c:102-125.
+ * ------------------------------------------------------------------------ */
+typedef struct {
+    const uint16_t *wq, *wk, *wv, *wo;        /* [2048,1280]x3, [1280,2048] bf16 */
+    const uint16_t *w1, *w2, *w3;             /* [5120,1280], [1280,5120], [5120,1280] */
+    const float *wq_bias, *wv_bias;           /* [2048] (wk has no bias) */
+    const float *wo_bias, *w2_bias;           /* [1280] */
+    const float *attention_norm, *ffn_norm;   /* [1280] */
+} vox_cuda_enc_layer_w_t;
+
+typedef struct {
+    const uint16_t *wq, *wk, *wv, *wo;        /* [4096,3072],[1024,3072]x2,[3072,4096] */
+    const uint16_t *w1, *w2, *w3;             /* [9216,3072],[3072,9216],[9216,3072] */
+    const float *attention_norm, *ffn_norm;   /* [3072] */
+} vox_cuda_dec_layer_w_t;
+
+typedef struct {
+    int n_enc_layers;                         /* 32 (fewer allowed: test models) */
+    int n_dec_layers;                         /* 26 */
+    const float *conv0_weight, *conv0_bias;   /* [1280,128,3], [1280] f32 */
+    const float *conv1_weight, *conv1_bias;   /* [1280,1280,3], [1280] f32 */
+    vox_cuda_enc_layer_w_t enc[VOX_CUDA_ENC_LAYERS];
+    const float *enc_norm;                    /* [1280] */
+    const uint16_t *adapter_w0;               /* [3072,5120] bf16 */
+    const uint16_t *adapter_w1;               /* [3072,3072] bf16 */
+    const uint16_t *tok_embeddings;           /* [131072,3072] bf16 (tied LM head) */
+    vox_cuda_dec_layer_w_t dec[VOX_CUDA_DEC_LAYERS];
+    const float *dec_norm;                    /* [3072] */
+    const float *ada_scale;                   /* [n_dec_layers*3072] f32, voxtral.c:47-80 */
+} vox_cuda_weights_t;
+
+typedef struct vox_cuda_model vox_cuda_model_t;   /* weights in HBM, shared by streams */
+typedef struct vox_cuda_state vox_cuda_state_t;   /* one stream's device state */
+
+/* ---- lifetime (replaces vox_metal_init/available/shutdown,
+ *      voxtral_metal.h:20-26, call sites main.c:181-183,407-409) ---------- */
+int  vox_cuda_init(void);            /* 1 = ready, 0 = no usable sm_100 device */
+int  vox_cuda_available(void);
+void vox_cuda_shutdown(void);
+const char *vox_cuda_last_error(void);
+size_t vox_cuda_memory_used(void);   /* vox_metal_memory_used, voxtral_metal.h:282 */
+
+/* ---- weights (replaces the warm-up block in vox_load, voxtral.c:186-285:
+ *      vox_metal_warmup_bf16 / _merged_2 / _merged_3 / _decoder_ops) ------- */
+vox_cuda_model_t *vox_cuda_model_create(const vox_cuda_weights_t *w);
+/* vox_set_delay recomputes ada_scale on the host (voxtral.c:1681-1687). */
+int  vox_cuda_model_set_ada_scale(vox_cuda_model_t *m, const float *ada_scale);
+void vox_cuda_model_free(vox_cuda_model_t *m);
+
+/* ---- per-stream state (replaces vox_metal_shared_alloc'd KV caches,
+ *      voxtral_metal.h:206-207, voxtral_decoder.c:208-243,
+ *      voxtral_encoder.c:371-391, and the stream's conv tails
+ *      voxtral.c:469-483) ------------------------------------------------- */
+vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m);
+void vox_cuda_state_free(vox_cuda_state_t *s);
+/* kv_cache_len = kv_pos_offset = 0 (voxtral.c:781-782,1050-1051). */
+void vox_cuda_state_reset_decoder(vox_cuda_state_t *s);
+/* enc_kv_cache_len = enc_kv_pos_offset = 0, conv tails / residuals cleared,
+ * adapter buffer emptied (voxtral.c:797-824,1279-1280). */
+void vox_cuda_state_reset_encoder(vox_cuda_state_t *s);
+/* Logical decoder position = kv_pos_offset + kv_cache_len of the reference. */
+int  vox_cuda_decoder_position(const vox_cuda_state_t *s);
+/* Override the decoder position bookkeeping (test hook for the 8192-window
+ * wrap: lets a harness start right before a compaction boundary the way the
+ * reference allows through its public ctx fields, voxtral.h:197-205). */
+int  vox_cuda_decoder_set_position(vox_cuda_state_t *s, int logical_pos, int n_valid);
+
+/* ---- decoder (hot path #1) -------------------------------------------- */
+/* vox_decoder_prefill / vox_metal_decoder_prefill_step
+ * (voxtral_decoder.c:447-612, voxtral_metal.h:254). x: host [seq_len,3072]. */
+int vox_cuda_decoder_prefill(vox_cuda_state_t *s, const float *x, int seq_len);
+/* vox_decoder_forward / vox_metal_decoder_full_step (voxtral_decoder.c:640-780,
+ * voxtral_metal.h:219).  embed: host [3072].  logits: host [131072] or NULL.
+ * Returns the greedy token id (lowest index wins ties), <0 on error. */
+int vox_cuda_decoder_step(vox_cuda_state_t *s, const float *embed, float *logits);
+/* Same step with the embedding built on the device:
+ * embed = adapter_buf[adapter_index] + bf16->f32(tok_embeddings[prev_token])
+ * (voxtral.c:1106-1113).  Only the 4-byte token id crosses PCIe. */
+int vox_cuda_decoder_step_fused(vox_cuda_state_t *s, int prev_token,
+                                int adapter_index, float *logits);
+/* n greedy steps back to back on the device: step i consumes adapter token
+ * adapter_index+i and the token produced by step i-1 (the while loop of
+ * stream_run_decoder, voxtral.c:1105-1145, without a host round trip per
+ * token).  The caller truncates at EOS.  Returns n or <0. */
+int vox_cuda_decoder_run(vox_cuda_state_t *s, int prev_token, int adapter_index,
+                         int n, int *tokens_out);
+/* Logits [131072] of the last step (device -> host). */
+int vox_cuda_decoder_read_logits(vox_cuda_state_t *s, float *logits);
+/* Prompt prefill with device-built embeddings (voxtral.c:1036-1055). */
+int vox_cuda_decoder_prefill_fused(vox_cuda_state_t *s, const int *tokens,
+                                   int adapter_start, int seq_len);
+/* Alternatives of the LAST step (stream_fill_alts, voxtral.c:955-1010):
+ * candidate ids >= 1000 and != best, ordered by probability, kept while
+ * 1 - p_i/p_best <= cutoff.  Returns the count written (<= max_alt-1). */
+int vox_cuda_decoder_alternatives(vox_cuda_state_t *s, int max_alt, float cutoff,
+                                  int *ids);
+
+/* ---- encoder (hot path #2) -------------------------------------------- */
+/* vox_encoder_forward_incremental / vox_metal_encoder_full_step
+ * (voxtral_encoder.c:495-693, voxtral_metal.h:245): x host [new_len,1280]
+ * in/out, 32 layers + final norm against the device encoder KV ring. */
+int vox_cuda_encoder_step(vox_cuda_state_t *s, float *x, int new_len);
+/* stream_conv_stem (voxtral.c:581-759): mel host [n_mel,128] ->
+ * out host [*out_len,1280]; tails and the parity residual stay on device.
+ * out must hold (n_mel/2 + 2) rows. */
+int vox_cuda_conv_stem(vox_cuda_state_t *s, const float *mel, int n_mel,
+                       float *out, int *out_len);
+/* vox_adapter_forward (voxtral_encoder.c:699-737): enc_out host
+ * [enc_len,1280] -> out host [enc_len/4,3072]. */
+int vox_cuda_adapter(vox_cuda_state_t *s, const float *enc_out, int enc_len,
+                     float *out);
+/* Whole encoder side of stream_run_encoder (voxtral.c:845-934) on the device:
+ * conv stem -> 32 layers -> 4-alignment residual -> adapter -> append to the
+ * device adapter buffer.  mel: host [n_mel,128].  Returns the total number of
+ * adapter tokens now buffered (>=0) or <0 on error. */
+int vox_cuda_encode_chunk(vox_cuda_state_t *s, const float *mel, int n_mel);
+int vox_cuda_adapter_count(const vox_cuda_state_t *s);
+/* Copy adapter tokens [start, start+n) to host [n,3072] (tests, fallback API). */
+int vox_cuda_adapter_read(vox_cuda_state_t *s, int start, int n, float *out);
+/* Host-provided adapter tokens (used when the encoder ran elsewhere). */
+int vox_cuda_adapter_append(vox_cuda_state_t *s, const float *tok, int n);
+/* stream_adapter_compact (voxtral.c:762-775): forget tokens < keep_from. */
+int vox_cuda_adapter_discard_before(vox_cuda_state_t *s, int keep_from);
+
+/* ---- log-mel front end (hot path #3) ---------------------------------- */
+/* mel_compute_available (voxtral_audio.c:454-513), batched over frames:
+ * frame t reads samples[t*160 .. t*160+399]; out host [n_frames,128].
+ * samples must hold (n_frames-1)*160+400 values. */
+int vox_cuda_mel_frames(const float *samples, int n_frames, float *mel_out);
+
+/* ---- op-level hook (replaces vox_metal_sgemm_bf16, voxtral_metal.h:38,
+ *      call sites voxtral_kernels.c:199-204,218-229,249-254) -------------- */
+/* C[M,N] = A[M,K] (f32 host) x B[N,K]^T.  B_bf16 is a host pointer: if it is
+ * one of the matrices uploaded by vox_cuda_model_create (looked up by pointer
+ * identity, as Metal's weight cache does, voxtral_metal.m:165-201) the HBM
+ * copy is used, otherwise B is uploaded for the call.  m may be NULL.
+ * N % 64 == 0 and K % 32 == 0.  fp32 accumulate.  0 on success. */
+int vox_cuda_sgemm_bf16(vox_cuda_model_t *m, int M, int N, int K, const float *A,
+                        const uint16_t *B_bf16, float *C);
+
+/* ---- measurement helpers (bench.py / profiles) ------------------------ */
+/* vox_cuda_decoder_run timed with CUDA events on the launch stream: returns
+ * the average device time per step in milliseconds (<0 on error). */
+float vox_cuda_bench_decoder_steps(vox_cuda_state_t *s, int prev_token,
+                                   int adapter_index, int n, int *tokens_out);
+/* Number of kernel launches issued by this library since init. */
+unsigned long long vox_cuda_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VOX_CUDA_H */

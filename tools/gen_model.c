@@ -1,0 +1,227 @@
+/*
+ * tools/gen_model.c - deterministic random-init Voxtral Realtime 4B checkpoint
+ * in the reference's safetensors layout (711 BF16 tensors; names and shapes
+ * per /root/reference/MODEL.md:156-197, cross-checked with the loaders
+ * voxtral_encoder.c:62-142, voxtral.c:103-106, voxtral_decoder.c:61-141),
+ * plus a synthetic tekken.json whose piece for id k is " t<k>" so that text
+ * output and token ids are a bijection (tokenizer needs only vocab[].rank /
+ * token_bytes and special_tokens[].rank / token_str,
+ * voxtral_tokenizer.c:229-312).
+ *
+ * There is no network in the build or on the GPU box, so no real checkpoint
+ * exists; both the CPU oracle and the CUDA backend load the SAME file written
+ * by this tool.  The generator is integer-only (splitmix64 + a 16-byte
+ * Irwin-Hall sum), hence bit-identical on every host.
+ *
+ *   gen_model <out_dir> [--seed N] [--enc-layers N] [--dec-layers N]
+ *             [--emb-sigma F] [--gain F] [--bias-sigma F] [--no-tokenizer]
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdint.h>
+#include <math.h>
+
+#define ENC "mm_streams_embeddings.embedding_module.whisper_encoder"
+#define EMB "mm_streams_embeddings.embedding_module.tok_embeddings.weight"
+#define ADP "mm_streams_embeddings.embedding_module.audio_language_projection"
+
+enum { K_LIN, K_NORM, K_BIAS, K_EMB };
+
+typedef struct {
+    char name[192];
+    int ndim;
+    long shape[3];
+    int kind;
+    size_t numel, offset;
+} tensor_t;
+
+static tensor_t T[1024];
+static int NT = 0;
+
+static void add(const char *name, int kind, int ndim, long a, long b, long c) {
+    tensor_t *t = &T[NT++];
+    snprintf(t->name, sizeof(t->name), "%s", name);
+    t->kind = kind; t->ndim = ndim;
+    t->shape[0] = a; t->shape[1] = b; t->shape[2] = c;
+    t->numel = (size_t)a * (ndim > 1 ? b : 1) * (ndim > 2 ? c : 1);
+}
+
+static inline uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+static inline unsigned bytesum(uint64_t x) {
+    x = (x & 0x00FF00FF00FF00FFull) + ((x >> 8) & 0x00FF00FF00FF00FFull);
+    x = (x & 0x0000FFFF0000FFFFull) + ((x >> 16) & 0x0000FFFF0000FFFFull);
+    return (unsigned)((x & 0xFFFFFFFFull) + (x >> 32));
+}
+
+/* ~N(0,1): sum of 16 uniform bytes, mean 2040, variance 16*(256^2-1)/12 */
+static inline float std_normal(uint64_t key, uint64_t i) {
+    unsigned s = bytesum(mix64(key + 2 * i)) + bytesum(mix64(key + 2 * i + 1));
+    return ((float)s - 2040.0f) * (1.0f / 295.60277f);
+}
+
+static inline uint16_t f32_to_bf16(float f) {
+    uint32_t u; memcpy(&u, &f, 4);
+    uint32_t r = ((u >> 16) & 1u) + 0x7FFFu;
+    return (uint16_t)((u + r) >> 16);
+}
+
+int main(int argc, char **argv) {
+    if (argc < 2) {
+        fprintf(stderr, "usage: %s <out_dir> [--seed N] [--enc-layers N] [--dec-layers N]"
+                        " [--emb-sigma F] [--gain F] [--bias-sigma F] [--no-tokenizer]\n", argv[0]);
+        return 2;
+    }
+    const char *out = argv[1];
+    uint64_t seed = 1234;
+    int enc_layers = 32, dec_layers = 26, tokenizer = 1;
+    float emb_sigma = 0.05f, gain = 1.0f, bias_sigma = 0.02f;
+    for (int i = 2; i < argc; i++) {
+        if (!strcmp(argv[i], "--seed") && i + 1 < argc) seed = strtoull(argv[++i], 0, 10);
+        else if (!strcmp(argv[i], "--enc-layers") && i + 1 < argc) enc_layers = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--dec-layers") && i + 1 < argc) dec_layers = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--emb-sigma") && i + 1 < argc) emb_sigma = (float)atof(argv[++i]);
+        else if (!strcmp(argv[i], "--gain") && i + 1 < argc) gain = (float)atof(argv[++i]);
+        else if (!strcmp(argv[i], "--bias-sigma") && i + 1 < argc) bias_sigma = (float)atof(argv[++i]);
+        else if (!strcmp(argv[i], "--no-tokenizer")) tokenizer = 0;
+        else { fprintf(stderr, "gen_model: bad argument %s\n", argv[i]); return 2; }
+    }
+
+    char n[256];
+    add(EMB, K_EMB, 2, 131072, 3072, 1);
+    add(ENC ".conv_layers.0.conv.weight", K_LIN, 3, 1280, 128, 3);
+    add(ENC ".conv_layers.0.conv.bias", K_BIAS, 1, 1280, 1, 1);
+    add(ENC ".conv_layers.1.conv.weight", K_LIN, 3, 1280, 1280, 3);
+    add(ENC ".conv_layers.1.conv.bias", K_BIAS, 1, 1280, 1, 1);
+    for (int i = 0; i < enc_layers; i++) {
+#define EL(suffix, kind, nd, a, b) \
+        snprintf(n, sizeof(n), ENC ".transformer.layers.%d." suffix, i); add(n, kind, nd, a, b, 1)
+        EL("attention.wq.weight", K_LIN, 2, 2048, 1280);
+        EL("attention.wq.bias", K_BIAS, 1, 2048, 1);
+        EL("attention.wk.weight", K_LIN, 2, 2048, 1280);
+        EL("attention.wv.weight", K_LIN, 2, 2048, 1280);
+        EL("attention.wv.bias", K_BIAS, 1, 2048, 1);
+        EL("attention.wo.weight", K_LIN, 2, 1280, 2048);
+        EL("attention.wo.bias", K_BIAS, 1, 1280, 1);
+        EL("attention_norm.weight", K_NORM, 1, 1280, 1);
+        EL("feed_forward.w1.weight", K_LIN, 2, 5120, 1280);
+        EL("feed_forward.w2.weight", K_LIN, 2, 1280, 5120);
+        EL("feed_forward.w2.bias", K_BIAS, 1, 1280, 1);
+        EL("feed_forward.w3.weight", K_LIN, 2, 5120, 1280);
+        EL("ffn_norm.weight", K_NORM, 1, 1280, 1);
+    }
+    add(ENC ".transformer.norm.weight", K_NORM, 1, 1280, 1, 1);
+    add(ADP ".0.weight", K_LIN, 2, 3072, 5120, 1);
+    add(ADP ".2.weight", K_LIN, 2, 3072, 3072, 1);
+    for (int i = 0; i < dec_layers; i++) {
+#define DL(suffix, kind, nd, a, b) \
+        snprintf(n, sizeof(n), "layers.%d." suffix, i); add(n, kind, nd, a, b, 1)
+        DL("ada_rms_norm_t_cond.0.weight", K_LIN, 2, 32, 3072);
+        DL("ada_rms_norm_t_cond.2.weight", K_LIN, 2, 3072, 32);
+        DL("attention.wq.weight", K_LIN, 2, 4096, 3072);
+        DL("attention.wk.weight", K_LIN, 2, 1024, 3072);
+        DL("attention.wv.weight", K_LIN, 2, 1024, 3072);
+        DL("attention.wo.weight", K_LIN, 2, 3072, 4096);
+        DL("attention_norm.weight", K_NORM, 1, 3072, 1);
+        DL("feed_forward.w1.weight", K_LIN, 2, 9216, 3072);
+        DL("feed_forward.w2.weight", K_LIN, 2, 3072, 9216);
+        DL("feed_forward.w3.weight", K_LIN, 2, 9216, 3072);
+        DL("ffn_norm.weight", K_NORM, 1, 3072, 1);
+    }
+    add("norm.weight", K_NORM, 1, 3072, 1, 1);
+
+    /* header */
+    size_t off = 0, hcap = (size_t)NT * 320 + 64, hlen = 0;
+    char *hdr = (char *)malloc(hcap);
+    hdr[hlen++] = '{';
+    for (int i = 0; i < NT; i++) {
+        tensor_t *t = &T[i];
+        t->offset = off;
+        size_t nb = t->numel * 2;
+        char shp[64];
+        if (t->ndim == 1) snprintf(shp, sizeof(shp), "[%ld]", t->shape[0]);
+        else if (t->ndim == 2) snprintf(shp, sizeof(shp), "[%ld,%ld]", t->shape[0], t->shape[1]);
+        else snprintf(shp, sizeof(shp), "[%ld,%ld,%ld]", t->shape[0], t->shape[1], t->shape[2]);
+        hlen += (size_t)snprintf(hdr + hlen, hcap - hlen,
+            "%s\"%s\":{\"dtype\":\"BF16\",\"shape\":%s,\"data_offsets\":[%zu,%zu]}",
+            i ? "," : "", t->name, shp, off, off + nb);
+        off += nb;
+    }
+    hdr[hlen++] = '}';
+    while (hlen % 8) hdr[hlen++] = ' ';
+
+    char path[1024];
+    snprintf(path, sizeof(path), "%s/consolidated.safetensors", out);
+    FILE *f = fopen(path, "wb");
+    if (!f) { perror(path); return 1; }
+    uint64_t hl = hlen;
+    fwrite(&hl, 8, 1, f);
+    fwrite(hdr, 1, hlen, f);
+
+    size_t maxel = 0;
+    for (int i = 0; i < NT; i++) if (T[i].numel > maxel) maxel = T[i].numel;
+    uint16_t *buf = (uint16_t *)malloc(maxel * 2);
+    if (!buf) { fprintf(stderr, "gen_model: out of memory\n"); return 1; }
+
+    for (int ti = 0; ti < NT; ti++) {
+        tensor_t *t = &T[ti];
+        /* key depends on the tensor NAME, so reduced-depth files share weights
+         * with the full file layer by layer */
+        uint64_t key = mix64(seed);
+        for (const char *p = t->name; *p; p++) key = mix64(key ^ (uint64_t)(unsigned char)*p);
+        float scale = 1.0f, shift = 0.0f;
+        if (t->kind == K_LIN) {
+            long fan_in = (t->ndim > 1 ? t->shape[1] : 1) * (t->ndim > 2 ? t->shape[2] : 1);
+            scale = gain / sqrtf((float)fan_in);
+        } else if (t->kind == K_NORM) { scale = 0.05f; shift = 1.0f; }
+        else if (t->kind == K_BIAS) scale = bias_sigma;
+        else if (t->kind == K_EMB) scale = emb_sigma;
+        size_t ne = t->numel;
+        #pragma omp parallel for schedule(static)
+        for (size_t i = 0; i < ne; i++)
+            buf[i] = f32_to_bf16(shift + scale * std_normal(key, i));
+        if (t->kind == K_EMB)  /* EOS (id 2) row zero: greedy never stops by chance */
+            memset(buf + (size_t)2 * 3072, 0, 3072 * 2);
+        if (fwrite(buf, 2, ne, f) != ne) { perror("fwrite"); return 1; }
+    }
+    fclose(f);
+    free(buf);
+    fprintf(stderr, "gen_model: %d tensors, %.3f GB -> %s (seed %llu, enc %d, dec %d, emb_sigma %g)\n",
+            NT, (double)(off + 8 + hlen) / 1e9, path, (unsigned long long)seed,
+            enc_layers, dec_layers, emb_sigma);
+
+    if (tokenizer) {
+        snprintf(path, sizeof(path), "%s/tekken.json", out);
+        f = fopen(path, "w");
+        if (!f) { perror(path); return 1; }
+        static const char b64[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+        fprintf(f, "{\"config\":{\"default_vocab_size\":131072,\"default_num_special_tokens\":1000},\"vocab\":[");
+        for (int r = 0; r < 131072 - 1000; r++) {
+            char piece[32], enc[64];
+            int len = snprintf(piece, sizeof(piece), " t%d", 1000 + r), o = 0;
+            for (int i = 0; i < len; i += 3) {
+                unsigned v = (unsigned char)piece[i] << 16;
+                if (i + 1 < len) v |= (unsigned char)piece[i + 1] << 8;
+                if (i + 2 < len) v |= (unsigned char)piece[i + 2];
+                enc[o++] = b64[(v >> 18) & 63];
+                enc[o++] = b64[(v >> 12) & 63];
+                enc[o++] = (i + 1 < len) ? b64[(v >> 6) & 63] : '=';
+                enc[o++] = (i + 2 < len) ? b64[v & 63] : '=';
+            }
+            enc[o] = 0;
+            fprintf(f, "%s{\"rank\":%d,\"token_bytes\":\"%s\",\"token_str\":null}", r ? "," : "", r, enc);
+        }
+        fprintf(f, "],\"special_tokens\":[");
+        for (int r = 0; r < 1000; r++)
+            fprintf(f, "%s{\"rank\":%d,\"token_str\":\"<sp%d>\",\"is_control\":true}", r ? "," : "", r, r);
+        fprintf(f, "]}");
+        fclose(f);
+    }
+    return 0;
+}

@@ -1,0 +1,101 @@
+// vox_internal.h - host-side structures shared by the .cu files of the backend.
+#pragma once
+#include "vox_common.cuh"
+
+// Device-resident scalars of one decoder stream.  Kernels read them from HBM so
+// that a captured CUDA graph can be replayed for every token without the host
+// patching parameters; the last kernel of a step advances them.
+struct DecStepParams {
+    int pos;            // logical position of the token being processed (kv_pos_offset + kv_cache_len)
+    int n_valid;        // KV entries valid BEFORE this step (<= DEC_WINDOW-1 after clamping)
+    int prev_token;     // token whose embedding is added (voxtral.c:1106-1113)
+    int adapter_index;  // physical row in the device adapter buffer
+    int use_host_embed; // 1: x comes from d_embed_in, 0: built on device
+    int out_token;      // greedy token of the last step
+    int step_count;     // steps executed since the counter was last reset
+    int pad;
+};
+
+struct DecLayerDev {
+    const uint16_t *wqkv;   // [6144,3072] rows: wq(4096) | wk(1024) | wv(1024)
+    const uint16_t *wo;     // [3072,4096]
+    const uint16_t *w13;    // [18432,3072] row 2i = w1[i], row 2i+1 = w3[i]
+    const uint16_t *w2;     // [3072,9216]
+    const float *attn_norm; // [3072]
+    const float *ffn_norm;  // [3072]
+};
+
+struct EncLayerDev {
+    const uint16_t *wqkv;   // [6144,1280] rows: wq | wk | wv
+    const uint16_t *wo;     // [1280,2048]
+    const uint16_t *w13;    // [10240,1280] row 2i = w1[i], row 2i+1 = w3[i]
+    const uint16_t *w2;     // [1280,5120]
+    const float *bqkv;      // [6144] (wk part zero)
+    const float *bo;        // [1280]
+    const float *b2;        // [1280]
+    const float *attn_norm; // [1280]
+    const float *ffn_norm;  // [1280]
+};
+
+struct vox_cuda_model {
+    int n_enc, n_dec;
+    // one arena, laid out in execution order (decoder first: its walk per token
+    // is then a single linear pass through HBM)
+    uint8_t *arena;
+    size_t arena_bytes;
+    DecLayerDev dec[VOX_CUDA_DEC_LAYERS];
+    EncLayerDev enc[VOX_CUDA_ENC_LAYERS];
+    const uint16_t *tok_emb;   // [131072,3072]
+    const float *dec_norm;     // [3072]
+    float *ada_scale;          // [n_dec,3072]
+    const float *enc_norm;     // [1280]
+    const uint16_t *conv0_w;   // [1280, 3*128]  tap-major: col = tap*128 + ic  (bf16, exact: source is bf16)
+    const uint16_t *conv1_w;   // [1280, 3*1280] tap-major
+    const float *conv0_b, *conv1_b;
+    const uint16_t *adapter_w0; // [3072,5120]
+    const uint16_t *adapter_w1; // [3072,3072]
+    float *inv_freq_dec;       // [64]  1/theta^(2d/128)
+    float *inv_freq_enc;       // [32]  1/theta^(2d/64)
+    // host pointer -> device pointer registry for vox_cuda_sgemm_bf16
+    struct Reg { const void *host; const void *dev; size_t bytes; } reg[512];
+    int n_reg;
+};
+
+struct vox_cuda_state {
+    vox_cuda_model *m;
+    cudaStream_t stream;
+    // ---- decoder ----
+    float *kv_k, *kv_v;          // [n_dec][DEC_WINDOW][1024] fp32 ring, slot = logical & 8191
+    DecStepParams *d_params;     // device
+    DecStepParams h_params;      // host mirror (authoritative between calls)
+    float *d_x, *d_q, *d_attn, *d_h, *d_logits, *d_embed_in, *d_rope;
+    float *d_attn_part;          // [NSPLIT][32][DEC_HD+2]
+    float *d_blockmax;           // per-CTA (val, idx) pairs of the logits kernel
+    int *d_tokens;               // ring of produced tokens (device), [TOKENS_RING]
+    int *h_tokens;               // pinned host copy
+    float *h_pinned;             // pinned staging (embed / logits)
+    cudaGraphExec_t step_graph;
+    int graph_ready;
+    // prefill scratch (allocated on demand)
+    float *pf_buf; size_t pf_bytes;
+    // ---- encoder ----
+    void *enc_priv;              // EncState*, see enc_host.cu
+    // ---- adapter tokens (device) ----
+    float *adapter_buf;          // [adapter_cap][3072]
+    int adapter_cap, adapter_count, adapter_offset; // count = total logical, offset = first kept
+    // ---- timing ----
+    cudaEvent_t ev0, ev1;
+};
+
+constexpr int ATTN_NSPLIT = 16;
+constexpr int TOKENS_RING = 65536;
+constexpr int LOGITS_ROWS_PER_CTA = 128;
+
+// dec_kernels.cu
+int dec_launch_step(vox_cuda_state *s, cudaStream_t st);
+int dec_prefill(vox_cuda_state *s, const float *d_x_in, int seq_len);
+
+// sgemm.cu : C[M,N] = A[M,K] fp32 (lda) x W[N,K]^T bf16, fp32 accumulate, CUDA cores
+enum { EPI_NONE = 0, EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4 };
+int sgemm_bf16w(cudaStream_t st, int M, int N, int K, const float *A, long lda,
+                const uint16_t *W, float *C, long ldc, const float *bias, int epi);
