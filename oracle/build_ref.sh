@@ -56,6 +56,21 @@ gcc -shared -fopenmp -o "$OUT/libvoxref.so" $OBJS "$OUT/ref_shim.o" "$OUT/sgemm_
     $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
 gcc -fopenmp -o "$OUT/voxtral_ref" "$OUT/main.o" $OBJS "$OUT/sgemm_fallback.o" \
     $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
-# the copied OpenBLAS finds its own deps next to itself
+# Strict-IEEE variant (no -ffast-math, no vector libm): same sources, same BLAS.
+# -ffast-math lets gcc re-associate the DFT-table angle 2*pi*k*n/400 and call
+# libmvec's 4-ulp vector cosf/sinf (voxtral_audio.c:531-537), which moves table
+# entries by up to ~1e-4; the strict build is what the C source says, evaluated
+# in IEEE float order, and is the pin for the 1e-5 mel tolerance.
+SCFLAGS="-O2 -march=x86-64-v3 -fno-fast-math -ffp-contract=off -fopenmp -DUSE_BLAS -DUSE_OPENBLAS $BLAS_DEF -I$HERE -I$REF -I$INC -fPIC -w"
+SOBJS=""
+for s in $SRCS; do
+    o="$OUT/strict_${s%.c}.o"
+    gcc $SCFLAGS -c "$REF/$s" -o "$o"
+    SOBJS="$SOBJS $o"
+done
+gcc $SCFLAGS -c "$HERE/ref_shim.c" -o "$OUT/strict_ref_shim.o"
+gcc $SCFLAGS -c "$HERE/sgemm_fallback.c" -o "$OUT/strict_sgemm_fallback.o"
+gcc -shared -fopenmp -o "$OUT/libvoxref_strict.so" $SOBJS "$OUT/strict_ref_shim.o" "$OUT/strict_sgemm_fallback.o" \
+    $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
 rm -f "$OUT"/*.o
 echo "build_ref: built $OUT/libvoxref.so and $OUT/voxtral_ref"

@@ -13,6 +13,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libvoxref.so")
+REF_STRICT_SO = os.path.join(ROOT, "oracle", "_ref", "libvoxref_strict.so")
 sys.path.insert(0, os.path.join(ROOT, "voxtral.c_b200"))
 
 f32p = C.POINTER(C.c_float)
@@ -143,3 +144,19 @@ class Ref:
 
     def fill_weights(self, w):
         self.L.refshim_fill_weights(self.ctx, C.byref(w))
+
+
+def strict_stream_mel(samples, delay_tokens=6, chunk=0):
+    """Streaming mel of the strict-IEEE reference build (oracle/build_ref.sh):
+    the pin for the 1e-5 mel tolerance (the -ffast-math build moves DFT table
+    entries by ~1e-4 and its mel by ~2e-4)."""
+    L = C.CDLL(REF_STRICT_SO)
+    L.refshim_stream_mel.restype = f32p
+    L.refshim_stream_mel.argtypes = [f32p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
+    L.refshim_free.argtypes = [C.c_void_p]
+    x = np.ascontiguousarray(samples, dtype=np.float32)
+    n = C.c_int()
+    p = L.refshim_stream_mel(x.ctypes.data_as(f32p), len(x), delay_tokens, chunk, C.byref(n))
+    a = np.ctypeslib.as_array(p, shape=(n.value, 128)).copy()
+    L.refshim_free(p)
+    return a
