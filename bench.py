@@ -111,7 +111,7 @@ def run_cuda(args, rank, world):
     hm = hostmodel.HostModel(mdir)
     model = vc.check(L.vox_cuda_model_create(C.byref(hm.weights)), "model_create")
     st = vc.check(L.vox_cuda_state_create(model), "state_create")
-    x = synth_clip(CLIP_SECONDS, 1 + rank)
+    x = synth_clip(args.clip_seconds, 1 + rank)
     buf, nf = frame_buffer(x)
     mel = np.empty((nf, 128), np.float32)
 
@@ -162,7 +162,7 @@ def run_cuda(args, rank, world):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = DEC_BYTES_PER_TOKEN / (ms_step * 1e-3) / 1e9
-        value = CLIP_SECONDS * args.steps * world / t_max
+        value = args.clip_seconds * args.steps * world / t_max
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_max / args.steps, "higher_is_better": True,
@@ -246,6 +246,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--clip-seconds", type=float, default=CLIP_SECONDS, help="profiling only; the headline is 60 s")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
