@@ -37,7 +37,11 @@ extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) {
     DM(s->d_x, DEC_DIM * 4); DM(s->d_q, DEC_QDIM * 4); DM(s->d_attn, DEC_QDIM * 4);
     DM(s->d_h, DEC_HIDDEN * 4); DM(s->d_logits, (size_t)VOCAB * 4); DM(s->d_embed_in, DEC_DIM * 4);
     DM(s->d_rope, DEC_HD * 4);
-    DM(s->d_attn_part, (size_t)ATTN_NSPLIT * DEC_HEADS * (DEC_HD + 2) * 4);
+    {
+        size_t part = (size_t)ATTN_NSPLIT * DEC_HEADS * (DEC_HD + 2);
+        if ((size_t)dec_mega_attn_part_floats() > part) part = (size_t)dec_mega_attn_part_floats();
+        DM(s->d_attn_part, part * 4);
+    }
     DM(s->d_blockmax, (size_t)2 * (VOCAB / LOGITS_ROWS_PER_CTA) * 4);
     DM(s->d_tokens, (size_t)TOKENS_RING * 4);
     s->adapter_cap = 1024;
@@ -48,6 +52,11 @@ extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) {
     if (cudaMemsetAsync(s->kv_k, 0, kv, s->stream) != cudaSuccess) goto fail;
     if (cudaMemsetAsync(s->kv_v, 0, kv, s->stream) != cudaSuccess) goto fail;
     if (enc_state_create(s)) goto fail;
+    {
+        const char *env = getenv("VOX_CUDA_DEC_GRAPH");
+        s->use_graph_steps = (env && atoi(env)) ? 1 : 0;
+    }
+    if (dec_mega_init(s)) goto fail;
     vox_cuda_state_reset_decoder(s);
     vox_cuda_state_reset_encoder(s);
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) goto fail;
@@ -63,6 +72,7 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->step_graph) cudaGraphExecDestroy(s->step_graph);
     enc_state_free(s);
+    dec_mega_free(s);
     void *ptrs[] = {s->kv_k, s->kv_v, s->d_params, s->d_x, s->d_q, s->d_attn, s->d_h, s->d_logits,
                     s->d_embed_in, s->d_rope, s->d_attn_part, s->d_blockmax, s->d_tokens,
                     s->adapter_buf, s->pf_buf};
@@ -115,6 +125,13 @@ static inline int step_kernels(const vox_cuda_state *s) { return 3 + 6 * s->m->n
 
 // Enqueue n steps; tokens land in d_tokens[(step_count0 + i) & ring].
 static int enqueue_steps(vox_cuda_state *s, int n) {
+    if (!s->use_graph_steps) {
+        // one persistent cooperative kernel runs up to MEGA_CHUNK steps back to back
+        const int MEGA_CHUNK = 512;
+        for (int i = 0; i < n; i += MEGA_CHUNK)
+            if (dec_mega_launch(s, n - i < MEGA_CHUNK ? n - i : MEGA_CHUNK)) return -1;
+        return 0;
+    }
     if (ensure_graph(s)) return -1;
     for (int i = 0; i < n; i++) CUDA_TRY(cudaGraphLaunch(s->step_graph, s->stream));
     g_launch_count += (unsigned long long)n * step_kernels(s);
@@ -220,7 +237,7 @@ extern "C" float vox_cuda_bench_decoder_steps(vox_cuda_state_t *s, int prev_toke
     s->h_params.prev_token = prev_token;
     s->h_params.adapter_index = phys;
     const int c0 = s->h_params.step_count;
-    if (push_params(s) || ensure_graph(s)) return -1.f;
+    if (push_params(s) || (s->use_graph_steps && ensure_graph(s))) return -1.f;
     if (cudaEventRecord(s->ev0, s->stream) != cudaSuccess) return -1.f;
     if (enqueue_steps(s, n)) return -1.f;
     if (cudaEventRecord(s->ev1, s->stream) != cudaSuccess) return -1.f;

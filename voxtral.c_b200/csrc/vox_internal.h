@@ -76,6 +76,8 @@ struct vox_cuda_state {
     float *h_pinned;             // pinned staging (embed / logits)
     cudaGraphExec_t step_graph;
     int graph_ready;
+    void *mega;                  // MegaHost*, dec_mega.cu (persistent cooperative step kernel)
+    int use_graph_steps;         // 1: legacy kernel-per-op CUDA graph (VOX_CUDA_DEC_GRAPH=1), 0: megakernel
     // prefill scratch (allocated on demand)
     float *pf_buf; size_t pf_bytes;
     // ---- encoder ----
@@ -90,6 +92,12 @@ struct vox_cuda_state {
 constexpr int ATTN_NSPLIT = 16;
 constexpr int TOKENS_RING = 65536;
 constexpr int LOGITS_ROWS_PER_CTA = 128;
+
+// dec_mega.cu
+int dec_mega_init(vox_cuda_state *s);
+void dec_mega_free(vox_cuda_state *s);
+int dec_mega_launch(vox_cuda_state *s, int n_steps);
+int dec_mega_attn_part_floats(void);
 
 // dec_kernels.cu
 int dec_launch_step(vox_cuda_state *s, cudaStream_t st);
