@@ -6,6 +6,7 @@
 #include <math.h>
 
 void vox_mem_account(long delta);
+const unsigned *dec_mega_error_record(vox_cuda_state *s);
 int enc_state_create(vox_cuda_state *s);
 void enc_state_free(vox_cuda_state *s);
 void enc_state_reset(vox_cuda_state *s);
@@ -244,7 +245,9 @@ extern "C" float vox_cuda_bench_decoder_steps(vox_cuda_state_t *s, int prev_toke
     if (cudaMemcpyAsync(s->h_tokens, s->d_tokens, (size_t)TOKENS_RING * 4, cudaMemcpyDeviceToHost,
                         s->stream) != cudaSuccess) return -1.f;
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
-        vox_set_error("bench_decoder_steps: %s", cudaGetErrorString(cudaGetLastError()));
+        const unsigned *er = dec_mega_error_record(s);
+        vox_set_error("bench_decoder_steps: %s (mega watchdog code %u cta %u tid %u info 0x%x)",
+                      cudaGetErrorString(cudaGetLastError()), er ? er[0] : 0, er ? er[1] : 0, er ? er[2] : 0, er ? er[3] : 0);
         return -1.f;
     }
     float ms = 0.f;

@@ -9,14 +9,15 @@
 //   * warp 8 (one elected lane) is the PRODUCER: it walks the static list of
 //     weight tiles this CTA owns - contiguous row ranges of every matrix, in
 //     consumption order, across phase, layer and token boundaries - and streams
-//     them into an 8 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
+//     them into a 7 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
 //     bulk copies, mbarrier complete_tx, L2 evict_first).  It never waits for
 //     activations, only for ring space, so the HBM pipe stays busy while the
-//     consumers sit in a grid barrier (192 KB/SM = 4.4 us of HBM time).
-//   * warps 0-7 are CONSUMERS: each warp owns a fixed K-slice of every row
-//     (the activation slice lives in registers), multiplies tiles as they land,
-//     and the per-tile epilogue applies RoPE + KV-ring write, residual add,
-//     SwiGLU, or logits + running argmax.
+//     consumers sit in a grid barrier (168 KB/SM = 3.8 us of HBM time).
+//   * warps 0-7 are CONSUMERS: tiles (1-4 whole rows) are dealt round-robin to
+//     warps 0-6 (warp s owns ring stage s), each warp multiplies its tile against the activation vector
+//     in shared memory on its own - no cross-warp reduction, no per-tile CTA
+//     barrier - and its epilogue lanes apply RoPE + KV-ring write, residual
+//     add, SwiGLU, or logits + running argmax.
 //   * phases are separated by a grid-wide barrier (release/acquire counter in
 //     global memory); attention is split over (kv head, key range) CTAs and its
 //     partials are merged in the wo prologue.
@@ -25,33 +26,43 @@
 // the summation order differs.
 #include "vox_internal.h"
 #include <stdlib.h>
+#include <string.h>
 
 namespace mk {
 
 constexpr int CW = 8;                       // consumer warps
 constexpr int CT = CW * 32;                 // consumer threads
-constexpr int NT = CT + 32;                 // + producer warp
+constexpr int NT = CT + 64;                 // + producer warp + L2 prefetch warp
 constexpr int STAGE_BYTES = 24576;
-constexpr int NSTAGE = 8;
+constexpr int NSTAGE = 7;
 constexpr int MAXTR = 4;                    // rows per tile at K = 3072
 constexpr int PART_LD = DEC_HD + 4;         // acc[128], m, l, pad (16-byte rows)
 constexpr int MAX_SPLITS = 32;
+constexpr int KMAX = DEC_HIDDEN;            // longest activation vector (w2 input)
 
 template <int K> struct TileRows { static constexpr int v = STAGE_BYTES / (K * 2); };
 static_assert(TileRows<3072>::v == 4 && TileRows<4096>::v == 3 && TileRows<9216>::v == 1, "");
 
+// Activation vector of the current phase, split so that lane l reads conflict-free
+// float4s: xa[c] = x[8c..8c+3], xb[c] = x[8c+4..8c+7].  The attention phase (which
+// has no activation vector) reuses the space for its per-warp partials.
+struct XVec { float4 xa[KMAX / 8]; float4 xb[KMAX / 8]; };
+struct AttnScratch { float qs[4][DEC_HD]; float wsm[CW][4][PART_LD]; };
+static_assert(NSTAGE <= CW, "one consumer warp per ring stage");
+static_assert(sizeof(AttnScratch) <= sizeof(XVec), "attention scratch must fit in the activation buffer");
+
 struct Smem {
     alignas(128) unsigned char ring[NSTAGE][STAGE_BYTES];
+    alignas(16) union { XVec x; AttnScratch at; } u;
     alignas(8) unsigned long long full[NSTAGE];
     alignas(8) unsigned long long empty[NSTAGE];
-    float part[2][MAXTR][CW];
     float red[CW];
     float rope[DEC_HD];                     // (cos, sin) x 64 for this step's position
-    alignas(16) float qs[4][DEC_HD];
-    alignas(16) float wsm[CW][4][PART_LD];
     float bv[CW];
     int bi[CW];
     int token;
+    volatile unsigned issued;               // tiles the producer has requested so far (read by the L2 prefetcher)
+    float resid[64];                        // residual values of the rows this CTA owns in wo / w2
 };
 
 struct Params {
@@ -67,7 +78,10 @@ struct Params {
     unsigned *bar;
     unsigned bar_base;
     int n_steps;
+    int inflight;                           // max tiles requested but not yet landed (1..NSTAGE)
+    int l2_ahead;                           // tiles the L2 prefetcher runs ahead of the producer (0 = off)
     unsigned *err;
+    unsigned long long *prof;               // optional [G][8] cycle counters of consumer thread 0 (debug)
 };
 
 // ---- PTX helpers ---------------------------------------------------------------
@@ -92,11 +106,18 @@ __device__ __forceinline__ bool mbar_try_wait(unsigned long long *b, unsigned pa
     return ok != 0;
 }
 // bounded wait: a protocol bug must end in a trap, never in a hung GPU
-__device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity, unsigned *err) {
+__device__ __noinline__ void die(volatile unsigned *err, unsigned code, unsigned info) {
+    if (atomicCAS((unsigned *)err, 0u, code) == 0u) {
+        err[1] = blockIdx.x; err[2] = threadIdx.x; err[3] = info;
+        __threadfence_system();
+    }
+    __trap();
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity, unsigned *err, unsigned info = 0) {
     if (mbar_try_wait(b, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(b, parity)) {
-        if (clock64() - t0 > 8000000000LL) { atomicExch(err, 1u); __trap(); }
+        if (clock64() - t0 > 3000000000LL) die(err, 1u, info);
     }
 }
 __device__ __forceinline__ unsigned long long policy_evict_first() {
@@ -110,11 +131,16 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
         ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
 
-__device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
+__device__ __forceinline__ unsigned ld_relaxed(const unsigned *p) {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
@@ -123,25 +149,33 @@ __device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
 
 // Grid-wide barrier for the consumer threads of all CTAs.  `target` is the
 // counter value at which this barrier opens (wrap-safe signed compare).
-__device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsigned *err) {
+// bar.sync orders the CTA's writes before thread 0's release; thread 0's acquire
+// fence followed by bar.sync orders the other CTAs' writes before our reads.
+__device__ __forceinline__ unsigned atom_release_add(unsigned *p, unsigned v) {
+    unsigned old;
+    asm volatile("atom.release.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsigned *err, long long *t_own = nullptr,
+                                          long long *t_atom = nullptr) {
     consumer_sync();
     if (threadIdx.x == 0) {
-        red_release_add(bar, 1u);
-        const long long t0 = clock64();
-        while ((int)(ld_acquire(bar) - target) < 0) {
-            if (clock64() - t0 > 8000000000LL) { atomicExch(err, 2u); __trap(); }
+        if (t_atom) {                           // profiling variant: returning atomic = measurable round trip
+            const long long ta_ = clock64();
+            const unsigned old = atom_release_add(bar, 1u);
+            *t_atom += (clock64() - ta_) + (long long)(old & 0u);
+        } else {
+            red_release_add(bar, 1u);
         }
+        const long long t0 = clock64();
+        while ((int)(ld_relaxed(bar) - target) < 0) {
+            if (clock64() - t0 > 3000000000LL) die(err, 2u, target);
+        }
+        if (t_own) *t_own += clock64() - t0;    // spin time
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     consumer_sync();
 }
-
-struct Pipe {
-    int stage;
-    unsigned phase;
-    __device__ __forceinline__ void advance() {
-        if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
-    }
-};
 
 // rows [r0, r1) of an R-row matrix owned by CTA c; boundaries are multiples of `unit`
 __device__ __forceinline__ void cta_rows(int R, int unit, int c, int G, int &r0, int &r1) {
@@ -150,90 +184,127 @@ __device__ __forceinline__ void cta_rows(int R, int unit, int c, int G, int &r0,
     r1 = (int)(((long long)(c + 1) * U) / G) * unit;
 }
 
+// Tiles are numbered globally per CTA (g = 0, 1, ...) in consumption order;
+// tile g lives in ring stage g % NSTAGE during mbarrier phase (g / NSTAGE) & 1.
+
 // ---- producer ----------------------------------------------------------------------
 template <int K>
-__device__ __forceinline__ void produce(Smem &sm, Pipe &pp, const uint16_t *W, int R, int unit, int c, int G,
-                                        unsigned long long policy, unsigned *err) {
+__device__ __forceinline__ void produce(Smem &sm, unsigned &g, const uint16_t *W, int R, int unit, int c, int G,
+                                        unsigned long long policy, unsigned inflight, unsigned *err) {
     constexpr int TR = TileRows<K>::v;
     int r0, r1;
     cta_rows(R, unit, c, G, r0, r1);
-    for (int r = r0; r < r1; r += TR) {
+    for (int r = r0; r < r1; r += TR, g++) {
         const int n = min(TR, r1 - r);
         const unsigned bytes = (unsigned)n * K * 2u;
-        mbar_wait(&sm.empty[pp.stage], pp.phase ^ 1u, err);
-        mbar_expect_tx(&sm.full[pp.stage], bytes);
-        bulk_g2s(sm.ring[pp.stage], W + (size_t)r * K, bytes, &sm.full[pp.stage], policy);
-        pp.advance();
-    }
-}
-
-// ---- consumer: tile dot products -------------------------------------------------------
-// Lane l of warp w owns columns (j*256 + w*32 + l)*4 .. +3, j < K/1024, of every row.
-template <int K, int TR>
-__device__ __forceinline__ void tile_dot(const unsigned char *tile, int nrows, const float (&xr)[K / 256],
-                                         float (&acc)[TR], int w, int lane) {
-    constexpr int J = K / 1024;
-    #pragma unroll
-    for (int r = 0; r < TR; r++) {
-        float a = 0.f;
-        if (r < nrows) {
-            const uint2 *rowp = reinterpret_cast<const uint2 *>(tile + (size_t)r * K * 2) + w * 32 + lane;
-            uint2 v[J];
-            #pragma unroll
-            for (int j = 0; j < J; j++) v[j] = rowp[j * 256];
-            #pragma unroll
-            for (int j = 0; j < J; j++) {
-                a = fmaf(bf16_lo(v[j].x), xr[4 * j + 0], a);
-                a = fmaf(bf16_hi(v[j].x), xr[4 * j + 1], a);
-                a = fmaf(bf16_lo(v[j].y), xr[4 * j + 2], a);
-                a = fmaf(bf16_hi(v[j].y), xr[4 * j + 3], a);
-            }
+        const unsigned stage = g % NSTAGE, ph = (g / NSTAGE) & 1u;
+        mbar_wait(&sm.empty[stage], ph ^ 1u, err, 0x80000000u | g);
+        if (g >= inflight) {
+            // throttle: a full ring of outstanding requests (25 MB chip-wide) adds microseconds of
+            // queueing to every grid barrier and prologue load; landed tiles cost nothing
+            const unsigned f = g - inflight;
+            mbar_wait(&sm.full[f % NSTAGE], (f / NSTAGE) & 1u, err, 0x40000000u | g);
         }
-        acc[r] = a;
+        mbar_expect_tx(&sm.full[stage], bytes);
+        bulk_g2s(sm.ring[stage], W + (size_t)r * K, bytes, &sm.full[stage], policy);
+        sm.issued = g + 1;
     }
 }
 
-// One GEMV phase for the consumers.  EPI(row, v0, v1, npair_or_row) is called by
-// one thread per output row (PAIR = false) or per adjacent row pair (PAIR = true).
-template <int K, bool PAIR, typename Epi>
-__device__ __forceinline__ void consume(Smem &sm, Pipe &cp, int &pbuf, int R, int unit, int c, int G,
-                                        const float (&xr)[K / 256], unsigned *err, Epi epi) {
+// ---- L2 prefetcher ---------------------------------------------------------------------
+// The smem ring holds 3.8 us of HBM time; attention plus two grid barriers stall the
+// consumers for longer.  A second elected thread walks the same tile list `ahead`
+// tiles in front of the producer and pulls those tiles into L2 (cp.async.bulk.prefetch),
+// so HBM keeps streaming through the stall and the ring later refills at L2 speed.
+template <int K>
+__device__ __forceinline__ void prefetch_l2(Smem &sm, unsigned &g, const uint16_t *W, int R, int unit, int c, int G,
+                                            unsigned ahead) {
     constexpr int TR = TileRows<K>::v;
-    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     int r0, r1;
     cta_rows(R, unit, c, G, r0, r1);
-    for (int r = r0; r < r1; r += TR) {
-        const int n = min(TR, r1 - r);
-        mbar_wait(&sm.full[cp.stage], cp.phase, err);
-        float acc[TR];
-        tile_dot<K, TR>(sm.ring[cp.stage], n, xr, acc, w, lane);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[cp.stage]);   // this warp is done with the stage
-        cp.advance();
-        #pragma unroll
-        for (int i = 0; i < TR; i++) acc[i] = warp_sum(acc[i]);
-        if (lane == 0) {
-            #pragma unroll
-            for (int i = 0; i < TR; i++) sm.part[pbuf][i][w] = acc[i];
-        }
-        consumer_sync();
-        if (PAIR) {
-            if (tid < (n >> 1)) {
-                float v0 = 0.f, v1 = 0.f;
-                #pragma unroll
-                for (int k = 0; k < CW; k++) { v0 += sm.part[pbuf][2 * tid][k]; v1 += sm.part[pbuf][2 * tid + 1][k]; }
-                epi(r + 2 * tid, v0, v1);
-            }
-        } else {
-            if (tid < n) {
-                float v0 = 0.f;
-                #pragma unroll
-                for (int k = 0; k < CW; k++) v0 += sm.part[pbuf][tid][k];
-                epi(r + tid, v0, 0.f);
-            }
-        }
-        pbuf ^= 1;
+    for (int r = r0; r < r1; r += TR, g++) {
+        unsigned is = sm.issued;
+        while (g >= is + NSTAGE + ahead) { __nanosleep(200); is = sm.issued; }
+        if (g < is + NSTAGE) continue;           // the producer is (nearly) there already
+        const unsigned bytes = (unsigned)min(TR, r1 - r) * K * 2u;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(W + (size_t)r * K), "r"(bytes) : "memory");
     }
+}
+
+// ---- consumer: one warp multiplies one whole tile ------------------------------------------
+template <int K, int TR, bool FULL>
+__device__ __forceinline__ void warp_tile(const unsigned char *tile, int n, const XVec &x, float (&acc)[TR], int lane) {
+    constexpr int NCH = K / 256;                                  // 16-byte chunks per lane per row
+    constexpr int NACC = TR >= 4 ? 1 : (TR >= 2 ? 2 : 4);         // accumulators per row (ILP)
+    static_assert(NCH % 4 == 0, "");
+    float a[TR][NACC];
+    #pragma unroll
+    for (int r = 0; r < TR; r++)
+        #pragma unroll
+        for (int k = 0; k < NACC; k++) a[r][k] = 0.f;
+    const uint4 *wp = reinterpret_cast<const uint4 *>(tile) + lane;
+    #pragma unroll 4
+    for (int ch = 0; ch < NCH; ch++) {
+        const float4 A = x.xa[ch * 32 + lane], B = x.xb[ch * 32 + lane];
+        #pragma unroll
+        for (int r = 0; r < TR; r++) {
+            if (FULL || r < n) {
+                const uint4 wv = wp[r * (K / 8) + ch * 32];
+                a[r][ch % NACC] = dot8(wv, A, B, a[r][ch % NACC]);
+            }
+        }
+    }
+    #pragma unroll
+    for (int r = 0; r < TR; r++) {
+        float t = a[r][0];
+        #pragma unroll
+        for (int k = 1; k < NACC; k++) t += a[r][k];
+        acc[r] = t;
+    }
+}
+
+// One GEMV phase for the consumers.  Ring stage s is owned by warp s (tile g goes to
+// warp g % NSTAGE): a warp then meets the phases of "its" mbarriers strictly in
+// order, which mbarrier parity waits require (a waiter may be at most one phase
+// ahead).  Warp NSTAGE..CW-1 only help with prologues and attention.  epi(row, v0, v1) is called by one lane per output row (PAIR = false)
+// or per adjacent row pair (PAIR = true).  g0 = global index of the phase's first tile.
+template <int K, bool PAIR, typename Epi>
+__device__ __forceinline__ void consume(Smem &sm, unsigned &g0, int R, int unit, int c, int G, unsigned *err,
+                                        long long &t_wait, Epi epi) {
+    constexpr int TR = TileRows<K>::v;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int r0, r1;
+    cta_rows(R, unit, c, G, r0, r1);
+    const int n_tiles = (r1 - r0 + TR - 1) / TR;
+    const int t0 = (int)(((unsigned)w + NSTAGE - g0 % NSTAGE) % NSTAGE);
+    for (int t = (w < NSTAGE) ? t0 : n_tiles; t < n_tiles; t += NSTAGE) {
+        const int r = r0 + t * TR;
+        const int n = min(TR, r1 - r);
+        const unsigned g = g0 + (unsigned)t;
+        const unsigned stage = (unsigned)w, ph = (g / NSTAGE) & 1u;
+        {
+            const long long tw = clock64();
+            mbar_wait(&sm.full[stage], ph, err, g);
+            t_wait += clock64() - tw;
+        }
+        float acc[TR];
+        if (n == TR) warp_tile<K, TR, true>(sm.ring[stage], n, sm.u.x, acc, lane);
+        else warp_tile<K, TR, false>(sm.ring[stage], n, sm.u.x, acc, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);      // stage may be refilled
+        #pragma unroll
+        for (int i = 0; i < TR; i++) acc[i] = warp_sum(acc[i]);   // every lane holds every row sum
+        if (PAIR) {
+            #pragma unroll
+            for (int i = 0; i < TR / 2; i++)
+                if (lane == i && 2 * i < n) epi(r + 2 * i, acc[2 * i], acc[2 * i + 1]);
+        } else {
+            #pragma unroll
+            for (int i = 0; i < TR; i++)
+                if (lane == i && i < n) epi(r + i, acc[i], 0.f);
+        }
+    }
+    g0 += (unsigned)n_tiles;
 }
 
 __device__ __forceinline__ float block_sum(Smem &sm, float v) {
@@ -255,89 +326,112 @@ __device__ __forceinline__ void argmax_merge(float &bv, int &bi, float v, int i)
 // ---- attention for one (kv head, key range) ------------------------------------------------
 // vox_causal_attention with seq_q = 1 (voxtral_kernels.c:541-611): the query at
 // logical position pos sees the last n_keys positions of the ring.
+//
+// Latency matters more than throughput here (a 60 s clip never exceeds ~800 keys),
+// so the unit of work is a GROUP of 8 keys handled by one warp with all 16 K and V
+// row loads (coalesced 512 B each) in flight at once - one memory round trip per
+// group.  Lanes own 4 of the 128 dims; the 8 keys x 4 GQA heads = 32 partial dot
+// products per lane are summed with a 31-shuffle transposed reduction that leaves
+// score (key i, head h) in lane 4i + h.  Groups are dealt to (split, warp) units;
+// units are merged per CTA in smem, and the splits are merged in the wo prologue.
+__device__ __forceinline__ int attn_splits(int n_keys, int G) {
+    const int ng = (n_keys + 7) >> 3;
+    return min(min(G >> 3, MAX_SPLITS), (ng + CW - 1) / CW);
+}
+
 __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const float *kc, const float *vc,
                                                 int pos, int n_keys, int c, int G) {
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const int kvh = c & 7, split = c >> 3;
-    const int s_max = min(G >> 3, MAX_SPLITS);
-    const int s_eff = min(s_max, (n_keys + 255) >> 8);
+    const int s_eff = attn_splits(n_keys, G);
     if (split >= s_eff) return;
     const int first = pos - n_keys + 1;
-    const int nb = (n_keys + 31) >> 5;
-    const int b0 = (int)(((long long)split * nb) / s_eff), b1 = (int)(((long long)(split + 1) * nb) / s_eff);
-    {
-        const float4 *qg = reinterpret_cast<const float4 *>(P.q + kvh * 4 * DEC_HD);
-        if (tid < 4 * DEC_HD / 4) reinterpret_cast<float4 *>(&sm.qs[0][0])[tid] = __ldcg(qg + tid);
-    }
-    consumer_sync();
+    const int ng = (n_keys + 7) >> 3;
+    const int U = s_eff * CW, u = split * CW + w;
+    const int g0 = (int)(((long long)u * ng) / U), g1 = (int)(((long long)(u + 1) * ng) / U);
     const float scale = 0.08838834764831845f;  // 1/sqrt(128)
-    float m[4], l[4];
+    float4 q[4];
+    #pragma unroll
+    for (int h = 0; h < 4; h++) q[h] = __ldcg(reinterpret_cast<const float4 *>(P.q + (kvh * 4 + h) * DEC_HD) + lane);
+    float m = -INFINITY, l = 0.f;              // running max / sum of head (lane & 3)
     float4 acc[4];
     #pragma unroll
-    for (int h = 0; h < 4; h++) { m[h] = -INFINITY; l[h] = 0.f; acc[h] = make_float4(0.f, 0.f, 0.f, 0.f); }
-    for (int b = b0 + w; b < b1; b += CW) {
-        const int j = b * 32 + lane;           // key index within the window
-        const bool valid = j < n_keys;
-        float s[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-        if (valid) {
-            const int slot = (first + j) & (DEC_WINDOW - 1);
-            const float4 *kr = reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + kvh * DEC_HD);
-            float d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
-            #pragma unroll 8
-            for (int i = 0; i < DEC_HD / 4; i++) {
-                const float4 kv = kr[i];
-                const float4 q0 = reinterpret_cast<const float4 *>(sm.qs[0])[i];
-                const float4 q1 = reinterpret_cast<const float4 *>(sm.qs[1])[i];
-                const float4 q2 = reinterpret_cast<const float4 *>(sm.qs[2])[i];
-                const float4 q3 = reinterpret_cast<const float4 *>(sm.qs[3])[i];
-                d0 += kv.x * q0.x + kv.y * q0.y + kv.z * q0.z + kv.w * q0.w;
-                d1 += kv.x * q1.x + kv.y * q1.y + kv.z * q1.z + kv.w * q1.w;
-                d2 += kv.x * q2.x + kv.y * q2.y + kv.z * q2.z + kv.w * q2.w;
-                d3 += kv.x * q3.x + kv.y * q3.y + kv.z * q3.z + kv.w * q3.w;
-            }
-            s[0] = d0 * scale; s[1] = d1 * scale; s[2] = d2 * scale; s[3] = d3 * scale;
+    for (int h = 0; h < 4; h++) acc[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const size_t hoff = (size_t)kvh * DEC_HD + 4 * lane;
+    for (int g = g0; g < g1; g++) {
+        const int j0 = g * 8;
+        const int nv = min(8, n_keys - j0);
+        float4 kf[8], vf[8];
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamp: always a valid row
+            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
+            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
         }
-        float p[4];
+        float v[32];
+        #pragma unroll
+        for (int i = 0; i < 8; i++)
+            #pragma unroll
+            for (int h = 0; h < 4; h++)
+                v[i * 4 + h] = kf[i].x * q[h].x + kf[i].y * q[h].y + kf[i].z * q[h].z + kf[i].w * q[h].w;
+        // transposed reduction: after the step with offset o, lanes with bit o set hold the upper half
+        #pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const bool up = (lane & o) != 0;
+            #pragma unroll
+            for (int k = 0; k < o; k++) {
+                const float keep = up ? v[k + o] : v[k];
+                const float send = up ? v[k] : v[k + o];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
+        }
+        const bool valid = (lane >> 2) < nv;
+        const float sc = valid ? v[0] * scale : -INFINITY;
+        float mx = sc;
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        const float mn = fmaxf(m, mx);                       // finite: every group has >= 1 valid key
+        const float corr = (m == -INFINITY) ? 0.f : expf(m - mn);
+        const float p = valid ? expf(sc - mn) : 0.f;
+        float ps = p;
+        ps += __shfl_xor_sync(0xffffffffu, ps, 4);
+        ps += __shfl_xor_sync(0xffffffffu, ps, 8);
+        ps += __shfl_xor_sync(0xffffffffu, ps, 16);
+        l = l * corr + ps;
+        m = mn;
         #pragma unroll
         for (int h = 0; h < 4; h++) {
-            const float mn = fmaxf(m[h], warp_max(s[h]));      // block has >= 1 valid key
-            const float corr = (m[h] == -INFINITY) ? 0.f : expf(m[h] - mn);
-            p[h] = valid ? expf(s[h] - mn) : 0.f;
-            l[h] = l[h] * corr + warp_sum(p[h]);
-            acc[h].x *= corr; acc[h].y *= corr; acc[h].z *= corr; acc[h].w *= corr;
-            m[h] = mn;
+            const float ch = __shfl_sync(0xffffffffu, corr, h);
+            acc[h].x *= ch; acc[h].y *= ch; acc[h].z *= ch; acc[h].w *= ch;
         }
-        const int kn = min(32, n_keys - b * 32);
-        for (int i = 0; i < kn; i++) {
-            const int slot = (first + b * 32 + i) & (DEC_WINDOW - 1);
-            const float4 v = reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + kvh * DEC_HD)[lane];
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
             #pragma unroll
             for (int h = 0; h < 4; h++) {
-                const float ph = __shfl_sync(0xffffffffu, p[h], i);
-                acc[h].x = fmaf(ph, v.x, acc[h].x); acc[h].y = fmaf(ph, v.y, acc[h].y);
-                acc[h].z = fmaf(ph, v.z, acc[h].z); acc[h].w = fmaf(ph, v.w, acc[h].w);
+                const float ph = __shfl_sync(0xffffffffu, p, i * 4 + h);    // 0 for padded keys
+                acc[h].x = fmaf(ph, vf[i].x, acc[h].x); acc[h].y = fmaf(ph, vf[i].y, acc[h].y);
+                acc[h].z = fmaf(ph, vf[i].z, acc[h].z); acc[h].w = fmaf(ph, vf[i].w, acc[h].w);
             }
         }
     }
     #pragma unroll
-    for (int h = 0; h < 4; h++) {
-        reinterpret_cast<float4 *>(&sm.wsm[w][h][0])[lane] = acc[h];
-        if (lane == 0) { sm.wsm[w][h][DEC_HD] = m[h]; sm.wsm[w][h][DEC_HD + 1] = l[h]; }
-    }
+    for (int h = 0; h < 4; h++) reinterpret_cast<float4 *>(&sm.u.at.wsm[w][h][0])[lane] = acc[h];
+    if (lane < 4) { sm.u.at.wsm[w][lane][DEC_HD] = m; sm.u.at.wsm[w][lane][DEC_HD + 1] = l; }
     consumer_sync();
     {   // merge the 8 warps: thread -> (head, two dims)
         const int h = tid >> 6, d = (tid & 63) * 2;
         float M = -INFINITY;
         #pragma unroll
-        for (int k = 0; k < CW; k++) M = fmaxf(M, sm.wsm[k][h][DEC_HD]);
+        for (int k = 0; k < CW; k++) M = fmaxf(M, sm.u.at.wsm[k][h][DEC_HD]);
         float n0 = 0.f, n1 = 0.f, den = 0.f;
         #pragma unroll
         for (int k = 0; k < CW; k++) {
-            const float mk_ = sm.wsm[k][h][DEC_HD];
+            const float mk_ = sm.u.at.wsm[k][h][DEC_HD];
             const float e = (mk_ == -INFINITY) ? 0.f : expf(mk_ - M);
-            n0 = fmaf(e, sm.wsm[k][h][d], n0);
-            n1 = fmaf(e, sm.wsm[k][h][d + 1], n1);
-            den = fmaf(e, sm.wsm[k][h][DEC_HD + 1], den);
+            n0 = fmaf(e, sm.u.at.wsm[k][h][d], n0);
+            n1 = fmaf(e, sm.u.at.wsm[k][h][d + 1], n1);
+            den = fmaf(e, sm.u.at.wsm[k][h][DEC_HD + 1], den);
         }
         float *o = P.attn_part + ((size_t)split * DEC_HEADS + kvh * 4 + h) * PART_LD;
         *reinterpret_cast<float2 *>(o + d) = make_float2(n0, n1);
@@ -346,6 +440,54 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
 }
 
 // ---- the kernel ----------------------------------------------------------------------------
+// load this lane's K-slice of a length-K fp32 vector (coherent at L2) and its sum of squares
+template <int K>
+__device__ __forceinline__ float load_slice(const float *v, int col0, float (&xr)[K / 256]) {
+    float ss = 0.f;
+    #pragma unroll
+    for (int j = 0; j < K / 1024; j++) {
+        const float4 t = __ldcg(reinterpret_cast<const float4 *>(v + j * 1024 + col0));
+        xr[4 * j] = t.x; xr[4 * j + 1] = t.y; xr[4 * j + 2] = t.z; xr[4 * j + 3] = t.w;
+        ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+    }
+    return ss;
+}
+
+// publish this thread's slice (columns (j*256 + tid)*4 .. +3) into the split smem layout
+template <int K>
+__device__ __forceinline__ void store_slice(Smem &sm, const float (&xr)[K / 256]) {
+    #pragma unroll
+    for (int j = 0; j < K / 1024; j++) {
+        const int g = j * 256 + (int)threadIdx.x;          // 4-column group
+        const float4 v = make_float4(xr[4 * j], xr[4 * j + 1], xr[4 * j + 2], xr[4 * j + 3]);
+        if (g & 1) sm.u.x.xb[g >> 1] = v; else sm.u.x.xa[g >> 1] = v;
+    }
+    consumer_sync();
+}
+
+// RMSNorm of the slice (voxtral_kernels.c:475-492), optional (1 + ada) (voxtral_decoder.c:742-745).
+// The norm weights are fetched before the block reduction so their latency overlaps it.
+__device__ __forceinline__ void norm_slice(Smem &sm, float (&xr)[DEC_DIM / 256], float ss, const float *nw,
+                                           const float *ada, int col0) {
+    float4 wv[DEC_DIM / 1024], av[DEC_DIM / 1024];
+    #pragma unroll
+    for (int j = 0; j < DEC_DIM / 1024; j++) {
+        wv[j] = *reinterpret_cast<const float4 *>(nw + j * 1024 + col0);
+        if (ada) av[j] = *reinterpret_cast<const float4 *>(ada + j * 1024 + col0);
+    }
+    const float tot = block_sum(sm, ss);
+    const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
+    #pragma unroll
+    for (int j = 0; j < DEC_DIM / 1024; j++) {
+        xr[4 * j] = xr[4 * j] * rinv * wv[j].x; xr[4 * j + 1] = xr[4 * j + 1] * rinv * wv[j].y;
+        xr[4 * j + 2] = xr[4 * j + 2] * rinv * wv[j].z; xr[4 * j + 3] = xr[4 * j + 3] * rinv * wv[j].w;
+        if (ada) {
+            xr[4 * j] *= (1.0f + av[j].x); xr[4 * j + 1] *= (1.0f + av[j].y);
+            xr[4 * j + 2] *= (1.0f + av[j].z); xr[4 * j + 3] *= (1.0f + av[j].w);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
@@ -353,7 +495,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     const int c = blockIdx.x, G = gridDim.x;
 
     if (tid == 0) {
-        for (int i = 0; i < NSTAGE; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], CW); }
+        sm.issued = 0;
+        for (int i = 0; i < NSTAGE; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }  // one warp consumes a tile
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -362,27 +505,52 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
 
     if (tid >= CT) {
         // =========================== PRODUCER ===========================
+        if (tid == CT + 32 && P.l2_ahead > 0) {
+            unsigned fg = 0;
+            for (int step = 0; step < P.n_steps; step++) {
+                for (int l = 0; l < n_dec; l++) {
+                    const DecLayerDev L = P.layers[l];
+                    prefetch_l2<DEC_DIM>(sm, fg, L.wqkv, DEC_QKV, 2, c, G, (unsigned)P.l2_ahead);
+                    prefetch_l2<DEC_QDIM>(sm, fg, L.wo, DEC_DIM, 1, c, G, (unsigned)P.l2_ahead);
+                    prefetch_l2<DEC_DIM>(sm, fg, L.w13, 2 * DEC_HIDDEN, 2, c, G, (unsigned)P.l2_ahead);
+                    prefetch_l2<DEC_HIDDEN>(sm, fg, L.w2, DEC_DIM, 1, c, G, (unsigned)P.l2_ahead);
+                }
+                prefetch_l2<DEC_DIM>(sm, fg, P.tok_emb, VOCAB, 1, c, G, (unsigned)P.l2_ahead);
+            }
+            return;
+        }
         if (tid != CT) return;
         const unsigned long long policy = policy_evict_first();
-        Pipe pp{0, 0u};
+        unsigned pg = 0;
         for (int step = 0; step < P.n_steps; step++) {
             for (int l = 0; l < n_dec; l++) {
                 const DecLayerDev L = P.layers[l];
-                produce<DEC_DIM>(sm, pp, L.wqkv, DEC_QKV, 2, c, G, policy, P.err);
-                produce<DEC_QDIM>(sm, pp, L.wo, DEC_DIM, 1, c, G, policy, P.err);
-                produce<DEC_DIM>(sm, pp, L.w13, 2 * DEC_HIDDEN, 2, c, G, policy, P.err);
-                produce<DEC_HIDDEN>(sm, pp, L.w2, DEC_DIM, 1, c, G, policy, P.err);
+                produce<DEC_DIM>(sm, pg, L.wqkv, DEC_QKV, 2, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_QDIM>(sm, pg, L.wo, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_DIM>(sm, pg, L.w13, 2 * DEC_HIDDEN, 2, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_HIDDEN>(sm, pg, L.w2, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
             }
-            produce<DEC_DIM>(sm, pp, P.tok_emb, VOCAB, 1, c, G, policy, P.err);
+            produce<DEC_DIM>(sm, pg, P.tok_emb, VOCAB, 1, c, G, policy, (unsigned)P.inflight, P.err);
         }
         return;
     }
 
     // =============================== CONSUMERS ===============================
     const int w = tid >> 5, lane = tid & 31;
-    Pipe cp{0, 0u};
-    int pbuf = 0;
+    unsigned gt = 0;                              // global index of the next phase's first tile
     unsigned bar_target = P.bar_base;
+    long long t_wait = 0, t_grid = 0, t_attn = 0, t_pro = 0, t_own = 0, t_atom = 0;
+    const long long t_start = clock64();
+#define MK_GRID_SYNC()                                              \
+    do {                                                            \
+        const long long tg_ = clock64();                            \
+        const bool rec_ = P.prof && tid == 0 && step == P.n_steps - 1 && bar_k < 12;   \
+        if (rec_) P.prof[(size_t)c * 32 + 8 + 2 * bar_k] = globaltimer_ns();          \
+        grid_sync(P.bar, bar_target += G, P.err, P.prof ? &t_own : nullptr, P.prof ? &t_atom : nullptr); \
+        if (rec_) P.prof[(size_t)c * 32 + 9 + 2 * bar_k] = globaltimer_ns();          \
+        bar_k++;                                                    \
+        t_grid += clock64() - tg_;                                  \
+    } while (0)
     // step scalars: every CTA tracks them in registers
     int pos = P.params->pos, n_valid = P.params->n_valid, prev_token = P.params->prev_token;
     int adapter_index = P.params->adapter_index, step_count = P.params->step_count;
@@ -390,29 +558,35 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
     // column base of this lane for unit j: (j*256 + w*32 + lane) * 4
     const int col0 = (w * 32 + lane) * 4;
+    // rows of the [3072]-row matrices (wo, w2) this CTA owns: residual values are staged in smem
+    int rr0, rr1;
+    cta_rows(DEC_DIM, 1, c, G, rr0, rr1);
 
     for (int step = 0; step < P.n_steps; step++) {
         const int n_keys = min(n_valid, DEC_WINDOW - 1) + 1;
         const int slot = pos & (DEC_WINDOW - 1);
-        const int s_eff = min(min(G >> 3, MAX_SPLITS), (n_keys + 255) >> 8);
+        const int s_eff = attn_splits(n_keys, G);
         // RoPE table of this position (voxtral_kernels.c:617-629)
         if (tid < DEC_HD / 2) {
             const float angle = (float)pos * P.inv_freq[tid];
             sm.rope[2 * tid] = cosf(angle);
             sm.rope[2 * tid + 1] = sinf(angle);
         }
+        int bar_k = 0;
         for (int l = 0; l < n_dec; l++) {
+            if (l == 10) bar_k = 0; else if (l < 10) bar_k = 100;
             const DecLayerDev L = P.layers[l];
             float *kc = P.kv_k + l * kv_layer, *vc = P.kv_v + l * kv_layer;
             // ---------------- phase 1: rmsnorm -> qkv -> rope -> q / KV ring ----------------
             {
+                const long long tp = clock64();
                 float xr[DEC_DIM / 256];
                 float ss = 0.f;
-                #pragma unroll
-                for (int j = 0; j < DEC_DIM / 1024; j++) {
-                    const int col = j * 1024 + col0;
-                    float4 v;
-                    if (l == 0) {
+                if (l == 0) {
+                    #pragma unroll
+                    for (int j = 0; j < DEC_DIM / 1024; j++) {
+                        const int col = j * 1024 + col0;
+                        float4 v;
                         // x = adapter[idx] + bf16->f32(tok_emb[prev])  (voxtral.c:1106-1113)
                         if (use_host_embed) v = __ldcg(reinterpret_cast<const float4 *>(P.embed_in + col));
                         else {
@@ -421,21 +595,16 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                             v.x += bf16_lo(e.x); v.y += bf16_hi(e.x); v.z += bf16_lo(e.y); v.w += bf16_hi(e.y);
                         }
                         if (c == 0) *reinterpret_cast<float4 *>(P.x + col) = v;
-                    } else {
-                        v = __ldcg(reinterpret_cast<const float4 *>(P.x + col));
+                        xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
+                        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
                     }
-                    xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
-                    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+                } else {
+                    ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 }
-                const float tot = block_sum(sm, ss);
-                const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
-                #pragma unroll
-                for (int j = 0; j < DEC_DIM / 1024; j++) {
-                    const float4 nw = *reinterpret_cast<const float4 *>(L.attn_norm + j * 1024 + col0);
-                    xr[4 * j] = xr[4 * j] * rinv * nw.x; xr[4 * j + 1] = xr[4 * j + 1] * rinv * nw.y;
-                    xr[4 * j + 2] = xr[4 * j + 2] * rinv * nw.z; xr[4 * j + 3] = xr[4 * j + 3] * rinv * nw.w;
-                }
-                consume<DEC_DIM, true>(sm, cp, pbuf, DEC_QKV, 2, c, G, xr, P.err,
+                norm_slice(sm, xr, ss, L.attn_norm, nullptr, col0);
+                store_slice<DEC_DIM>(sm, xr);
+                t_pro += clock64() - tp;
+                consume<DEC_DIM, true>(sm, gt, DEC_QKV, 2, c, G, P.err, t_wait,
                     [&](int row, float v0, float v1) {
                         if (row < DEC_QDIM + DEC_KVDIM) {
                             const int d = (row & (DEC_HD - 1)) >> 1;
@@ -450,109 +619,121 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                         *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
                     });
             }
-            grid_sync(P.bar, bar_target += G, P.err);
+            MK_GRID_SYNC();
             // ---------------- phase 2: attention partials ----------------
-            attention_phase(sm, P, kc, vc, pos, n_keys, c, G);
-            grid_sync(P.bar, bar_target += G, P.err);
+            {
+                const long long ta = clock64();
+                attention_phase(sm, P, kc, vc, pos, n_keys, c, G);
+                t_attn += clock64() - ta;
+            }
+            MK_GRID_SYNC();
             // ---------------- phase 3: merge partials -> wo -> residual ----------------
             {
+                const long long tp = clock64();
+                if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_QDIM / 256];
+                // online merge of the split partials, 4 splits x 4 heads of loads in flight per round trip
+                float Mj[4], dj[4];
+                float4 nj[4];
                 #pragma unroll
-                for (int j = 0; j < DEC_QDIM / 1024; j++) {
-                    const int head = j * 8 + w;          // column j*1024 + w*128 + 4*lane
-                    float M = -INFINITY;
-                    for (int s = 0; s < s_eff; s++)
-                        M = fmaxf(M, __ldcg(P.attn_part + ((size_t)s * DEC_HEADS + head) * PART_LD + DEC_HD));
-                    float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
-                    float den = 0.f;
-                    for (int s = 0; s < s_eff; s++) {
-                        const float *o = P.attn_part + ((size_t)s * DEC_HEADS + head) * PART_LD;
-                        const float ms = __ldcg(o + DEC_HD);
-                        const float e = (ms == -INFINITY) ? 0.f : expf(ms - M);
-                        const float4 a = __ldcg(reinterpret_cast<const float4 *>(o) + lane);
-                        num.x = fmaf(e, a.x, num.x); num.y = fmaf(e, a.y, num.y);
-                        num.z = fmaf(e, a.z, num.z); num.w = fmaf(e, a.w, num.w);
-                        den = fmaf(e, __ldcg(o + DEC_HD + 1), den);
+                for (int j = 0; j < 4; j++) { Mj[j] = -INFINITY; dj[j] = 0.f; nj[j] = make_float4(0.f, 0.f, 0.f, 0.f); }
+                for (int sb = 0; sb < s_eff; sb += 4) {
+                    float2 ml[4][4];
+                    float4 av[4][4];
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        #pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const int sidx = min(sb + k, s_eff - 1);     // clamped duplicates are masked below
+                            const float *o = P.attn_part + ((size_t)sidx * DEC_HEADS + (j * 8 + w)) * PART_LD;
+                            ml[j][k] = __ldcg(reinterpret_cast<const float2 *>(o + DEC_HD));
+                            av[j][k] = __ldcg(reinterpret_cast<const float4 *>(o) + lane);
+                        }
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        float M = Mj[j];
+                        #pragma unroll
+                        for (int k = 0; k < 4; k++) if (sb + k < s_eff) M = fmaxf(M, ml[j][k].x);
+                        const float c0 = (Mj[j] == -INFINITY) ? 0.f : expf(Mj[j] - M);
+                        nj[j].x *= c0; nj[j].y *= c0; nj[j].z *= c0; nj[j].w *= c0; dj[j] *= c0;
+                        #pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            if (sb + k < s_eff) {
+                                const float e = (ml[j][k].x == -INFINITY) ? 0.f : expf(ml[j][k].x - M);
+                                nj[j].x = fmaf(e, av[j][k].x, nj[j].x); nj[j].y = fmaf(e, av[j][k].y, nj[j].y);
+                                nj[j].z = fmaf(e, av[j][k].z, nj[j].z); nj[j].w = fmaf(e, av[j][k].w, nj[j].w);
+                                dj[j] = fmaf(e, ml[j][k].y, dj[j]);
+                            }
+                        }
+                        Mj[j] = M;
                     }
-                    const float inv = den > 0.f ? 1.0f / den : 0.f;
-                    xr[4 * j] = num.x * inv; xr[4 * j + 1] = num.y * inv;
-                    xr[4 * j + 2] = num.z * inv; xr[4 * j + 3] = num.w * inv;
                 }
-                consume<DEC_QDIM, false>(sm, cp, pbuf, DEC_DIM, 1, c, G, xr, P.err,
-                    [&](int row, float v0, float) { P.x[row] = __ldcg(P.x + row) + v0; });
+                #pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float inv = dj[j] > 0.f ? 1.0f / dj[j] : 0.f;
+                    xr[4 * j] = nj[j].x * inv; xr[4 * j + 1] = nj[j].y * inv;
+                    xr[4 * j + 2] = nj[j].z * inv; xr[4 * j + 3] = nj[j].w * inv;
+                }
+                store_slice<DEC_QDIM>(sm, xr);           // (its barrier also publishes sm.resid)
+                t_pro += clock64() - tp;
+                consume<DEC_QDIM, false>(sm, gt, DEC_DIM, 1, c, G, P.err, t_wait,
+                    [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
             }
-            grid_sync(P.bar, bar_target += G, P.err);
+            MK_GRID_SYNC();
             // ---------------- phase 4: rmsnorm * (1 + ada) -> w1|w3 -> SwiGLU ----------------
             {
+                const long long tp = clock64();
                 float xr[DEC_DIM / 256];
-                float ss = 0.f;
-                #pragma unroll
-                for (int j = 0; j < DEC_DIM / 1024; j++) {
-                    const float4 v = __ldcg(reinterpret_cast<const float4 *>(P.x + j * 1024 + col0));
-                    xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
-                    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-                }
-                const float tot = block_sum(sm, ss);
-                const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
-                const float *ada = P.ada_scale + (size_t)l * DEC_DIM;
-                #pragma unroll
-                for (int j = 0; j < DEC_DIM / 1024; j++) {
-                    const float4 nw = *reinterpret_cast<const float4 *>(L.ffn_norm + j * 1024 + col0);
-                    const float4 ad = *reinterpret_cast<const float4 *>(ada + j * 1024 + col0);
-                    xr[4 * j] = xr[4 * j] * rinv * nw.x * (1.0f + ad.x);
-                    xr[4 * j + 1] = xr[4 * j + 1] * rinv * nw.y * (1.0f + ad.y);
-                    xr[4 * j + 2] = xr[4 * j + 2] * rinv * nw.z * (1.0f + ad.z);
-                    xr[4 * j + 3] = xr[4 * j + 3] * rinv * nw.w * (1.0f + ad.w);
-                }
-                consume<DEC_DIM, true>(sm, cp, pbuf, 2 * DEC_HIDDEN, 2, c, G, xr, P.err,
+                const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
+                norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
+                store_slice<DEC_DIM>(sm, xr);
+                t_pro += clock64() - tp;
+                consume<DEC_DIM, true>(sm, gt, 2 * DEC_HIDDEN, 2, c, G, P.err, t_wait,
                     [&](int row, float v0, float v1) { P.h[row >> 1] = silu(v0) * v1; });
             }
-            grid_sync(P.bar, bar_target += G, P.err);
+            MK_GRID_SYNC();
             // ---------------- phase 5: w2 -> residual ----------------
             {
+                const long long tp = clock64();
+                if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_HIDDEN / 256];
-                #pragma unroll
-                for (int j = 0; j < DEC_HIDDEN / 1024; j++) {
-                    const float4 v = __ldcg(reinterpret_cast<const float4 *>(P.h + j * 1024 + col0));
-                    xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
-                }
-                consume<DEC_HIDDEN, false>(sm, cp, pbuf, DEC_DIM, 1, c, G, xr, P.err,
-                    [&](int row, float v0, float) { P.x[row] = __ldcg(P.x + row) + v0; });
+                (void)load_slice<DEC_HIDDEN>(P.h, col0, xr);
+                store_slice<DEC_HIDDEN>(sm, xr);
+                t_pro += clock64() - tp;
+                consume<DEC_HIDDEN, false>(sm, gt, DEC_DIM, 1, c, G, P.err, t_wait,
+                    [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
             }
-            grid_sync(P.bar, bar_target += G, P.err);
+            MK_GRID_SYNC();
         }
         // ---------------- final norm -> logits -> argmax (voxtral_decoder.c:765-779) ----------------
         {
+            const long long tp = clock64();
             float xr[DEC_DIM / 256];
-            float ss = 0.f;
-            #pragma unroll
-            for (int j = 0; j < DEC_DIM / 1024; j++) {
-                const float4 v = __ldcg(reinterpret_cast<const float4 *>(P.x + j * 1024 + col0));
-                xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
-                ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-            }
-            const float tot = block_sum(sm, ss);
-            const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
-            #pragma unroll
-            for (int j = 0; j < DEC_DIM / 1024; j++) {
-                const float4 nw = *reinterpret_cast<const float4 *>(P.dec_norm + j * 1024 + col0);
-                xr[4 * j] = xr[4 * j] * rinv * nw.x; xr[4 * j + 1] = xr[4 * j + 1] * rinv * nw.y;
-                xr[4 * j + 2] = xr[4 * j + 2] * rinv * nw.z; xr[4 * j + 3] = xr[4 * j + 3] * rinv * nw.w;
-            }
+            const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
+            norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
+            store_slice<DEC_DIM>(sm, xr);
+            t_pro += clock64() - tp;
             float bv = -INFINITY;
             int bi = 0x7fffffff;
-            consume<DEC_DIM, false>(sm, cp, pbuf, VOCAB, 1, c, G, xr, P.err,
+            consume<DEC_DIM, false>(sm, gt, VOCAB, 1, c, G, P.err, t_wait,
                 [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); });
-            if (tid < MAXTR) { sm.bv[tid] = bv; sm.bi[tid] = bi; }
+            // epilogue lanes of every warp hold candidates: block-wide merge
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                argmax_merge(bv, bi, ov, oi);
+            }
+            if (lane == 0) { sm.bv[w] = bv; sm.bi[w] = bi; }
             consumer_sync();
             if (tid == 0) {
                 #pragma unroll
-                for (int k = 1; k < MAXTR; k++) argmax_merge(bv, bi, sm.bv[k], sm.bi[k]);
+                for (int k = 1; k < CW; k++) argmax_merge(bv, bi, sm.bv[k], sm.bi[k]);
                 P.blockmax[2 * c] = bv;
                 P.blockmax[2 * c + 1] = __int_as_float(bi);
             }
         }
-        grid_sync(P.bar, bar_target += G, P.err);
+        MK_GRID_SYNC();
         // every CTA derives the token; CTA 0 records it
         {
             float bv = -INFINITY;
@@ -565,8 +746,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
                 argmax_merge(bv, bi, ov, oi);
             }
-            consumer_sync();               // sm.bv / sm.bi readers above are done
-            if (lane == 0) { sm.bv[w] = bv; sm.bi[w] = bi; }
+            if (lane == 0) { sm.bv[w] = bv; sm.bi[w] = bi; }   // (the grid barrier separates this from the reads above)
             consumer_sync();
             if (tid == 0) {
                 for (int k = 1; k < CW; k++) argmax_merge(bv, bi, sm.bv[k], sm.bi[k]);
@@ -582,10 +762,17 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         n_valid = min(n_valid + 1, DEC_WINDOW);
         adapter_index += 1;
     }
+#undef MK_GRID_SYNC
     if (c == 0 && tid == 0) {
         DecStepParams *p = P.params;
         p->out_token = prev_token; p->prev_token = prev_token; p->step_count = step_count;
         p->pos = pos; p->n_valid = n_valid; p->adapter_index = adapter_index;
+    }
+    if (P.prof && tid == 0) {
+        unsigned long long *o = P.prof + (size_t)c * 32;
+        o[0] = (unsigned long long)(clock64() - t_start);
+        o[1] = (unsigned long long)t_wait; o[2] = (unsigned long long)t_grid;
+        o[3] = (unsigned long long)t_attn; o[4] = (unsigned long long)t_pro; o[5] = (unsigned long long)t_own; o[6] = (unsigned long long)t_atom;
     }
 }
 
@@ -595,6 +782,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
 struct MegaHost {
     DecLayerDev *d_layers;
     unsigned *d_bar, *d_err;
+    unsigned long long *d_prof;   // [grid][8] when VOX_CUDA_MEGA_PROF=1
+    int inflight, l2_ahead;
     unsigned bar_count;      // value of *d_bar after all launches enqueued so far
     int grid;
     int barriers_per_step;
@@ -616,8 +805,28 @@ int dec_mega_init(vox_cuda_state *s) {
     CUDA_TRY(cudaMemcpy(h->d_layers, s->m->dec, sizeof(DecLayerDev) * VOX_CUDA_DEC_LAYERS, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMalloc((void **)&h->d_bar, 8));
     CUDA_TRY(cudaMemset(h->d_bar, 0, 8));
-    h->d_err = h->d_bar + 1;
+    // watchdog record in mapped host memory: still readable after a device-side trap
+    CUDA_TRY(cudaHostAlloc((void **)&h->d_err, 16, cudaHostAllocMapped));
+    memset(h->d_err, 0, 16);
     h->bar_count = 0;
+    h->inflight = mk::NSTAGE;
+    h->l2_ahead = 0;
+    {
+        const char *env = getenv("VOX_CUDA_MEGA_L2AHEAD");
+        if (env && atoi(env) >= 0 && atoi(env) <= 256) h->l2_ahead = atoi(env);
+    }
+    {
+        const char *env = getenv("VOX_CUDA_MEGA_INFLIGHT");
+        if (env && atoi(env) >= 1 && atoi(env) <= mk::NSTAGE) h->inflight = atoi(env);
+    }
+    {
+        const char *env = getenv("VOX_CUDA_MEGA_PROF");
+        if (env && atoi(env)) {
+            CUDA_TRY(cudaMalloc((void **)&h->d_prof, (size_t)h->grid * 32 * sizeof(unsigned long long)));
+            CUDA_TRY(cudaMemset(h->d_prof, 0, (size_t)h->grid * 32 * sizeof(unsigned long long)));
+        }
+    }
+    if (h->grid > 8 * 64) { vox_set_error("dec_mega: grid too large"); return -1; }
     return 0;
 }
 
@@ -626,6 +835,8 @@ void dec_mega_free(vox_cuda_state *s) {
     if (!h) return;
     cudaFree(h->d_layers);
     cudaFree(h->d_bar);
+    if (h->d_err) cudaFreeHost(h->d_err);
+    if (h->d_prof) cudaFree(h->d_prof);
     free(h);
     s->mega = nullptr;
 }
@@ -643,7 +854,7 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.blockmax = s->d_blockmax;
     P.embed_in = s->d_embed_in; P.adapter = s->adapter_buf;
     P.params = s->d_params; P.tokens = s->d_tokens;
-    P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.err = h->d_err;
+    P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.err = h->d_err; P.prof = h->d_prof;
     void *args[] = {&P};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void *)mk::dec_mega_kernel, dim3(h->grid), dim3(mk::NT), args,
                                          sizeof(mk::Smem), s->stream));
@@ -653,3 +864,40 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
 }
 
 int dec_mega_attn_part_floats(void) { return mk::MAX_SPLITS * DEC_HEADS * mk::PART_LD; }
+
+// Debug: cycle counters of the last launch, averaged over CTAs:
+// out[0..4] = total, waiting for weight tiles, grid barriers, attention, prologues.
+extern "C" int vox_cuda_debug_mega_profile(vox_cuda_state_t *s, double *out) {
+    MegaHost *h = s ? (MegaHost *)s->mega : nullptr;
+    if (!h || !h->d_prof) return -1;
+    const int n = h->grid * 32;
+    unsigned long long *buf = (unsigned long long *)malloc((size_t)n * 8);
+    if (cudaMemcpy(buf, h->d_prof, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) { free(buf); return -1; }
+    for (int k = 0; k < 7; k++) {
+        double a = 0;
+        for (int c = 0; c < h->grid; c++) a += (double)buf[c * 32 + k];
+        out[k] = a / h->grid;
+    }
+    free(buf);
+    return 0;
+}
+
+// Watchdog record of the megakernel (code 1 = tile mbarrier wait timed out, 2 = grid barrier timed out).
+const unsigned *dec_mega_error_record(vox_cuda_state *s) {
+    MegaHost *h = s ? (MegaHost *)s->mega : nullptr;
+    return h ? h->d_err : nullptr;
+}
+
+// Debug: arrival / exit timestamps (ns) of barriers 0..11 counted from layer 10 of the last step; out[grid][24]
+extern "C" int vox_cuda_debug_mega_barriers(vox_cuda_state_t *s, unsigned long long *out, int *grid) {
+    MegaHost *h = s ? (MegaHost *)s->mega : nullptr;
+    if (!h || !h->d_prof) return -1;
+    const int n = h->grid * 32;
+    unsigned long long *buf = (unsigned long long *)malloc((size_t)n * 8);
+    if (cudaMemcpy(buf, h->d_prof, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) { free(buf); return -1; }
+    for (int c = 0; c < h->grid; c++)
+        for (int k = 0; k < 24; k++) out[c * 24 + k] = buf[c * 32 + 8 + k];
+    *grid = h->grid;
+    free(buf);
+    return 0;
+}
