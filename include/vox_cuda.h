@@ -188,6 +188,20 @@ int vox_cuda_mel_frames(const float *samples, int n_frames, float *mel_out);
 int vox_cuda_sgemm_bf16(vox_cuda_model_t *m, int M, int N, int K, const float *A,
                         const uint16_t *B_bf16, float *C);
 
+/* Tensor-core twin of the hook above (the encoder's throughput path): A is
+ * rounded to bf16 on the device, products accumulate in fp32 on the tcgen05
+ * tensor cores (TMEM).  Differs from vox_cuda_sgemm_bf16 by the bf16 rounding of
+ * A only (relative 2^-9 per element); the encoder tolerance of 2e-2 max-abs
+ * covers it.  flags: VOX_CUDA_TC_* ; bias [N] may be NULL; with
+ * VOX_CUDA_TC_RESIDUAL C is read and accumulated into; with VOX_CUDA_TC_SWIGLU
+ * columns are (gate, up) pairs and C is [M, N/2].  N % 128 == 0, K % 64 == 0. */
+#define VOX_CUDA_TC_BIAS      1
+#define VOX_CUDA_TC_GELU      2
+#define VOX_CUDA_TC_RESIDUAL  4
+#define VOX_CUDA_TC_SWIGLU    8
+int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const uint16_t *B_bf16,
+                          const float *bias, int flags, float *C);
+
 /* ---- measurement helpers (bench.py / profiles) ------------------------ */
 /* vox_cuda_decoder_run timed with CUDA events on the launch stream: returns
  * the average device time per step in milliseconds (<0 on error). */

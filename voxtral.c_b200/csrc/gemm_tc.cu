@@ -1,0 +1,378 @@
+// gemm_tc.cu - bf16 x bf16 -> fp32 GEMM on the 5th-generation tensor cores.
+//
+//   C[M,N] = epi( A[M,K] (bf16, row stride lda) x W[N,K]^T (bf16) )
+//
+// This is the throughput matmul of the encoder (voxtral_encoder.c:562-686 is a
+// chain of vox_linear*_bf16 calls, i.e. sgemm on widened weights,
+// voxtral_kernels.c:197-264): QKV, wo, w1|w3, w2, the conv stem as an
+// im2col-free GEMM (overlapping A rows through the TMA row stride) and the
+// adapter.  Activations are rounded to bf16 (the documented 2e-2 budget);
+// accumulation is fp32 in TMEM.
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0   TMA producer: cp.async.bulk.tensor 2-D tiles (128 x 64 bf16, SWIZZLE_128B)
+//            of A and W into a 6-stage shared-memory ring, mbarrier complete_tx
+//   warp 1   MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16
+//            (M=128, N=128, K=16) x4 per stage from UMMA smem descriptors into one
+//            of two 128-column TMEM accumulators; tcgen05.commit frees the stage /
+//            publishes the accumulator
+//   warps 2-5 epilogue: tcgen05.ld 32x32b.x32 (one TMEM lane quarter each), then
+//            bias / GELU / residual add / SwiGLU / bf16 cast straight to global,
+//            overlapping the next tile's main loop (double-buffered TMEM).
+#include "vox_internal.h"
+#include "gemm_tc.h"
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <string.h>
+
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 64;
+constexpr int STAGES = 6, ACC = 2;
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;       // 16 KB each
+constexpr int NT = 192;
+constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;   // + barriers + alignment slack
+constexpr uint32_t IDESC = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);   // K-major A and B
+
+__device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mb_init(uint64_t *b, unsigned n) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(b)), "r"(n));
+}
+__device__ __forceinline__ void mb_expect_tx(uint64_t *b, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mb_arrive(uint64_t *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(b)) : "memory");
+}
+__device__ __forceinline__ bool mb_try(uint64_t *b, unsigned parity) {
+    unsigned ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(s32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mb_wait(uint64_t *b, unsigned parity) {
+    if (mb_try(b, parity)) return;
+    const long long t0 = clock64();
+    while (!mb_try(b, parity))
+        if (clock64() - t0 > 4000000000LL) __trap();     // a protocol bug must not hang the GPU
+}
+__device__ __forceinline__ void tma_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(s32(dst)), "l"(map), "r"(s32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: rows of 128 B, 8-row groups 1024 B apart
+// (cute::UMMA::SmemDescriptor: start>>4 | LBO<<16 | SBO<<32 | version 1 <<46 | layout 2 <<61)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+struct KParams {
+    int M, N, K;
+    float *out_f32;
+    long ldo_f32;
+    uint16_t *out_bf16;
+    long ldo_bf16;
+    const float *bias;
+    int flags;
+};
+
+// epilogue of one thread: row `row`, 32 consecutive columns starting at `col`
+__device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col, const uint32_t (&r)[32]) {
+    float v[32];
+    #pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+    if (p.flags & TC_BIAS) {
+        #pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+            const float4 b = *reinterpret_cast<const float4 *>(p.bias + col + i);
+            v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+        }
+    }
+    if (p.flags & TC_GELU) {
+        #pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = gelu_tanh(v[i]);
+    }
+    if (p.flags & TC_SWIGLU) {
+        // 16 outputs: h[col/2 + i] = silu(v[2i]) * v[2i+1]   (voxtral_encoder.c:670-676)
+        float h[16];
+        #pragma unroll
+        for (int i = 0; i < 16; i++) h[i] = silu(v[2 * i]) * v[2 * i + 1];
+        if (p.flags & TC_OUT_BF16) {
+            uint4 *o = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + (col >> 1));
+            o[0] = make_uint4(pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]), pack_bf16(h[6], h[7]));
+            o[1] = make_uint4(pack_bf16(h[8], h[9]), pack_bf16(h[10], h[11]), pack_bf16(h[12], h[13]), pack_bf16(h[14], h[15]));
+        }
+        if (p.flags & TC_OUT_F32) {
+            float4 *o = reinterpret_cast<float4 *>(p.out_f32 + (size_t)row * p.ldo_f32 + (col >> 1));
+            #pragma unroll
+            for (int i = 0; i < 4; i++) o[i] = make_float4(h[4 * i], h[4 * i + 1], h[4 * i + 2], h[4 * i + 3]);
+        }
+        return;
+    }
+    if (p.flags & (TC_OUT_F32 | TC_RESIDUAL)) {
+        float4 *o = reinterpret_cast<float4 *>(p.out_f32 + (size_t)row * p.ldo_f32 + col);
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
+            float4 t = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            if (p.flags & TC_RESIDUAL) {
+                const float4 x = o[i];
+                t.x += x.x; t.y += x.y; t.z += x.z; t.w += x.w;
+            }
+            o[i] = t;
+        }
+    }
+    if (p.flags & TC_OUT_BF16) {
+        uint4 *o = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + col);
+        #pragma unroll
+        for (int i = 0; i < 4; i++)
+            o[i] = make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
+                              pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
+    }
+}
+
+__global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                        const __grid_constant__ CUtensorMap tmB, const KParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *base = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *sA = base, *sB = base + STAGES * A_BYTES;
+    uint64_t *full = reinterpret_cast<uint64_t *>(base + STAGES * (A_BYTES + B_BYTES));
+    uint64_t *empty = full + STAGES, *tfull = empty + STAGES, *tempty = tfull + ACC;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + ACC);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; i++) { mb_init(&full[i], 1); mb_init(&empty[i], 1); }
+        for (int i = 0; i < ACC; i++) { mb_init(&tfull[i], 1); mb_init(&tempty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "n"(ACC * BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int tiles_n = p.N / BN, tiles_m = (p.M + BM - 1) / BM;
+    const int total = tiles_n * tiles_m, nkb = p.K / BK;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0; unsigned ph = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+                for (int kb = 0; kb < nkb; kb++) {
+                    mb_wait(&empty[s], ph ^ 1u);
+                    mb_expect_tx(&full[s], A_BYTES + B_BYTES);
+                    tma_2d(sA + s * A_BYTES, &tmA, kb * BK, m0, &full[s]);
+                    tma_2d(sB + s * B_BYTES, &tmB, kb * BK, n0, &full[s]);
+                    if (++s == STAGES) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        int s = 0; unsigned ph = 0;
+        int it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, it++) {
+            const int as = it & 1;
+            const unsigned aph = (unsigned)(it >> 1) & 1u;
+            mb_wait(&tempty[as], aph ^ 1u);                 // epilogue has drained this accumulator
+            tc_fence_after();
+            const uint32_t d = tmem_base + (uint32_t)(as * BN);
+            for (int kb = 0; kb < nkb; kb++) {
+                mb_wait(&full[s], ph);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t da = umma_desc(s32(sA + s * A_BYTES)), db = umma_desc(s32(sB + s * B_BYTES));
+                    #pragma unroll
+                    for (int k = 0; k < BK / 16; k++)       // +32 B per K=16 step inside the 128 B swizzle row
+                        umma_f16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (kb | k) ? 1u : 0u);
+                    umma_commit(&empty[s]);                 // stage reusable once these MMAs retire
+                    if (kb == nkb - 1) umma_commit(&tfull[as]);
+                }
+                __syncwarp();
+                if (++s == STAGES) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else {
+        const int q = warp & 3;                             // TMEM lane quarter this warp may access
+        int it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, it++) {
+            const int as = it & 1;
+            const unsigned aph = (unsigned)(it >> 1) & 1u;
+            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+            const int row = m0 + q * 32 + lane;
+            mb_wait(&tfull[as], aph);
+            tc_fence_after();
+            #pragma unroll 1
+            for (int cc = 0; cc < BN / 32; cc++) {
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + cc * 32), r);
+                if (row < p.M) epilogue_row(p, row, n0 + cc * 32, r);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mb_arrive(&tempty[as]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(ACC * BN));
+    }
+}
+
+}  // namespace tc
+
+// ---- host ----------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static int g_sms = 0;
+
+static int tc_init(void) {
+    if (g_encode) return 0;
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    // resolved at run time: libvoxcuda.so keeps no link-time dependency on libcuda
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) {
+        vox_set_error("gemm_tc: cuTensorMapEncodeTiled not available from the driver");
+        return -1;
+    }
+    g_encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_TRY(cudaFuncSetAttribute(tc::gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+    return 0;
+}
+
+// 2-D bf16 tensor map: dim0 = K (contiguous), dim1 = rows with byte stride ld*2; box 64 x 128, 128 B swizzle
+static int make_map(CUtensorMap *m, const uint16_t *ptr, int rows, int K, long ld) {
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)tc::BM};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *)ptr, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        vox_set_error("gemm_tc: cuTensorMapEncodeTiled failed (%d) rows=%d K=%d ld=%ld ptr=%p", (int)r, rows, K, ld, ptr);
+        return -1;
+    }
+    return 0;
+}
+
+int gemm_tc(cudaStream_t st, int M, int N, int K, const uint16_t *A, long lda, const uint16_t *W,
+            const TcEpilogue &epi) {
+    if (M <= 0) return 0;
+    if (tc_init()) return -1;
+    if (N % tc::BN || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
+        vox_set_error("gemm_tc: unsupported shape M=%d N=%d K=%d lda=%ld", M, N, K, lda);
+        return -1;
+    }
+    CUtensorMap ma, mb;
+    if (make_map(&ma, A, M, K, lda) || make_map(&mb, W, N, K, K)) return -1;
+    tc::KParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.out_f32 = epi.out_f32; p.ldo_f32 = epi.ldo_f32; p.out_bf16 = epi.out_bf16; p.ldo_bf16 = epi.ldo_bf16;
+    p.bias = epi.bias; p.flags = epi.flags;
+    const int total = (N / tc::BN) * ((M + tc::BM - 1) / tc::BM);
+    const int grid = total < g_sms ? total : g_sms;
+    tc::gemm_tc_kernel<<<grid, tc::NT, tc::SMEM_BYTES, st>>>(ma, mb, p);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// fp32 -> bf16 (round to nearest even) rows, used to feed host fp32 activations to the tensor-core path
+__global__ void f32_to_bf16_kernel(const float *__restrict__ in, uint16_t *__restrict__ out, size_t n) {
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (i + 1 < n) {
+        const float2 v = *reinterpret_cast<const float2 *>(in + i);
+        *reinterpret_cast<uint32_t *>(out + i) = tc::pack_bf16(v.x, v.y);
+    } else if (i < n) {
+        out[i] = (uint16_t)(tc::pack_bf16(in[i], 0.f) & 0xFFFFu);
+    }
+}
+int f32_to_bf16(cudaStream_t st, const float *in, uint16_t *out, size_t n) {
+    if (!n) return 0;
+    const size_t pairs = (n + 1) / 2;
+    f32_to_bf16_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>(in, out, n);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// C ABI (include/vox_cuda.h): tensor-core twin of vox_cuda_sgemm_bf16 with host buffers.
+extern "C" int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const uint16_t *B_bf16, const float *bias,
+                                     int flags, float *C) {
+    if (!A || !B_bf16 || !C || M <= 0) return -1;
+    if (!vox_cuda_available() && !vox_cuda_init()) return -1;
+    float *dA = nullptr, *dC = nullptr, *dbias = nullptr;
+    uint16_t *dAb = nullptr, *dW = nullptr;
+    const int nout = (flags & TC_SWIGLU) ? N / 2 : N;
+    int rc = -1;
+    if (cudaMalloc((void **)&dA, (size_t)M * K * 4) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dAb, (size_t)M * K * 2) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dW, (size_t)N * K * 2) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dC, (size_t)M * nout * 4) != cudaSuccess) goto done;
+    if (cudaMemcpy(dA, A, (size_t)M * K * 4, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
+    if (cudaMemcpy(dW, B_bf16, (size_t)N * K * 2, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
+    if (flags & TC_RESIDUAL)
+        if (cudaMemcpy(dC, C, (size_t)M * nout * 4, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
+    if (bias) {
+        if (cudaMalloc((void **)&dbias, (size_t)N * 4) != cudaSuccess) goto done;
+        if (cudaMemcpy(dbias, bias, (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
+    }
+    {
+        if (f32_to_bf16(0, dA, dAb, (size_t)M * K)) goto done;
+        TcEpilogue e;
+        e.out_f32 = dC; e.ldo_f32 = nout; e.out_bf16 = nullptr; e.ldo_bf16 = 0; e.bias = dbias;
+        e.flags = (flags & (TC_BIAS | TC_GELU | TC_RESIDUAL | TC_SWIGLU)) | TC_OUT_F32;
+        if (!bias) e.flags &= ~TC_BIAS;
+        if (gemm_tc(0, M, N, K, dAb, K, dW, e)) goto done;
+    }
+    if (cudaMemcpy(C, dC, (size_t)M * nout * 4, cudaMemcpyDeviceToHost) != cudaSuccess) goto done;
+    rc = 0;
+done:
+    if (rc && !*vox_cuda_last_error())
+        vox_set_error("vox_cuda_gemm_bf16_tc(%d,%d,%d) failed: %s", M, N, K, cudaGetErrorString(cudaGetLastError()));
+    else if (rc)
+        fprintf(stderr, "vox_cuda_gemm_bf16_tc(%d,%d,%d): cuda status %s\n", M, N, K, cudaGetErrorString(cudaGetLastError()));
+    cudaFree(dA); cudaFree(dAb); cudaFree(dW); cudaFree(dC); cudaFree(dbias);
+    return rc;
+}
