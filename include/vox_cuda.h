@@ -199,6 +199,7 @@ int vox_cuda_sgemm_bf16(vox_cuda_model_t *m, int M, int N, int K, const float *A
 #define VOX_CUDA_TC_GELU      2
 #define VOX_CUDA_TC_RESIDUAL  4
 #define VOX_CUDA_TC_SWIGLU    8
+#define VOX_CUDA_TC_SPLIT_A   128  /* A = hi + lo (two bf16 terms): fp32-class accuracy, 2x tensor work */
 int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const uint16_t *B_bf16,
                           const float *bias, int flags, float *C);
 

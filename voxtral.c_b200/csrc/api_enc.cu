@@ -39,9 +39,14 @@ int enc_state_create(vox_cuda_state *s) {
     return 0;
 }
 
+void enc_fast_free(vox_cuda_state *s);
+int adapter_fast(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *out);
+static int enc_precise_mode(void);
+
 void enc_state_free(vox_cuda_state *s) {
     EncState *e = (EncState *)s->enc_priv;
     if (!e) return;
+    enc_fast_free(s);
     void *ptrs[] = {e->kv_k, e->kv_v, e->mel_in, e->c0, e->x, e->xn, e->qkv, e->att, e->gu, e->hh, e->encout, e->mid};
     for (void *p : ptrs) if (p) cudaFree(p);
     vox_mem_account(-(long)(2 * e->kv_bytes));
@@ -140,18 +145,23 @@ int enc_layers_precise(vox_cuda_state *s, float *x, int M, float *out) {
 
 int enc_layers_fast(vox_cuda_state *s, float *x, int M, float *out);  // enc_fast.cu
 
-static int enc_layers(vox_cuda_state *s, float *x, int M, float *out) {
+static int enc_precise_mode(void) {
     static int mode = -1;
     if (mode < 0) {
         const char *env = getenv("VOX_CUDA_ENC_PRECISE");
         mode = (env && atoi(env)) ? 1 : 0;
     }
-    return mode ? enc_layers_precise(s, x, M, out) : enc_layers_fast(s, x, M, out);
+    return mode;
+}
+
+static int enc_layers(vox_cuda_state *s, float *x, int M, float *out) {
+    return enc_precise_mode() ? enc_layers_precise(s, x, M, out) : enc_layers_fast(s, x, M, out);
 }
 
 // ---- adapter (vox_adapter_forward, voxtral_encoder.c:699-737) -----------------------
 static int adapter_device(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *mid, float *out) {
     vox_cuda_model *m = s->m;
+    if (!enc_precise_mode()) return adapter_fast(s, enc_rows, k_tokens, out);
     if (sgemm_bf16w(s->stream, k_tokens, DEC_DIM, 4 * ENC_DIM, enc_rows, 4 * ENC_DIM, m->adapter_w0, mid,
                     DEC_DIM, nullptr, EPI_GELU)) return -1;
     return sgemm_bf16w(s->stream, k_tokens, DEC_DIM, DEC_DIM, mid, DEC_DIM, m->adapter_w1, out, DEC_DIM,

@@ -98,7 +98,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 struct KParams {
-    int M, N, K;
+    int M, N, K, Kw;        // K = walked A columns (Kw or 2*Kw), Kw = weight columns
+    long split_off;
     float *out_f32;
     long ldo_f32;
     uint16_t *out_bf16;
@@ -106,6 +107,25 @@ struct KParams {
     const float *bias;
     int flags;
 };
+
+// bf16 store of NV consecutive values; TC_OUT_SPLIT adds the rounding residual lo = bf16(v - hi)
+template <int NV>
+__device__ __forceinline__ void store_bf16(const KParams &p, int row, int col, const float (&v)[NV]) {
+    uint32_t hi[NV / 2], lo[NV / 2];
+    #pragma unroll
+    for (int i = 0; i < NV / 2; i++) {
+        hi[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+        lo[i] = pack_bf16(v[2 * i] - bf16_lo(hi[i]), v[2 * i + 1] - bf16_hi(hi[i]));
+    }
+    uint4 *o = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + col);
+    #pragma unroll
+    for (int i = 0; i < NV / 8; i++) o[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
+    if (p.flags & TC_OUT_SPLIT) {
+        uint4 *ol = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + p.split_off + col);
+        #pragma unroll
+        for (int i = 0; i < NV / 8; i++) ol[i] = make_uint4(lo[4 * i], lo[4 * i + 1], lo[4 * i + 2], lo[4 * i + 3]);
+    }
+}
 
 // epilogue of one thread: row `row`, 32 consecutive columns starting at `col`
 __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col, const uint32_t (&r)[32]) {
@@ -128,11 +148,7 @@ __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col,
         float h[16];
         #pragma unroll
         for (int i = 0; i < 16; i++) h[i] = silu(v[2 * i]) * v[2 * i + 1];
-        if (p.flags & TC_OUT_BF16) {
-            uint4 *o = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + (col >> 1));
-            o[0] = make_uint4(pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]), pack_bf16(h[6], h[7]));
-            o[1] = make_uint4(pack_bf16(h[8], h[9]), pack_bf16(h[10], h[11]), pack_bf16(h[12], h[13]), pack_bf16(h[14], h[15]));
-        }
+        if (p.flags & TC_OUT_BF16) store_bf16<16>(p, row, col >> 1, h);
         if (p.flags & TC_OUT_F32) {
             float4 *o = reinterpret_cast<float4 *>(p.out_f32 + (size_t)row * p.ldo_f32 + (col >> 1));
             #pragma unroll
@@ -152,13 +168,7 @@ __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col,
             o[i] = t;
         }
     }
-    if (p.flags & TC_OUT_BF16) {
-        uint4 *o = reinterpret_cast<uint4 *>(p.out_bf16 + (size_t)row * p.ldo_bf16 + col);
-        #pragma unroll
-        for (int i = 0; i < 4; i++)
-            o[i] = make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
-                              pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
-    }
+    if (p.flags & TC_OUT_BF16) store_bf16<32>(p, row, col, v);
 }
 
 __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -199,7 +209,7 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
                     mb_wait(&empty[s], ph ^ 1u);
                     mb_expect_tx(&full[s], A_BYTES + B_BYTES);
                     tma_2d(sA + s * A_BYTES, &tmA, kb * BK, m0, &full[s]);
-                    tma_2d(sB + s * B_BYTES, &tmB, kb * BK, n0, &full[s]);
+                    tma_2d(sB + s * B_BYTES, &tmB, (kb * BK) % p.Kw, n0, &full[s]);
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
                 }
             }
@@ -296,18 +306,18 @@ static int make_map(CUtensorMap *m, const uint16_t *ptr, int rows, int K, long l
     return 0;
 }
 
-int gemm_tc(cudaStream_t st, int M, int N, int K, const uint16_t *A, long lda, const uint16_t *W,
+int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, long lda, const uint16_t *W,
             const TcEpilogue &epi) {
     if (M <= 0) return 0;
     if (tc_init()) return -1;
-    if (N % tc::BN || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
+    if ((KA != K && KA != 2 * K) || N % tc::BN || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
         vox_set_error("gemm_tc: unsupported shape M=%d N=%d K=%d lda=%ld", M, N, K, lda);
         return -1;
     }
     CUtensorMap ma, mb;
-    if (make_map(&ma, A, M, K, lda) || make_map(&mb, W, N, K, K)) return -1;
+    if (make_map(&ma, A, M, KA, lda) || make_map(&mb, W, N, K, K)) return -1;
     tc::KParams p;
-    p.M = M; p.N = N; p.K = K;
+    p.M = M; p.N = N; p.K = KA; p.Kw = K; p.split_off = epi.split_off;
     p.out_f32 = epi.out_f32; p.ldo_f32 = epi.ldo_f32; p.out_bf16 = epi.out_bf16; p.ldo_bf16 = epi.ldo_bf16;
     p.bias = epi.bias; p.flags = epi.flags;
     const int total = (N / tc::BN) * ((M + tc::BM - 1) / tc::BM);
@@ -318,20 +328,22 @@ int gemm_tc(cudaStream_t st, int M, int N, int K, const uint16_t *A, long lda, c
     return 0;
 }
 
-// fp32 -> bf16 (round to nearest even) rows, used to feed host fp32 activations to the tensor-core path
-__global__ void f32_to_bf16_kernel(const float *__restrict__ in, uint16_t *__restrict__ out, size_t n) {
-    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
-    if (i + 1 < n) {
-        const float2 v = *reinterpret_cast<const float2 *>(in + i);
-        *reinterpret_cast<uint32_t *>(out + i) = tc::pack_bf16(v.x, v.y);
-    } else if (i < n) {
-        out[i] = (uint16_t)(tc::pack_bf16(in[i], 0.f) & 0xFFFFu);
+// fp32 -> bf16 (round to nearest even) rows for the A operand; split writes [hi | lo]
+__global__ void f32_to_bf16_rows_kernel(const float *__restrict__ in, long ldi, uint16_t *__restrict__ out, long ldo,
+                                        int cols, int split) {
+    const float *ir = in + (size_t)blockIdx.x * ldi;
+    uint16_t *orow = out + (size_t)blockIdx.x * ldo;
+    for (int i = threadIdx.x * 2; i < cols; i += blockDim.x * 2) {
+        const float2 v = *reinterpret_cast<const float2 *>(ir + i);
+        const uint32_t hi = tc::pack_bf16(v.x, v.y);
+        *reinterpret_cast<uint32_t *>(orow + i) = hi;
+        if (split)
+            *reinterpret_cast<uint32_t *>(orow + cols + i) = tc::pack_bf16(v.x - bf16_lo(hi), v.y - bf16_hi(hi));
     }
 }
-int f32_to_bf16(cudaStream_t st, const float *in, uint16_t *out, size_t n) {
-    if (!n) return 0;
-    const size_t pairs = (n + 1) / 2;
-    f32_to_bf16_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>(in, out, n);
+int f32_to_bf16_rows(cudaStream_t st, const float *in, long ldi, uint16_t *out, long ldo, int rows, int cols, int split) {
+    if (rows <= 0) return 0;
+    f32_to_bf16_rows_kernel<<<rows, 256, 0, st>>>(in, ldi, out, ldo, cols, split);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -347,7 +359,7 @@ extern "C" int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const 
     const int nout = (flags & TC_SWIGLU) ? N / 2 : N;
     int rc = -1;
     if (cudaMalloc((void **)&dA, (size_t)M * K * 4) != cudaSuccess) goto done;
-    if (cudaMalloc((void **)&dAb, (size_t)M * K * 2) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dAb, (size_t)M * K * 4) != cudaSuccess) goto done;
     if (cudaMalloc((void **)&dW, (size_t)N * K * 2) != cudaSuccess) goto done;
     if (cudaMalloc((void **)&dC, (size_t)M * nout * 4) != cudaSuccess) goto done;
     if (cudaMemcpy(dA, A, (size_t)M * K * 4, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
@@ -359,12 +371,13 @@ extern "C" int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const 
         if (cudaMemcpy(dbias, bias, (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess) goto done;
     }
     {
-        if (f32_to_bf16(0, dA, dAb, (size_t)M * K)) goto done;
+        const int split = (flags & 128) ? 1 : 0;           // VOX_CUDA_TC_SPLIT_A
+        if (f32_to_bf16_rows(0, dA, K, dAb, split ? 2 * K : K, M, K, split)) goto done;
         TcEpilogue e;
-        e.out_f32 = dC; e.ldo_f32 = nout; e.out_bf16 = nullptr; e.ldo_bf16 = 0; e.bias = dbias;
+        e.out_f32 = dC; e.ldo_f32 = nout; e.out_bf16 = nullptr; e.ldo_bf16 = 0; e.bias = dbias; e.split_off = 0;
         e.flags = (flags & (TC_BIAS | TC_GELU | TC_RESIDUAL | TC_SWIGLU)) | TC_OUT_F32;
         if (!bias) e.flags &= ~TC_BIAS;
-        if (gemm_tc(0, M, N, K, dAb, K, dW, e)) goto done;
+        if (gemm_tc(0, M, N, K, split ? 2 * K : K, dAb, split ? 2 * K : K, dW, e)) goto done;
     }
     if (cudaMemcpy(C, dC, (size_t)M * nout * 4, cudaMemcpyDeviceToHost) != cudaSuccess) goto done;
     rc = 0;

@@ -10,6 +10,7 @@ enum {
     TC_SWIGLU = 8,      // columns are (gate, up) pairs: out[m][n/2] = silu(g) * u
     TC_OUT_F32 = 16,    // write fp32 to out_f32 (ldo_f32)
     TC_OUT_BF16 = 32,   // write bf16 to out_bf16 (ldo_bf16)
+    TC_OUT_SPLIT = 64,  // with TC_OUT_BF16: also write the bf16 rounding residual at column offset split_off
 };
 
 struct TcEpilogue {
@@ -19,10 +20,17 @@ struct TcEpilogue {
     long ldo_bf16;
     const float *bias;
     int flags;
+    long split_off;     // TC_OUT_SPLIT: lo part goes to out_bf16[row][split_off + col]
 };
 
 // A: device bf16 [M rows, K] with row stride lda (elements; rows may overlap: lda < K is allowed,
 // lda*2 must be a multiple of 16 bytes).  W: device bf16 [N, K] row-major.
 // N % 128 == 0, K % 64 == 0.  Returns 0 on success.
-int gemm_tc(cudaStream_t st, int M, int N, int K, const uint16_t *A, long lda, const uint16_t *W,
+// Split activations ("bf16x2"): when KA == 2*K the A rows hold [hi(K) | lo(K)] with
+// a = hi + lo to ~16 mantissa bits; the kernel walks KA and wraps the W coordinate
+// modulo K, i.e. C = hi W^T + lo W^T, which restores fp32-class accuracy at twice
+// the (cheap) tensor work.  KA == K is the plain single-bf16 product.
+int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, long lda, const uint16_t *W,
             const TcEpilogue &epi);
+// fp32 -> bf16 rows; split != 0 writes [hi | lo] rows of 2*cols
+int f32_to_bf16_rows(cudaStream_t st, const float *in, long ldi, uint16_t *out, long ldo, int rows, int cols, int split);
