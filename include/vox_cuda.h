@@ -178,6 +178,24 @@ int vox_cuda_adapter_discard_before(vox_cuda_state_t *s, int keep_from);
  * samples must hold (n_frames-1)*160+400 values. */
 int vox_cuda_mel_frames(const float *samples, int n_frames, float *mel_out);
 
+/* ---- whole clip (batch mode) --------------------------------------------
+ * The hot path of vox_transcribe_audio (voxtral.c:1390-1396: vox_stream_feed of
+ * the whole clip + vox_stream_finish) in one call with every stage on the
+ * device.  pcm: the PADDED sample buffer exactly as the reference's mel context
+ * sees it - 200 + 32*1280 zeros, the samples, the flush padding
+ * (voxtral.c:1645-1658) and the 200 reflected samples of vox_mel_finish
+ * (voxtral_audio.c:602-629); n_frames = mel frames to compute.  pcm may be a
+ * host pointer (pinned memory from vox_cuda_host_alloc avoids a staging copy)
+ * or NULL to use the buffer last uploaded with vox_cuda_pcm_upload (device
+ * resident input).  prompt_len = 1 + 32 + delay_tokens (39).  Writes the greedy
+ * token ids of all decode steps (the caller truncates at EOS = 2) and returns
+ * their count; *device_ms (optional) = CUDA-event time of the whole call. */
+void *vox_cuda_host_alloc(size_t bytes);
+void  vox_cuda_host_free(void *p);
+int   vox_cuda_pcm_upload(vox_cuda_state_t *s, const float *pcm, int n_samples);
+int   vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, int n_frames,
+                          int prompt_len, int *tokens_out, int max_tokens, float *device_ms);
+
 /* ---- op-level hook (replaces vox_metal_sgemm_bf16, voxtral_metal.h:38,
  *      call sites voxtral_kernels.c:199-204,218-229,249-254) -------------- */
 /* C[M,N] = A[M,K] (f32 host) x B[N,K]^T.  B_bf16 is a host pointer: if it is

@@ -1,6 +1,7 @@
 // api_dec.cu - per-stream state and the decoder entry points of the C ABI.
 #include "vox_internal.h"
 #include "rows.h"
+#include "gemm_tc.h"
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
@@ -10,6 +11,7 @@ const unsigned *dec_mega_error_record(vox_cuda_state *s);
 int enc_state_create(vox_cuda_state *s);
 void enc_state_free(vox_cuda_state *s);
 void enc_state_reset(vox_cuda_state *s);
+void batch_free(vox_cuda_state *s);
 
 static int dmalloc(void **p, size_t bytes) {
     if (cudaMalloc(p, bytes) != cudaSuccess) {
@@ -72,6 +74,7 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     if (!s) return;
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->step_graph) cudaGraphExecDestroy(s->step_graph);
+    batch_free(s);
     enc_state_free(s);
     dec_mega_free(s);
     void *ptrs[] = {s->kv_k, s->kv_v, s->d_params, s->d_x, s->d_q, s->d_attn, s->d_h, s->d_logits,
@@ -266,6 +269,15 @@ extern "C" float vox_cuda_bench_decoder_steps(vox_cuda_state_t *s, int prev_toke
 // PF_ROWS (causal attention makes blocked prefill exact).
 constexpr int PF_ROWS = 64;
 
+// Two arithmetic modes, like the encoder: default = tcgen05 GEMMs on bf16x2 split
+// activations (fp32-class accuracy, weights streamed once at HBM speed);
+// VOX_CUDA_PREFILL_F32=1 = fp32 CUDA-core GEMM.
+static int prefill_f32_mode(void) {
+    static int m = -1;
+    if (m < 0) { const char *env = getenv("VOX_CUDA_PREFILL_F32"); m = (env && atoi(env)) ? 1 : 0; }
+    return m;
+}
+
 static int ensure_pf(vox_cuda_state *s) {
     const size_t per_row = (size_t)(2 * DEC_DIM + DEC_QKV + DEC_QDIM + 2 * DEC_HIDDEN + DEC_HIDDEN) * 4;
     const size_t need = per_row * PF_ROWS;
@@ -274,6 +286,13 @@ static int ensure_pf(vox_cuda_state *s) {
     if (cudaMalloc((void **)&s->pf_buf, need) != cudaSuccess) { vox_set_error("prefill scratch alloc failed"); return -1; }
     s->pf_bytes = need;
     return 0;
+}
+
+static TcEpilogue pf_epi(float *of, long ldf, uint16_t *ob, long ldb, int flags, long split_off = 0) {
+    TcEpilogue t;
+    t.out_f32 = of; t.ldo_f32 = ldf; t.out_bf16 = ob; t.ldo_bf16 = ldb; t.bias = nullptr; t.flags = flags;
+    t.split_off = split_off;
+    return t;
 }
 
 // x_dev: [seq_len, 3072] device, consumed (used as the residual stream).
@@ -286,6 +305,11 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
     float *att = qkv + (size_t)PF_ROWS * DEC_QKV;
     float *gu = att + (size_t)PF_ROWS * DEC_QDIM;
     float *hh = gu + (size_t)PF_ROWS * 2 * DEC_HIDDEN;
+    // bf16x2 views of the same scratch (tensor-core mode): [hi | lo] rows
+    uint16_t *xn_b = (uint16_t *)xn;      // [PF_ROWS][2*3072]   (same bytes as fp32 [PF_ROWS][3072])
+    uint16_t *att_b = (uint16_t *)gu;     // [PF_ROWS][2*4096]   (gu is unused in this mode)
+    uint16_t *hh_b = (uint16_t *)hh;      // [PF_ROWS][2*9216]
+    const bool tcm = !prefill_f32_mode();
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
     for (int r0 = 0; r0 < seq_len; r0 += PF_ROWS) {
         const int M = seq_len - r0 < PF_ROWS ? seq_len - r0 : PF_ROWS;
@@ -295,17 +319,35 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
         for (int l = 0; l < m->n_dec; l++) {
             const DecLayerDev &L = m->dec[l];
             float *kc = s->kv_k + l * kv_layer, *vc = s->kv_v + l * kv_layer;
-            if (rows_rmsnorm(st, x, DEC_DIM, L.attn_norm, nullptr, xn, DEC_DIM, M, DEC_DIM)) return -1;
-            if (sgemm_bf16w(st, M, DEC_QKV, DEC_DIM, xn, DEC_DIM, L.wqkv, qkv, DEC_QKV, nullptr, EPI_NONE)) return -1;
+            const float *ada = m->ada_scale + (size_t)l * DEC_DIM;
+            if (tcm) {
+                if (rows_rmsnorm_bf16(st, x, DEC_DIM, L.attn_norm, nullptr, xn_b, 2 * DEC_DIM, M, DEC_DIM, 1)) return -1;
+                if (gemm_tc(st, M, DEC_QKV, DEC_DIM, 2 * DEC_DIM, xn_b, 2 * DEC_DIM, L.wqkv,
+                            pf_epi(qkv, DEC_QKV, nullptr, 0, TC_OUT_F32))) return -1;
+            } else {
+                if (rows_rmsnorm(st, x, DEC_DIM, L.attn_norm, nullptr, xn, DEC_DIM, M, DEC_DIM)) return -1;
+                if (sgemm_bf16w(st, M, DEC_QKV, DEC_DIM, xn, DEC_DIM, L.wqkv, qkv, DEC_QKV, nullptr, EPI_NONE)) return -1;
+            }
             if (rows_rope_kv(st, qkv, M, DEC_QDIM, DEC_KVDIM, DEC_HD, m->inv_freq_dec, pos0,
                              DEC_WINDOW - 1, kc, vc)) return -1;
             if (rows_attention(st, DEC_HD, qkv, DEC_QKV, kc, vc, DEC_KVDIM, DEC_WINDOW - 1, DEC_HEADS,
                                DEC_HEADS / DEC_KVH, M, pos0, first_valid, DEC_WINDOW, att, DEC_QDIM)) return -1;
-            if (sgemm_bf16w(st, M, DEC_DIM, DEC_QDIM, att, DEC_QDIM, L.wo, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
-            if (rows_rmsnorm(st, x, DEC_DIM, L.ffn_norm, m->ada_scale + (size_t)l * DEC_DIM, xn, DEC_DIM, M, DEC_DIM)) return -1;
-            if (sgemm_bf16w(st, M, 2 * DEC_HIDDEN, DEC_DIM, xn, DEC_DIM, L.w13, gu, 2 * DEC_HIDDEN, nullptr, EPI_NONE)) return -1;
-            if (rows_swiglu(st, gu, hh, M, DEC_HIDDEN)) return -1;
-            if (sgemm_bf16w(st, M, DEC_DIM, DEC_HIDDEN, hh, DEC_HIDDEN, L.w2, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
+            if (tcm) {
+                if (f32_to_bf16_rows(st, att, DEC_QDIM, att_b, 2 * DEC_QDIM, M, DEC_QDIM, 1)) return -1;
+                if (gemm_tc(st, M, DEC_DIM, DEC_QDIM, 2 * DEC_QDIM, att_b, 2 * DEC_QDIM, L.wo,
+                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL))) return -1;
+                if (rows_rmsnorm_bf16(st, x, DEC_DIM, L.ffn_norm, ada, xn_b, 2 * DEC_DIM, M, DEC_DIM, 1)) return -1;
+                if (gemm_tc(st, M, 2 * DEC_HIDDEN, DEC_DIM, 2 * DEC_DIM, xn_b, 2 * DEC_DIM, L.w13,
+                            pf_epi(nullptr, 0, hh_b, 2 * DEC_HIDDEN, TC_SWIGLU | TC_OUT_BF16 | TC_OUT_SPLIT, DEC_HIDDEN))) return -1;
+                if (gemm_tc(st, M, DEC_DIM, DEC_HIDDEN, 2 * DEC_HIDDEN, hh_b, 2 * DEC_HIDDEN, L.w2,
+                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL))) return -1;
+            } else {
+                if (sgemm_bf16w(st, M, DEC_DIM, DEC_QDIM, att, DEC_QDIM, L.wo, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
+                if (rows_rmsnorm(st, x, DEC_DIM, L.ffn_norm, ada, xn, DEC_DIM, M, DEC_DIM)) return -1;
+                if (sgemm_bf16w(st, M, 2 * DEC_HIDDEN, DEC_DIM, xn, DEC_DIM, L.w13, gu, 2 * DEC_HIDDEN, nullptr, EPI_NONE)) return -1;
+                if (rows_swiglu(st, gu, hh, M, DEC_HIDDEN)) return -1;
+                if (sgemm_bf16w(st, M, DEC_DIM, DEC_HIDDEN, hh, DEC_HIDDEN, L.w2, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
+            }
         }
         s->h_params.pos += M;
         s->h_params.n_valid = s->h_params.n_valid + M > DEC_WINDOW ? DEC_WINDOW : s->h_params.n_valid + M;

@@ -93,14 +93,14 @@ int enc_layers_fast(vox_cuda_state *s, float *x, int M, float *out) {
     for (int l = 0; l < m->n_enc; l++) {
         const EncLayerDev &L = m->enc[l];
         float *kc = e->kv_k + l * kv_layer, *vc = e->kv_v + l * kv_layer;
-        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.attn_norm, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
+        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.attn_norm, nullptr, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
         if (gemm_tc(st, M, 3 * ENC_QKV, ENC_DIM, mul * ENC_DIM, f->xn_b, mul * ENC_DIM, L.wqkv,
                     epi(e->qkv, 3 * ENC_QKV, nullptr, 0, L.bqkv, TC_BIAS | TC_OUT_F32))) return -1;
         if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
         if (enc_attention(s, e->qkv, kc, vc, M, pos0, f->att_b, mul * ENC_QKV, sp)) return -1;
         if (gemm_tc(st, M, ENC_DIM, ENC_QKV, mul * ENC_QKV, f->att_b, mul * ENC_QKV, L.wo,
                     epi(x, ENC_DIM, nullptr, 0, L.bo, TC_BIAS | TC_RESIDUAL))) return -1;
-        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.ffn_norm, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
+        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.ffn_norm, nullptr, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
         if (gemm_tc(st, M, 2 * ENC_HIDDEN, ENC_DIM, mul * ENC_DIM, f->xn_b, mul * ENC_DIM, L.w13,
                     epi(nullptr, 0, f->hh_b, mul * ENC_HIDDEN, nullptr, TC_SWIGLU | TC_OUT_BF16 | osp, ENC_HIDDEN))) return -1;
         if (gemm_tc(st, M, ENC_DIM, ENC_HIDDEN, mul * ENC_HIDDEN, f->hh_b, mul * ENC_HIDDEN, L.w2,

@@ -28,8 +28,8 @@ __global__ void __launch_bounds__(256) rows_rmsnorm_kernel(
 
 // same, output rounded to bf16 (A operand of the tensor-core GEMMs)
 __global__ void __launch_bounds__(256) rows_rmsnorm_bf16_kernel(
-    const float *__restrict__ x, long ldx, const float *__restrict__ w, uint16_t *__restrict__ out, long ldo, int dim,
-    int split) {
+    const float *__restrict__ x, long ldx, const float *__restrict__ w, const float *__restrict__ ada,
+    uint16_t *__restrict__ out, long ldo, int dim, int split) {
     const float *xr = x + (size_t)blockIdx.x * ldx;
     uint16_t *orow = out + (size_t)blockIdx.x * ldo;
     __shared__ float red[8];
@@ -43,7 +43,8 @@ __global__ void __launch_bounds__(256) rows_rmsnorm_bf16_kernel(
     for (int i = 0; i < 8; i++) tot += red[i];
     const float rinv = 1.0f / sqrtf(tot / (float)dim + NORM_EPS);
     for (int i = threadIdx.x * 2; i < dim; i += 512) {
-        const float y0 = xr[i] * rinv * w[i], y1 = xr[i + 1] * rinv * w[i + 1];
+        float y0 = xr[i] * rinv * w[i], y1 = xr[i + 1] * rinv * w[i + 1];
+        if (ada) { y0 *= (1.0f + ada[i]); y1 *= (1.0f + ada[i + 1]); }
         const __nv_bfloat162 v = __floats2bfloat162_rn(y0, y1);
         *reinterpret_cast<__nv_bfloat162 *>(orow + i) = v;
         if (split)   // second bf16 term: y = hi + lo to ~16 mantissa bits
@@ -52,10 +53,10 @@ __global__ void __launch_bounds__(256) rows_rmsnorm_bf16_kernel(
     }
 }
 
-int rows_rmsnorm_bf16(cudaStream_t st, const float *x, long ldx, const float *w, uint16_t *out, long ldo,
-                      int rows, int dim, int split) {
+int rows_rmsnorm_bf16(cudaStream_t st, const float *x, long ldx, const float *w, const float *ada, uint16_t *out,
+                      long ldo, int rows, int dim, int split) {
     if (rows <= 0) return 0;
-    rows_rmsnorm_bf16_kernel<<<rows, 256, 0, st>>>(x, ldx, w, out, ldo, dim, split);
+    rows_rmsnorm_bf16_kernel<<<rows, 256, 0, st>>>(x, ldx, w, ada, out, ldo, dim, split);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return 0;

@@ -82,6 +82,7 @@ struct vox_cuda_state {
     float *pf_buf; size_t pf_bytes;
     // ---- encoder ----
     void *enc_priv;              // EncState*, see enc_host.cu
+    void *batch;                 // BatchBuf*, api_batch.cu (resident PCM / mel of the whole-clip entry point)
     // ---- adapter tokens (device) ----
     float *adapter_buf;          // [adapter_cap][3072]
     int adapter_cap, adapter_count, adapter_offset; // count = total logical, offset = first kept

@@ -75,6 +75,10 @@ SIGNATURES = {
     "vox_cuda_adapter_discard_before": (C.c_int, [C.c_void_p, C.c_int]),
     "vox_cuda_mel_frames": (C.c_int, [f32p, C.c_int, f32p]),
     "vox_cuda_sgemm_bf16": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, f32p, u16p, f32p]),
+    "vox_cuda_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "vox_cuda_host_free": (None, [C.c_void_p]),
+    "vox_cuda_pcm_upload": (C.c_int, [C.c_void_p, f32p, C.c_int]),
+    "vox_cuda_transcribe": (C.c_int, [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, i32p, C.c_int, C.POINTER(C.c_float)]),
     "vox_cuda_gemm_bf16_tc": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, f32p, C.c_int, f32p]),
     "vox_cuda_bench_decoder_steps": (C.c_float, [C.c_void_p, C.c_int, C.c_int, C.c_int, i32p]),
 }
