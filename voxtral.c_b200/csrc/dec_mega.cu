@@ -80,6 +80,7 @@ struct Params {
     int n_steps;
     int inflight;                           // max tiles requested but not yet landed (1..NSTAGE)
     int l2_ahead;                           // tiles the L2 prefetcher runs ahead of the producer (0 = off)
+    int spin_ns;                            // back-off of the grid-barrier poll loop (0 = tight loop)
     unsigned *err;
     unsigned long long *prof;               // optional [G][8] cycle counters of consumer thread 0 (debug)
 };
@@ -157,7 +158,7 @@ __device__ __forceinline__ unsigned atom_release_add(unsigned *p, unsigned v) {
     return old;
 }
 __device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsigned *err, long long *t_own = nullptr,
-                                          long long *t_atom = nullptr) {
+                                          long long *t_atom = nullptr, unsigned spin_ns = 0) {
     consumer_sync();
     if (threadIdx.x == 0) {
         if (t_atom) {                           // profiling variant: returning atomic = measurable round trip
@@ -169,6 +170,7 @@ __device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsign
         }
         const long long t0 = clock64();
         while ((int)(ld_relaxed(bar) - target) < 0) {
+            if (spin_ns) __nanosleep(spin_ns);
             if (clock64() - t0 > 3000000000LL) die(err, 2u, target);
         }
         if (t_own) *t_own += clock64() - t0;    // spin time
@@ -231,17 +233,37 @@ __device__ __forceinline__ void prefetch_l2(Smem &sm, unsigned &g, const uint16_
     }
 }
 
+// Packed fp32 FMA (Blackwell FFMA2): both halves of a bf16 pair in one instruction.
+// Halves the FMA-pipe work of the GEMV inner loop (2 ALU unpacks + 1 FFMA2 per weight pair).
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long A, B, C, D;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(A) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(B) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(C) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(D) : "l"(A), "l"(B), "l"(C));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(D));
+    return d;
+}
+__device__ __forceinline__ float2 dot8x2(const uint4 &w, const float4 &a, const float4 &b, float2 acc) {
+    acc = ffma2(make_float2(bf16_lo(w.x), bf16_hi(w.x)), make_float2(a.x, a.y), acc);
+    acc = ffma2(make_float2(bf16_lo(w.y), bf16_hi(w.y)), make_float2(a.z, a.w), acc);
+    acc = ffma2(make_float2(bf16_lo(w.z), bf16_hi(w.z)), make_float2(b.x, b.y), acc);
+    acc = ffma2(make_float2(bf16_lo(w.w), bf16_hi(w.w)), make_float2(b.z, b.w), acc);
+    return acc;
+}
+
 // ---- consumer: one warp multiplies one whole tile ------------------------------------------
 template <int K, int TR, bool FULL>
 __device__ __forceinline__ void warp_tile(const unsigned char *tile, int n, const XVec &x, float (&acc)[TR], int lane) {
     constexpr int NCH = K / 256;                                  // 16-byte chunks per lane per row
-    constexpr int NACC = TR >= 4 ? 1 : (TR >= 2 ? 2 : 4);         // accumulators per row (ILP)
+    constexpr int NACC = TR >= 4 ? 1 : (TR >= 2 ? 2 : 4);         // packed accumulators per row (ILP)
     static_assert(NCH % 4 == 0, "");
-    float a[TR][NACC];
+    float2 a[TR][NACC];
     #pragma unroll
     for (int r = 0; r < TR; r++)
         #pragma unroll
-        for (int k = 0; k < NACC; k++) a[r][k] = 0.f;
+        for (int k = 0; k < NACC; k++) a[r][k] = make_float2(0.f, 0.f);
     const uint4 *wp = reinterpret_cast<const uint4 *>(tile) + lane;
     #pragma unroll 4
     for (int ch = 0; ch < NCH; ch++) {
@@ -250,15 +272,15 @@ __device__ __forceinline__ void warp_tile(const unsigned char *tile, int n, cons
         for (int r = 0; r < TR; r++) {
             if (FULL || r < n) {
                 const uint4 wv = wp[r * (K / 8) + ch * 32];
-                a[r][ch % NACC] = dot8(wv, A, B, a[r][ch % NACC]);
+                a[r][ch % NACC] = dot8x2(wv, A, B, a[r][ch % NACC]);
             }
         }
     }
     #pragma unroll
     for (int r = 0; r < TR; r++) {
-        float t = a[r][0];
+        float t = a[r][0].x + a[r][0].y;
         #pragma unroll
-        for (int k = 1; k < NACC; k++) t += a[r][k];
+        for (int k = 1; k < NACC; k++) t += a[r][k].x + a[r][k].y;
         acc[r] = t;
     }
 }
@@ -546,7 +568,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         const long long tg_ = clock64();                            \
         const bool rec_ = P.prof && tid == 0 && step == P.n_steps - 1 && bar_k < 12;   \
         if (rec_) P.prof[(size_t)c * 32 + 8 + 2 * bar_k] = globaltimer_ns();          \
-        grid_sync(P.bar, bar_target += G, P.err, P.prof ? &t_own : nullptr, P.prof ? &t_atom : nullptr); \
+        grid_sync(P.bar, bar_target += G, P.err, P.prof ? &t_own : nullptr, P.prof ? &t_atom : nullptr, (unsigned)P.spin_ns); \
         if (rec_) P.prof[(size_t)c * 32 + 9 + 2 * bar_k] = globaltimer_ns();          \
         bar_k++;                                                    \
         t_grid += clock64() - tg_;                                  \
@@ -783,7 +805,7 @@ struct MegaHost {
     DecLayerDev *d_layers;
     unsigned *d_bar, *d_err;
     unsigned long long *d_prof;   // [grid][8] when VOX_CUDA_MEGA_PROF=1
-    int inflight, l2_ahead;
+    int inflight, l2_ahead, spin_ns;
     unsigned bar_count;      // value of *d_bar after all launches enqueued so far
     int grid;
     int barriers_per_step;
@@ -811,6 +833,11 @@ int dec_mega_init(vox_cuda_state *s) {
     h->bar_count = 0;
     h->inflight = mk::NSTAGE;
     h->l2_ahead = 0;
+    h->spin_ns = 0;
+    {
+        const char *env = getenv("VOX_CUDA_MEGA_SPIN_NS");
+        if (env && atoi(env) >= 0) h->spin_ns = atoi(env);
+    }
     {
         const char *env = getenv("VOX_CUDA_MEGA_L2AHEAD");
         if (env && atoi(env) >= 0 && atoi(env) <= 256) h->l2_ahead = atoi(env);
@@ -854,7 +881,7 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.blockmax = s->d_blockmax;
     P.embed_in = s->d_embed_in; P.adapter = s->adapter_buf;
     P.params = s->d_params; P.tokens = s->d_tokens;
-    P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.err = h->d_err; P.prof = h->d_prof;
+    P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.spin_ns = h->spin_ns; P.err = h->d_err; P.prof = h->d_prof;
     void *args[] = {&P};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void *)mk::dec_mega_kernel, dim3(h->grid), dim3(mk::NT), args,
                                          sizeof(mk::Smem), s->stream));
