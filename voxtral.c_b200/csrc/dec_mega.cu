@@ -9,15 +9,15 @@
 //   * warp 8 (one elected lane) is the PRODUCER: it walks the static list of
 //     weight tiles this CTA owns - contiguous row ranges of every matrix, in
 //     consumption order, across phase, layer and token boundaries - and streams
-//     them into a 7 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
+//     them into an 8 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
 //     bulk copies, mbarrier complete_tx, L2 evict_first).  It never waits for
 //     activations, only for ring space, so the HBM pipe stays busy while the
-//     consumers sit in a grid barrier (168 KB/SM = 3.8 us of HBM time).
-//   * warps 0-7 are CONSUMERS: tiles (1-4 whole rows) are dealt round-robin to
-//     warps 0-6 (warp s owns ring stage s), each warp multiplies its tile against the activation vector
-//     in shared memory on its own - no cross-warp reduction, no per-tile CTA
-//     barrier - and its epilogue lanes apply RoPE + KV-ring write, residual
-//     add, SwiGLU, or logits + running argmax.
+//     consumers sit in a grid barrier (192 KB/SM = 4.4 us of HBM time).
+//   * warps 0-7 are CONSUMERS: each warp owns a fixed K-slice of every row (its
+//     slice of the activation vector lives in registers), all warps multiply each
+//     tile as it lands (packed FFMA2), row sums are combined once per group of
+//     <= 16 rows, and the group's epilogue lanes apply RoPE + KV-ring write,
+//     residual add, SwiGLU, or logits + running argmax.
 //   * phases are separated by a grid-wide barrier (release/acquire counter in
 //     global memory); attention is split over (kv head, key range) CTAs and its
 //     partials are merged in the wo prologue.
@@ -30,11 +30,15 @@
 
 namespace mk {
 
+#ifndef MK_PROF
+#define MK_PROF 1                           // per-tile wait timing of the consumers (VOX_CUDA_MEGA_PROF readout)
+#endif
+
 constexpr int CW = 8;                       // consumer warps
 constexpr int CT = CW * 32;                 // consumer threads
 constexpr int NT = CT + 64;                 // + producer warp + L2 prefetch warp
 constexpr int STAGE_BYTES = 24576;
-constexpr int NSTAGE = 7;
+constexpr int NSTAGE = 8;
 constexpr int MAXTR = 4;                    // rows per tile at K = 3072
 constexpr int PART_LD = DEC_HD + 4;         // acc[128], m, l, pad (16-byte rows)
 constexpr int MAX_SPLITS = 32;
@@ -46,14 +50,14 @@ static_assert(TileRows<3072>::v == 4 && TileRows<4096>::v == 3 && TileRows<9216>
 // Activation vector of the current phase, split so that lane l reads conflict-free
 // float4s: xa[c] = x[8c..8c+3], xb[c] = x[8c+4..8c+7].  The attention phase (which
 // has no activation vector) reuses the space for its per-warp partials.
-struct XVec { float4 xa[KMAX / 8]; float4 xb[KMAX / 8]; };
 struct AttnScratch { float qs[4][DEC_HD]; float wsm[CW][4][PART_LD]; };
-static_assert(NSTAGE <= CW, "one consumer warp per ring stage");
-static_assert(sizeof(AttnScratch) <= sizeof(XVec), "attention scratch must fit in the activation buffer");
+constexpr int GROWS = 16;                   // rows per consumer sync group
+template <int K> struct GroupTiles { static constexpr int v = (K == 9216) ? 8 : 4; };
 
 struct Smem {
     alignas(128) unsigned char ring[NSTAGE][STAGE_BYTES];
-    alignas(16) union { XVec x; AttnScratch at; } u;
+    alignas(16) struct { AttnScratch at; } u;
+    float part[2][GROWS][CW];               // per-warp partial row sums of a sync group (double buffered)
     alignas(8) unsigned long long full[NSTAGE];
     alignas(8) unsigned long long empty[NSTAGE];
     float red[CW];
@@ -253,78 +257,109 @@ __device__ __forceinline__ float2 dot8x2(const uint4 &w, const float4 &a, const 
     return acc;
 }
 
-// ---- consumer: one warp multiplies one whole tile ------------------------------------------
-template <int K, int TR, bool FULL>
-__device__ __forceinline__ void warp_tile(const unsigned char *tile, int n, const XVec &x, float (&acc)[TR], int lane) {
-    constexpr int NCH = K / 256;                                  // 16-byte chunks per lane per row
-    constexpr int NACC = TR >= 4 ? 1 : (TR >= 2 ? 2 : 4);         // packed accumulators per row (ILP)
-    static_assert(NCH % 4 == 0, "");
-    float2 a[TR][NACC];
-    #pragma unroll
-    for (int r = 0; r < TR; r++)
-        #pragma unroll
-        for (int k = 0; k < NACC; k++) a[r][k] = make_float2(0.f, 0.f);
-    const uint4 *wp = reinterpret_cast<const uint4 *>(tile) + lane;
-    #pragma unroll 4
-    for (int ch = 0; ch < NCH; ch++) {
-        const float4 A = x.xa[ch * 32 + lane], B = x.xb[ch * 32 + lane];
-        #pragma unroll
-        for (int r = 0; r < TR; r++) {
-            if (FULL || r < n) {
-                const uint4 wv = wp[r * (K / 8) + ch * 32];
-                a[r][ch % NACC] = dot8x2(wv, A, B, a[r][ch % NACC]);
-            }
-        }
-    }
-    #pragma unroll
-    for (int r = 0; r < TR; r++) {
-        float t = a[r][0].x + a[r][0].y;
-        #pragma unroll
-        for (int k = 1; k < NACC; k++) t += a[r][k].x + a[r][k].y;
-        acc[r] = t;
-    }
-}
-
-// One GEMV phase for the consumers.  Ring stage s is owned by warp s (tile g goes to
-// warp g % NSTAGE): a warp then meets the phases of "its" mbarriers strictly in
-// order, which mbarrier parity waits require (a waiter may be at most one phase
-// ahead).  Warp NSTAGE..CW-1 only help with prologues and attention.  epi(row, v0, v1) is called by one lane per output row (PAIR = false)
-// or per adjacent row pair (PAIR = true).  g0 = global index of the phase's first tile.
+// ---- consumers: every warp owns a K-slice of every row -----------------------------------------
+// Lane l of warp w owns columns (j*256 + w*32 + l)*4 .. +3 (j < K/1024) of every row; its
+// slice of the activation vector stays in registers for the whole phase (no re-reads from
+// shared memory), and all 8 warps work on each tile, so a phase ends within one tile-time
+// of its last byte landing.  Partial row sums are reduced across lanes with a transposed
+// shuffle reduction and across warps through shared memory once per GROUP of tiles
+// (<= 16 rows), not per tile.  epi(row, v0, v1) is called by one lane per output row
+// (PAIR = false) or per adjacent row pair (PAIR = true).  g0 = global index of the phase's first tile.
 template <int K, bool PAIR, typename Epi>
-__device__ __forceinline__ void consume(Smem &sm, unsigned &g0, int R, int unit, int c, int G, unsigned *err,
-                                        long long &t_wait, Epi epi) {
-    constexpr int TR = TileRows<K>::v;
+__device__ __forceinline__ void consume(Smem &sm, unsigned &g0, int &pbuf, int R, int unit, int c, int G,
+                                        const float (&xr)[K / 256], unsigned *err, long long &t_wait, Epi epi) {
+    constexpr int TR = TileRows<K>::v, GT = GroupTiles<K>::v, J = K / 1024;
+    static_assert(GT * TR <= GROWS, "");
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int r0, r1;
     cta_rows(R, unit, c, G, r0, r1);
     const int n_tiles = (r1 - r0 + TR - 1) / TR;
-    const int t0 = (int)(((unsigned)w + NSTAGE - g0 % NSTAGE) % NSTAGE);
-    for (int t = (w < NSTAGE) ? t0 : n_tiles; t < n_tiles; t += NSTAGE) {
-        const int r = r0 + t * TR;
-        const int n = min(TR, r1 - r);
+    // (software-pipelining the tile registers over two buffers was tried: it spills at 168
+    // registers and ran 2.15 ms/step even with setmaxnreg 232, so tiles are fetched in order)
+    uint2 vA[TR * J];
+    auto fetch = [&](int t, uint2 (&vv)[TR * J]) {
         const unsigned g = g0 + (unsigned)t;
-        const unsigned stage = (unsigned)w, ph = (g / NSTAGE) & 1u;
-        {
+        const unsigned stage = g % NSTAGE, ph = (g / NSTAGE) & 1u;
+        if (MK_PROF) {
             const long long tw = clock64();
             mbar_wait(&sm.full[stage], ph, err, g);
             t_wait += clock64() - tw;
-        }
-        float acc[TR];
-        if (n == TR) warp_tile<K, TR, true>(sm.ring[stage], n, sm.u.x, acc, lane);
-        else warp_tile<K, TR, false>(sm.ring[stage], n, sm.u.x, acc, lane);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[stage]);      // stage may be refilled
-        #pragma unroll
-        for (int i = 0; i < TR; i++) acc[i] = warp_sum(acc[i]);   // every lane holds every row sum
-        if (PAIR) {
-            #pragma unroll
-            for (int i = 0; i < TR / 2; i++)
-                if (lane == i && 2 * i < n) epi(r + 2 * i, acc[2 * i], acc[2 * i + 1]);
         } else {
-            #pragma unroll
-            for (int i = 0; i < TR; i++)
-                if (lane == i && i < n) epi(r + i, acc[i], 0.f);
+            mbar_wait(&sm.full[stage], ph, err, g);
         }
+        const int n = min(TR, r1 - (r0 + t * TR));
+        const uint2 *tp = reinterpret_cast<const uint2 *>(sm.ring[stage]) + w * 32 + lane;
+        #pragma unroll
+        for (int r = 0; r < TR; r++)
+            #pragma unroll
+            for (int j = 0; j < J; j++)
+                vv[r * J + j] = (r < n) ? tp[r * (K / 4) + j * 256] : make_uint2(0u, 0u);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);      // release orders the loads above before the refill
+    };
+    auto multiply = [&](const uint2 (&vv)[TR * J], float2 *out) {
+        #pragma unroll
+        for (int r = 0; r < TR; r++) {
+            float2 acc = make_float2(0.f, 0.f);
+            #pragma unroll
+            for (int j = 0; j < J; j++) {
+                const uint2 v = vv[r * J + j];
+                acc = ffma2(make_float2(bf16_lo(v.x), bf16_hi(v.x)), make_float2(xr[4 * j], xr[4 * j + 1]), acc);
+                acc = ffma2(make_float2(bf16_lo(v.y), bf16_hi(v.y)), make_float2(xr[4 * j + 2], xr[4 * j + 3]), acc);
+            }
+            out[r] = acc;                                  // rows beyond the tile were loaded as zeros
+        }
+    };
+    int grp = 0;
+    for (int tg = 0; tg < n_tiles; tg += GT, grp++) {
+        float2 a2[GT * TR];
+        #pragma unroll
+        for (int i = 0; i < GT * TR; i++) a2[i] = make_float2(0.f, 0.f);
+        #pragma unroll
+        for (int ti = 0; ti < GT; ti++) {
+            const int t = tg + ti;
+            if (t < n_tiles) {
+                fetch(t, vA);
+                multiply(vA, &a2[ti * TR]);
+            }
+        }
+        // transposed reduction of up to 16 row sums over the 32 lanes: lane l ends with row (l >> 1)
+        float v[GROWS];
+        #pragma unroll
+        for (int i = 0; i < GROWS; i++) v[i] = (i < GT * TR) ? a2[i < GT * TR ? i : 0].x + a2[i < GT * TR ? i : 0].y : 0.f;
+        #pragma unroll
+        for (int h = GROWS / 2; h >= 1; h >>= 1) {
+            const bool up = (lane & (2 * h)) != 0;
+            #pragma unroll
+            for (int k = 0; k < h; k++) {
+                const float keep = up ? v[k + h] : v[k];
+                const float send = up ? v[k] : v[k + h];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2 * h);
+            }
+        }
+        v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+        if ((lane & 1) == 0) sm.part[pbuf][lane >> 1][w] = v[0];
+        consumer_sync();
+        const int rbase = r0 + tg * TR;
+        const int rows = min(r1 - rbase, GT * TR);
+        if (w == (grp & (CW - 1))) {                        // epilogue duty rotates over the warps
+            if (PAIR) {
+                if (lane < (rows >> 1)) {
+                    float v0 = 0.f, v1 = 0.f;
+                    #pragma unroll
+                    for (int k = 0; k < CW; k++) { v0 += sm.part[pbuf][2 * lane][k]; v1 += sm.part[pbuf][2 * lane + 1][k]; }
+                    epi(rbase + 2 * lane, v0, v1);
+                }
+            } else {
+                if (lane < rows) {
+                    float v0 = 0.f;
+                    #pragma unroll
+                    for (int k = 0; k < CW; k++) v0 += sm.part[pbuf][lane][k];
+                    epi(rbase + lane, v0, 0.f);
+                }
+            }
+        }
+        pbuf ^= 1;
     }
     g0 += (unsigned)n_tiles;
 }
@@ -475,18 +510,6 @@ __device__ __forceinline__ float load_slice(const float *v, int col0, float (&xr
     return ss;
 }
 
-// publish this thread's slice (columns (j*256 + tid)*4 .. +3) into the split smem layout
-template <int K>
-__device__ __forceinline__ void store_slice(Smem &sm, const float (&xr)[K / 256]) {
-    #pragma unroll
-    for (int j = 0; j < K / 1024; j++) {
-        const int g = j * 256 + (int)threadIdx.x;          // 4-column group
-        const float4 v = make_float4(xr[4 * j], xr[4 * j + 1], xr[4 * j + 2], xr[4 * j + 3]);
-        if (g & 1) sm.u.x.xb[g >> 1] = v; else sm.u.x.xa[g >> 1] = v;
-    }
-    consumer_sync();
-}
-
 // RMSNorm of the slice (voxtral_kernels.c:475-492), optional (1 + ada) (voxtral_decoder.c:742-745).
 // The norm weights are fetched before the block reduction so their latency overlaps it.
 __device__ __forceinline__ void norm_slice(Smem &sm, float (&xr)[DEC_DIM / 256], float ss, const float *nw,
@@ -518,7 +541,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
 
     if (tid == 0) {
         sm.issued = 0;
-        for (int i = 0; i < NSTAGE; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }  // one warp consumes a tile
+        for (int i = 0; i < NSTAGE; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], CW); }  // every consumer warp releases a stage
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -560,6 +583,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     // =============================== CONSUMERS ===============================
     const int w = tid >> 5, lane = tid & 31;
     unsigned gt = 0;                              // global index of the next phase's first tile
+    int pbuf = 0;
     unsigned bar_target = P.bar_base;
     long long t_wait = 0, t_grid = 0, t_attn = 0, t_pro = 0, t_own = 0, t_atom = 0;
     const long long t_start = clock64();
@@ -624,9 +648,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                     ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 }
                 norm_slice(sm, xr, ss, L.attn_norm, nullptr, col0);
-                store_slice<DEC_DIM>(sm, xr);
                 t_pro += clock64() - tp;
-                consume<DEC_DIM, true>(sm, gt, DEC_QKV, 2, c, G, P.err, t_wait,
+                consume<DEC_DIM, true>(sm, gt, pbuf, DEC_QKV, 2, c, G, xr, P.err, t_wait,
                     [&](int row, float v0, float v1) {
                         if (row < DEC_QDIM + DEC_KVDIM) {
                             const int d = (row & (DEC_HD - 1)) >> 1;
@@ -696,9 +719,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                     xr[4 * j] = nj[j].x * inv; xr[4 * j + 1] = nj[j].y * inv;
                     xr[4 * j + 2] = nj[j].z * inv; xr[4 * j + 3] = nj[j].w * inv;
                 }
-                store_slice<DEC_QDIM>(sm, xr);           // (its barrier also publishes sm.resid)
                 t_pro += clock64() - tp;
-                consume<DEC_QDIM, false>(sm, gt, DEC_DIM, 1, c, G, P.err, t_wait,
+                consume<DEC_QDIM, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait,
                     [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
             }
             MK_GRID_SYNC();
@@ -708,9 +730,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 float xr[DEC_DIM / 256];
                 const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
-                store_slice<DEC_DIM>(sm, xr);
                 t_pro += clock64() - tp;
-                consume<DEC_DIM, true>(sm, gt, 2 * DEC_HIDDEN, 2, c, G, P.err, t_wait,
+                consume<DEC_DIM, true>(sm, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, xr, P.err, t_wait,
                     [&](int row, float v0, float v1) { P.h[row >> 1] = silu(v0) * v1; });
             }
             MK_GRID_SYNC();
@@ -720,9 +741,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_HIDDEN / 256];
                 (void)load_slice<DEC_HIDDEN>(P.h, col0, xr);
-                store_slice<DEC_HIDDEN>(sm, xr);
                 t_pro += clock64() - tp;
-                consume<DEC_HIDDEN, false>(sm, gt, DEC_DIM, 1, c, G, P.err, t_wait,
+                consume<DEC_HIDDEN, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait,
                     [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
             }
             MK_GRID_SYNC();
@@ -733,11 +753,10 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             float xr[DEC_DIM / 256];
             const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
             norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
-            store_slice<DEC_DIM>(sm, xr);
             t_pro += clock64() - tp;
             float bv = -INFINITY;
             int bi = 0x7fffffff;
-            consume<DEC_DIM, false>(sm, gt, VOCAB, 1, c, G, P.err, t_wait,
+            consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
                 [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); });
             // epilogue lanes of every warp hold candidates: block-wide merge
             #pragma unroll
