@@ -68,3 +68,23 @@ def test_no_cpu_fallback_without_gpu():
     out = np.zeros(128, np.float32)
     assert L.vox_cuda_mel_frames(vc.fptr(x), 1, vc.fptr(out)) < 0
     assert not L.vox_cuda_model_create(C.byref(vc.Weights()))
+
+
+def test_product_does_not_import_oracle():
+    """oracle/ is test infrastructure: nothing in the shipped package may reference it, and the
+    shared library must not link anything from oracle/_ref."""
+    import subprocess
+    pkg = os.path.join(ROOT, "voxtral.c_b200")
+    bad = []
+    for dirpath, _, files in os.walk(pkg):
+        if os.sep + "build" in dirpath:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".c", ".cpp")) or f == "Makefile":
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                if re.search(r"vox_oracle|oracle/|libvoxref|refshim_", src):
+                    bad.append(os.path.join(dirpath, f))
+    assert not bad, bad
+    so = os.path.join(pkg, "libvoxcuda.so")
+    needed = subprocess.run(["readelf", "-d", so], capture_output=True, text=True).stdout
+    assert "voxref" not in needed and "openblas" not in needed

@@ -1,7 +1,7 @@
 """ctypes binding of include/vox_cuda.h (libvoxcuda.so).
 
 Plumbing only: every call goes straight to the C ABI.  Importing this module
-never touches oracle/; it raises if the CUDA library is missing (there is no
+never touches the test oracle; it raises if the CUDA library is missing (there is no
 CPU fallback in the product path).
 """
 import ctypes as C
