@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvoxcuda.so")
+LIB_PATH = os.environ.get("VOX_CUDA_LIB") or os.path.join(HERE, "libvoxcuda.so")
 
 ENC_LAYERS, DEC_LAYERS = 32, 26
 ENC_DIM, DEC_DIM, VOCAB, MEL_BINS = 1280, 3072, 131072, 128
