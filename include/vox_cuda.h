@@ -114,6 +114,16 @@ int  vox_cuda_decoder_position(const vox_cuda_state_t *s);
  * wrap: lets a harness start right before a compaction boundary the way the
  * reference allows through its public ctx fields, voxtral.h:197-205). */
 int  vox_cuda_decoder_set_position(vox_cuda_state_t *s, int logical_pos, int n_valid);
+/* Copy n rows [n,1024] of fp32 K and V of one decoder layer between the host and
+ * the device ring, addressed by LOGICAL position (slot = pos & 8191); pos + n may
+ * cross the ring end.  The host layout is the reference's kv_cache_k/v row layout
+ * (voxtral_decoder.c:188-196), so a harness - or a host that switches a running
+ * stream from the CPU path to the GPU - can move ctx->kv_cache_k + (layer *
+ * kv_cache_max + physical) * 1024 straight across (voxtral.h:197-205). */
+int  vox_cuda_decoder_kv_write(vox_cuda_state_t *s, int layer, int logical_pos, int n,
+                               const float *k, const float *v);
+int  vox_cuda_decoder_kv_read(vox_cuda_state_t *s, int layer, int logical_pos, int n,
+                              float *k, float *v);
 
 /* ---- decoder (hot path #1) -------------------------------------------- */
 /* vox_decoder_prefill / vox_metal_decoder_prefill_step

@@ -142,6 +142,18 @@ class Ref:
         row = np.ctypeslib.as_array(p, shape=(131072, 3072))[token]
         return (row.astype(np.uint32) << 16).view(np.float32)
 
+    def kv_views(self):
+        """numpy views [26, kv_cache_max, 1024] of the reference's fp32 K and V caches
+        (voxtral.h:197-205; allocated by the first prefill, voxtral_decoder.c:457-462)."""
+        kmax = self.get("kv_cache_max")
+        self.L.refshim_kv_k.restype = f32p
+        self.L.refshim_kv_v.restype = f32p
+        self.L.refshim_kv_k.argtypes = [C.c_void_p]
+        self.L.refshim_kv_v.argtypes = [C.c_void_p]
+        k = np.ctypeslib.as_array(self.L.refshim_kv_k(self.ctx), shape=(26, kmax, 1024))
+        v = np.ctypeslib.as_array(self.L.refshim_kv_v(self.ctx), shape=(26, kmax, 1024))
+        return k, v
+
     def fill_weights(self, w):
         self.L.refshim_fill_weights(self.ctx, C.byref(w))
 

@@ -109,6 +109,33 @@ extern "C" int vox_cuda_decoder_set_position(vox_cuda_state_t *s, int logical_po
     return push_params(s);
 }
 
+// ---- KV ring <-> host (logical addressing) ------------------------------------------
+static int kv_copy(vox_cuda_state *s, int layer, int logical_pos, int n, float *k, float *v, bool to_device) {
+    if (!s || layer < 0 || layer >= s->m->n_dec || logical_pos < 0 || n < 0 || n > DEC_WINDOW || (!k && !v)) return -1;
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    const size_t layer_off = (size_t)layer * DEC_WINDOW * DEC_KVDIM;
+    int done = 0;
+    while (done < n) {
+        const int slot = (logical_pos + done) & (DEC_WINDOW - 1);
+        const int run = (n - done < DEC_WINDOW - slot) ? n - done : DEC_WINDOW - slot;   // up to the ring end
+        const size_t bytes = (size_t)run * DEC_KVDIM * sizeof(float);
+        const size_t doff = layer_off + (size_t)slot * DEC_KVDIM, hoff = (size_t)done * DEC_KVDIM;
+        if (k) CUDA_TRY(to_device ? cudaMemcpy(s->kv_k + doff, k + hoff, bytes, cudaMemcpyHostToDevice)
+                                  : cudaMemcpy(k + hoff, s->kv_k + doff, bytes, cudaMemcpyDeviceToHost));
+        if (v) CUDA_TRY(to_device ? cudaMemcpy(s->kv_v + doff, v + hoff, bytes, cudaMemcpyHostToDevice)
+                                  : cudaMemcpy(v + hoff, s->kv_v + doff, bytes, cudaMemcpyDeviceToHost));
+        done += run;
+    }
+    return 0;
+}
+extern "C" int vox_cuda_decoder_kv_write(vox_cuda_state_t *s, int layer, int logical_pos, int n,
+                                         const float *k, const float *v) {
+    return kv_copy(s, layer, logical_pos, n, const_cast<float *>(k), const_cast<float *>(v), true);
+}
+extern "C" int vox_cuda_decoder_kv_read(vox_cuda_state_t *s, int layer, int logical_pos, int n, float *k, float *v) {
+    return kv_copy(s, layer, logical_pos, n, k, v, false);
+}
+
 // ---- one step ----------------------------------------------------------------
 static int ensure_graph(vox_cuda_state *s) {
     if (s->graph_ready) return 0;

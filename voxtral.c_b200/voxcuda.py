@@ -58,6 +58,8 @@ SIGNATURES = {
     "vox_cuda_state_reset_encoder": (None, [C.c_void_p]),
     "vox_cuda_decoder_position": (C.c_int, [C.c_void_p]),
     "vox_cuda_decoder_set_position": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "vox_cuda_decoder_kv_write": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, f32p, f32p]),
+    "vox_cuda_decoder_kv_read": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, f32p, f32p]),
     "vox_cuda_decoder_prefill": (C.c_int, [C.c_void_p, f32p, C.c_int]),
     "vox_cuda_decoder_step": (C.c_int, [C.c_void_p, f32p, f32p]),
     "vox_cuda_decoder_step_fused": (C.c_int, [C.c_void_p, C.c_int, C.c_int, f32p]),
