@@ -47,6 +47,8 @@ if L.vox_cuda_debug_mega_barriers(st, buf, C.byref(g)) == 0:
     a = np.array(buf[:g.value * 24], dtype=np.int64).reshape(g.value, 12, 2)
     names = ["qkv", "attn", "wo", "w13", "w2"]
     t0 = a[:, 0, 0].min()
+    if os.environ.get("DEC_PROBE_DUMP"):
+        np.save(os.environ["DEC_PROBE_DUMP"], a)          # [cta, barrier, (arrive, exit)] ns, for offline analysis
     for k in range(12):
         arr, ex = a[:, k, 0], a[:, k, 1]
         print(f"barrier {k:2d} after {names[k % 5]:4s}: first arrive {arr.min() - t0:7d} ns, last arrive {arr.max() - t0:7d} "
