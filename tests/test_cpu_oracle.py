@@ -135,3 +135,15 @@ def test_decoder_kv_compaction_keeps_window_and_positions():
     assert dec.pos_offset == 38 + 1024 and dec.cache_len == 8193
     assert np.array_equal(dec.k[0][:8192], k_tail)
     assert np.isfinite(logits).all() and 0 <= tok < 131072
+
+
+def test_fill_alts_rules():
+    """stream_fill_alts (voxtral.c:955-1010): control ids < 1000 never appear, the best token is
+    skipped, order is by probability, the cutoff is on 1 - p_i / p_best."""
+    lg = np.full(131072, -5.0, np.float32)
+    lg[7] = 9.0                      # control token with the highest logit: never an alternative
+    lg[5000], lg[6000], lg[7000], lg[8000] = 4.0, 3.9, 3.0, 1.0
+    assert vo.fill_alts(lg, 5000, 4, 1.0) == [6000, 7000, 8000]
+    assert vo.fill_alts(lg, 5000, 3, 1.0) == [6000, 7000]
+    assert vo.fill_alts(lg, 5000, 4, 0.2) == [6000]          # 1 - e^-0.1 = 0.095 kept, 1 - e^-1 = 0.63 cut
+    assert vo.fill_alts(lg, 5000, 1, 1.0) == [] and vo.fill_alts(lg, 5000, 4, 0.0) == []

@@ -183,3 +183,27 @@ def test_full_size_properties_60s(full_env):
         assert d < 2e-3
     finally:
         e.L.vox_cuda_state_free(st)
+
+
+def test_alternatives_match_oracle(full_env):
+    """--alt (stream_fill_alts, voxtral.c:955-1010): ids >= 1000, by probability, cut by 1 - p_i/p_best."""
+    import vox_oracle as vo
+    e = full_env
+    rng = np.random.default_rng(17)
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        emb = (0.5 * rng.standard_normal((38, 3072))).astype(np.float32)
+        assert e.L.vox_cuda_decoder_prefill(st, e.vc.fptr(emb), 38) == 0
+        logits = np.empty(131072, np.float32)
+        ids = np.empty(8, np.int32)
+        for step in range(3):
+            x = (0.5 * rng.standard_normal(3072)).astype(np.float32)
+            tok = e.L.vox_cuda_decoder_step(st, e.vc.fptr(x), e.vc.fptr(logits))
+            assert tok == int(np.argmax(logits))
+            for n_alt, cutoff in ((4, 1.0), (4, 0.5), (3, 0.2), (2, 0.05), (1, 1.0), (4, 0.0)):
+                n = e.L.vox_cuda_decoder_alternatives(st, n_alt, C.c_float(cutoff), e.vc.iptr(ids))
+                want = vo.fill_alts(logits, tok, n_alt, cutoff)
+                assert ids[:n].tolist() == want, (step, n_alt, cutoff, ids[:n].tolist(), want)
+    finally:
+        e.L.vox_cuda_state_free(st)
