@@ -81,6 +81,7 @@ typedef struct {
 
 typedef struct vox_cuda_model vox_cuda_model_t;   /* weights in HBM, shared by streams */
 typedef struct vox_cuda_state vox_cuda_state_t;   /* one stream's device state */
+typedef struct vox_cuda_group vox_cuda_group_t;   /* B streams decoded in lock step (one weight pass per step) */
 
 /* ---- lifetime (replaces vox_metal_init/available/shutdown,
  *      voxtral_metal.h:20-26, call sites main.c:181-183,407-409) ---------- */
@@ -205,6 +206,39 @@ void  vox_cuda_host_free(void *p);
 int   vox_cuda_pcm_upload(vox_cuda_state_t *s, const float *pcm, int n_samples);
 int   vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, int n_frames,
                           int prompt_len, int *tokens_out, int max_tokens, float *device_ms);
+
+/* ---- stream groups: B independent streams, one pass over the weights per step ----------------
+ * The reference holds one stream per vox_ctx_t (voxtral.h:188-239, voxtral.c:1242-1286) and
+ * vox_decoder_forward (voxtral_decoder.c:640-780) reads all 6.86 GB of decoder weights for each
+ * token of each stream.  A group keeps the adapter rows and K/V rings of n_streams (<= 128)
+ * streams on the device and advances all of them by one token per step, so the weights cross HBM
+ * once per step for every stream.  Per-stream arithmetic is that of vox_decoder_prefill /
+ * vox_decoder_forward on the stream's own rows: the greedy ids of stream i equal a single-stream
+ * run on the same audio.  max_positions bounds the adapter tokens of one stream (its K/V ring
+ * holds min(8192, next power of two) rows, 212,992 B per position).
+ *   vox_cuda_group_encode      whole-clip front end of one stream (same pcm / n_frames contract as
+ *                              vox_cuda_transcribe); returns its adapter-token count
+ *   vox_cuda_group_set_adapter adapter rows computed elsewhere (host fp32 [n,3072])
+ *   vox_cuda_group_decode      prompt prefill (prompt_len = 39) of every encoded stream, then
+ *                              lock-step greedy decode of all remaining positions; tokens_out is
+ *                              [n_streams][max_tokens], counts_out[i] = ids written for stream i
+ *                              (the caller truncates at EOS = 2); returns the number of steps */
+vox_cuda_group_t *vox_cuda_group_create(vox_cuda_model_t *m, int n_streams, int max_positions);
+void vox_cuda_group_free(vox_cuda_group_t *g);
+int  vox_cuda_group_streams(const vox_cuda_group_t *g);
+int  vox_cuda_group_encode(vox_cuda_group_t *g, int stream, const float *pcm, int n_samples, int n_frames);
+int  vox_cuda_group_set_adapter(vox_cuda_group_t *g, int stream, const float *rows, int n);
+int  vox_cuda_group_decode(vox_cuda_group_t *g, int prompt_len, int *tokens_out, int max_tokens,
+                           int *counts_out, float *device_ms);
+
+/* The group's matrix product alone, host buffers (parity tests of the kernel): C[b][n] =
+ * sum_k A[b][k] W[n][k] for B <= 128 activation rows at once - vox_linear_nobias_bf16
+ * (voxtral_kernels.c:215-236) for B streams in one pass over W.  A is split into two bf16 terms on
+ * the device (fp32-class accuracy), products accumulate in fp32 in TMEM; the K range is cut into
+ * ksplit parts summed in order.  swiglu != 0: rows (2i, 2i+1) of W are (gate, up) and C is
+ * [B, N/2] = silu(g) * u (needs ksplit 1).  N % 128 == 0, K % 64 == 0.  0 on success. */
+int vox_cuda_gemm_bf16_streams(int B, int N, int K, const float *A, const uint16_t *W_bf16, int ksplit,
+                               int swiglu, float *C);
 
 /* ---- op-level hook (replaces vox_metal_sgemm_bf16, voxtral_metal.h:38,
  *      call sites voxtral_kernels.c:199-204,218-229,249-254) -------------- */

@@ -62,9 +62,8 @@ extern "C" int vox_cuda_pcm_upload(vox_cuda_state_t *s, const float *pcm, int n_
     return 0;
 }
 
-extern "C" int vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, int n_frames,
-                                   int prompt_len, int *tokens_out, int max_tokens, float *device_ms) {
-    if (!s || !tokens_out || n_frames <= 0 || prompt_len < 2 || prompt_len > 128) return -1;
+// front half of the whole-clip call: PCM (host, or resident when pcm == NULL) -> adapter rows on the device
+int batch_encode_clip(vox_cuda_state *s, const float *pcm, int n_samples, int n_frames) {
     BatchBuf *b = bb_get(s);
     EncState *e = (EncState *)s->enc_priv;
     cudaStream_t st = s->stream;
@@ -75,7 +74,6 @@ extern "C" int vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_
         if (!b->d_pcm || b->pcm_n < (n_frames - 1) * 160 + 400) { vox_set_error("transcribe: no resident PCM (vox_cuda_pcm_upload)"); return -1; }
         if (bb_reserve(b, 0, (size_t)n_frames)) return -1;
     }
-    CUDA_TRY(cudaEventRecord(s->ev0, st));
     if (pcm) CUDA_TRY(cudaMemcpyAsync(b->d_pcm, pcm, (size_t)n_samples * 4, cudaMemcpyHostToDevice, st));
     if (mel_frames_device(st, b->d_pcm, n_frames, b->d_mel, VOX_CUDA_MEL_BINS)) return -1;
     vox_cuda_state_reset_encoder(s);
@@ -86,6 +84,15 @@ extern "C" int vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_
                                  (size_t)n * VOX_CUDA_MEL_BINS * 4, cudaMemcpyDeviceToDevice, st));
         if (encode_chunk_device_mel(s, n)) return -1;
     }
+    return 0;
+}
+
+extern "C" int vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, int n_frames,
+                                   int prompt_len, int *tokens_out, int max_tokens, float *device_ms) {
+    if (!s || !tokens_out || n_frames <= 0 || prompt_len < 2 || prompt_len > 128) return -1;
+    cudaStream_t st = s->stream;
+    CUDA_TRY(cudaEventRecord(s->ev0, st));
+    if (batch_encode_clip(s, pcm, n_samples, n_frames)) return -1;
     const int T = s->adapter_count;
     const int n_pre = prompt_len - 1;            // rows fed to prefill; row n_pre produces the first token
     if (T < prompt_len) { vox_set_error("transcribe: only %d adapter tokens (< prompt %d)", T, prompt_len); return -1; }

@@ -322,8 +322,12 @@ static TcEpilogue pf_epi(float *of, long ldf, uint16_t *ob, long ldb, int flags,
     return t;
 }
 
-// x_dev: [seq_len, 3072] device, consumed (used as the residual stream).
-static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
+// x_dev: [seq_len, 3072] device, consumed (used as the residual stream).  K/V rows go to the ring
+// kbase/vbase ([n_dec] layers kv_layer floats apart, slot = logical position & mask); *pos / *n_valid
+// are the logical position of the first row and the valid entries before it, advanced on return.
+// Enqueues only (no synchronisation); scratch is the state's prefill buffer.
+int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase, float *vbase, size_t kv_layer,
+                     int mask, int *pos, int *n_valid) {
     if (ensure_pf(s)) return -1;
     vox_cuda_model *m = s->m;
     cudaStream_t st = s->stream;
@@ -337,15 +341,14 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
     uint16_t *att_b = (uint16_t *)gu;     // [PF_ROWS][2*4096]   (gu is unused in this mode)
     uint16_t *hh_b = (uint16_t *)hh;      // [PF_ROWS][2*9216]
     const bool tcm = !prefill_f32_mode();
-    const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
     for (int r0 = 0; r0 < seq_len; r0 += PF_ROWS) {
         const int M = seq_len - r0 < PF_ROWS ? seq_len - r0 : PF_ROWS;
         float *x = x_dev + (size_t)r0 * DEC_DIM;
-        const int pos0 = s->h_params.pos;
-        const int first_valid = pos0 - s->h_params.n_valid;
+        const int pos0 = *pos;
+        const int first_valid = pos0 - *n_valid;
         for (int l = 0; l < m->n_dec; l++) {
             const DecLayerDev &L = m->dec[l];
-            float *kc = s->kv_k + l * kv_layer, *vc = s->kv_v + l * kv_layer;
+            float *kc = kbase + l * kv_layer, *vc = vbase + l * kv_layer;
             const float *ada = m->ada_scale + (size_t)l * DEC_DIM;
             if (tcm) {
                 if (rows_rmsnorm_bf16(st, x, DEC_DIM, L.attn_norm, nullptr, xn_b, 2 * DEC_DIM, M, DEC_DIM, 1)) return -1;
@@ -356,8 +359,8 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
                 if (sgemm_bf16w(st, M, DEC_QKV, DEC_DIM, xn, DEC_DIM, L.wqkv, qkv, DEC_QKV, nullptr, EPI_NONE)) return -1;
             }
             if (rows_rope_kv(st, qkv, M, DEC_QDIM, DEC_KVDIM, DEC_HD, m->inv_freq_dec, pos0,
-                             DEC_WINDOW - 1, kc, vc)) return -1;
-            if (rows_attention(st, DEC_HD, qkv, DEC_QKV, kc, vc, DEC_KVDIM, DEC_WINDOW - 1, DEC_HEADS,
+                             mask, kc, vc)) return -1;
+            if (rows_attention(st, DEC_HD, qkv, DEC_QKV, kc, vc, DEC_KVDIM, mask, DEC_HEADS,
                                DEC_HEADS / DEC_KVH, M, pos0, first_valid, DEC_WINDOW, att, DEC_QDIM)) return -1;
             if (tcm) {
                 if (f32_to_bf16_rows(st, att, DEC_QDIM, att_b, 2 * DEC_QDIM, M, DEC_QDIM, 1)) return -1;
@@ -376,11 +379,17 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
                 if (sgemm_bf16w(st, M, DEC_DIM, DEC_HIDDEN, hh, DEC_HIDDEN, L.w2, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
             }
         }
-        s->h_params.pos += M;
-        s->h_params.n_valid = s->h_params.n_valid + M > DEC_WINDOW ? DEC_WINDOW : s->h_params.n_valid + M;
+        *pos += M;
+        *n_valid = *n_valid + M > DEC_WINDOW ? DEC_WINDOW : *n_valid + M;
     }
+    return 0;
+}
+
+static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
+    if (dec_prefill_into(s, x_dev, seq_len, s->kv_k, s->kv_v, (size_t)DEC_WINDOW * DEC_KVDIM, DEC_WINDOW - 1,
+                         &s->h_params.pos, &s->h_params.n_valid)) return -1;
     if (push_params(s)) return -1;
-    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
     return 0;
 }
 

@@ -100,6 +100,12 @@ void dec_mega_free(vox_cuda_state *s);
 int dec_mega_launch(vox_cuda_state *s, int n_steps);
 int dec_mega_attn_part_floats(void);
 
+// api_dec.cu: prompt prefill into an arbitrary K/V ring (used by the state itself and by stream groups)
+int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase, float *vbase, size_t kv_layer,
+                     int mask, int *pos, int *n_valid);
+// api_batch.cu: PCM -> mel -> conv stem -> encoder -> adapter rows in s->adapter_buf (resets the state)
+int batch_encode_clip(vox_cuda_state *s, const float *pcm, int n_samples, int n_frames);
+
 // dec_kernels.cu
 int dec_launch_step(vox_cuda_state *s, cudaStream_t st);
 int dec_prefill(vox_cuda_state *s, const float *d_x_in, int seq_len);

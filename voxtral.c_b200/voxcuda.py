@@ -67,6 +67,13 @@ SIGNATURES = {
     "vox_cuda_decoder_read_logits": (C.c_int, [C.c_void_p, f32p]),
     "vox_cuda_decoder_prefill_fused": (C.c_int, [C.c_void_p, i32p, C.c_int, C.c_int]),
     "vox_cuda_decoder_alternatives": (C.c_int, [C.c_void_p, C.c_int, C.c_float, i32p]),
+    "vox_cuda_gemm_bf16_streams": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, C.c_int, C.c_int, f32p]),
+    "vox_cuda_group_create": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
+    "vox_cuda_group_free": (None, [C.c_void_p]),
+    "vox_cuda_group_streams": (C.c_int, [C.c_void_p]),
+    "vox_cuda_group_encode": (C.c_int, [C.c_void_p, C.c_int, f32p, C.c_int, C.c_int]),
+    "vox_cuda_group_set_adapter": (C.c_int, [C.c_void_p, C.c_int, f32p, C.c_int]),
+    "vox_cuda_group_decode": (C.c_int, [C.c_void_p, C.c_int, i32p, C.c_int, i32p, f32p]),
     "vox_cuda_encoder_step": (C.c_int, [C.c_void_p, f32p, C.c_int]),
     "vox_cuda_conv_stem": (C.c_int, [C.c_void_p, f32p, C.c_int, f32p, i32p]),
     "vox_cuda_adapter": (C.c_int, [C.c_void_p, f32p, C.c_int, f32p]),
