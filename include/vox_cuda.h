@@ -240,6 +240,10 @@ int  vox_cuda_group_decode(vox_cuda_group_t *g, int prompt_len, int *tokens_out,
 int vox_cuda_gemm_bf16_streams(int B, int N, int K, const float *A, const uint16_t *W_bf16, int ksplit,
                                int swiglu, float *C);
 
+/* Device-resident timing of that product alone (weights rotate over > 400 MB of copies so no launch
+ * finds its matrix in L2): mean microseconds per launch over iters launches, < 0 on error. */
+float vox_cuda_bench_gemm_streams(int B, int N, int K, int ksplit, int swiglu, int iters);
+
 /* ---- op-level hook (replaces vox_metal_sgemm_bf16, voxtral_metal.h:38,
  *      call sites voxtral_kernels.c:199-204,218-229,249-254) -------------- */
 /* C[M,N] = A[M,K] (f32 host) x B[N,K]^T.  B_bf16 is a host pointer: if it is

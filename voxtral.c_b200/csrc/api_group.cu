@@ -21,6 +21,7 @@
 // position / previous token on the device, so a whole clip decodes without a host round trip.
 #include "vox_internal.h"
 #include "gemm_wt.h"
+#include "tc_ptx.cuh"
 #include <string.h>
 #include <stdlib.h>
 #include <math.h>
@@ -48,6 +49,8 @@ __global__ void __launch_bounds__(256) group_norm_kernel(
     const int b = blockIdx.x, tid = threadIdx.x;
     float *xr = x + (size_t)b * DEC_DIM;
     float v[12];
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     if (mode == 0) {
         const Slot sl = slots[b];
         const float *a = adapter + (size_t)b * adapter_stride + (size_t)sl.aidx * DEC_DIM;
@@ -119,6 +122,8 @@ __global__ void __launch_bounds__(256, 2) group_attn_kernel(
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     __shared__ __align__(16) float qs[4][DEC_HD];
     __shared__ __align__(16) float wsm[AT_WARPS][4][DEC_HD + 4];
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     const int pos = slots[b].pos;
     float *kc = kv_k + (size_t)b * stream_stride, *vc = kv_v + (size_t)b * stream_stride;
     const size_t slot_new = (size_t)(pos & ring_mask) * DEC_KVDIM + (size_t)kvh * DEC_HD;
@@ -249,6 +254,8 @@ __global__ void __launch_bounds__(256, 2) group_attn_kernel(
 __global__ void __launch_bounds__(1024) group_argmax_kernel(const float *__restrict__ logits, Slot *__restrict__ slots,
                                                             int *__restrict__ tokens, int step, int n_streams) {
     const int b = blockIdx.x, tid = threadIdx.x;
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     const float4 *row = reinterpret_cast<const float4 *>(logits + (size_t)b * VOCAB);
     float best = -INFINITY; int bi = 0x7fffffff;
     for (int i = tid; i < VOCAB / 4; i += 1024) {        // ascending indices per thread: strict > keeps the first
@@ -414,31 +421,29 @@ static int group_step(vox_cuda_group *g, int step) {
     for (int l = 0; l < m->n_dec; l++) {
         const DecLayerDev &L = m->dec[l];
         if (l == 0)
-            group_norm_kernel<<<B, 256, 0, st>>>(g->x, 0, nullptr, 0, 0, g->adapter, astride, m->tok_emb, g->d_slots,
-                                                 L.attn_norm, nullptr, g->xn_b);
+            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 0, nullptr, 0, 0L, g->adapter, astride, m->tok_emb, g->d_slots,
+                                L.attn_norm, nullptr, g->xn_b));
         else
-            group_norm_kernel<<<B, 256, 0, st>>>(g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0, nullptr, g->d_slots,
-                                                 L.attn_norm, nullptr, g->xn_b);
+            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+                                L.attn_norm, nullptr, g->xn_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_qkv[l])) return -1;
-        group_attn_kernel<<<dim3(B, DEC_KVH), 256, 0, st>>>(g->part, KS_QKV, (long)B * DEC_QKV, g->d_slots, m->inv_freq_dec,
-                                                            g->kv_k + l * g->kv_layer, g->kv_v + l * g->kv_layer, g->kv_stream,
-                                                            g->mask, g->att_b);
+        CUDA_TRY(launch_pdl(group_attn_kernel, dim3(B, DEC_KVH), 256, 0, st, g->part, KS_QKV, (long)B * DEC_QKV, g->d_slots,
+                            m->inv_freq_dec, g->kv_k + l * g->kv_layer, g->kv_v + l * g->kv_layer, g->kv_stream, g->mask, g->att_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_wo[l])) return -1;
-        group_norm_kernel<<<B, 256, 0, st>>>(g->x, 1, g->part, KS_WO, (long)B * DEC_DIM, nullptr, 0, nullptr, g->d_slots,
-                                             L.ffn_norm, m->ada_scale + (size_t)l * DEC_DIM, g->xn_b);
+        CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_WO, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+                            L.ffn_norm, m->ada_scale + (size_t)l * DEC_DIM, g->xn_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_w13[l])) return -1;
         if (gemm_wt_launch(st, &g->op_w2[l])) return -1;
     }
-    group_norm_kernel<<<B, 256, 0, st>>>(g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0, nullptr, g->d_slots,
-                                         m->dec_norm, nullptr, g->xn_b);
+    CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+                        m->dec_norm, nullptr, g->xn_b));
     LAUNCHED();
     if (gemm_wt_launch(st, &g->op_logits)) return -1;
-    group_argmax_kernel<<<B, 1024, 0, st>>>(g->logits, g->d_slots, g->d_tokens, step, B);
+    CUDA_TRY(launch_pdl(group_argmax_kernel, B, 1024, 0, st, g->logits, g->d_slots, g->d_tokens, step, B));
     LAUNCHED();
-    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 

@@ -31,6 +31,11 @@ using namespace tcx;
 constexpr int BMW = 128, BK = 64, ACC = 2, NT = 192;
 constexpr int A_BYTES = BMW * BK * 2;                       // 16 KB of weights per stage
 
+__device__ __forceinline__ void bulk_1d(void *dst, const void *src, unsigned bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(s32(dst)), "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+}
+
 template <int NB> struct Cfg {
     static constexpr int B_BYTES = NB * BK * 2;             // one activation half (hi or lo)
     static constexpr int STAGE = A_BYTES + 2 * B_BYTES;
@@ -41,6 +46,7 @@ template <int NB> struct Cfg {
 
 struct KParams {
     int n_tiles, nkb, ksplit, B, split, mode;
+    const uint8_t *wt, *at;                                 // tiled operands (see gemm_wt.h); null: tensor maps
     float *out_f32; long ldo; long split_stride;            // mode 0: out_f32[s*split_stride + b*ldo + n]
     uint16_t *out_bf16; long ldb; long lo_off;              // mode 1: rows (2i, 2i+1) = (gate, up)
 };
@@ -75,20 +81,46 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
     const int total = p.n_tiles * p.ksplit;
     const int Kw = p.nkb * BK;                              // activation lo half starts at column Kw
 
+    pdl_launch_dependents();                                // the next kernel may start its own prologue
     if (warp == 0) {
         if (lane == 0) {
             int s = 0; unsigned ph = 0;
             const unsigned tx = A_BYTES + (p.split ? 2 : 1) * C::B_BYTES;
+            // Weights do not depend on the previous kernel: the first ring of weight tiles is requested
+            // before the dependency wait, so HBM keeps streaming across the kernel boundary.
+            int pre = 0;
+            if (blockIdx.x < total) {
+                const int tile = blockIdx.x / p.ksplit, sp = blockIdx.x % p.ksplit;
+                const int kb0 = (int)((long)sp * p.nkb / p.ksplit), kb1 = (int)((long)(sp + 1) * p.nkb / p.ksplit);
+                pre = min(C::STAGES, kb1 - kb0);
+                for (int i = 0; i < pre; i++) {
+                    uint8_t *st = base + i * C::STAGE;
+                    mb_expect_tx(&full[i], tx);
+                    if (p.wt) bulk_1d(st, p.wt + ((size_t)tile * p.nkb + kb0 + i) * A_BYTES, A_BYTES, &full[i]);
+                    else tma_2d(st, &tmW, (kb0 + i) * BK, tile * BMW, &full[i]);
+                }
+            }
+            pdl_wait();
             for (int it = blockIdx.x; it < total; it += gridDim.x) {
                 const int tile = it / p.ksplit, sp = it % p.ksplit;
                 const int kb0 = (int)((long)sp * p.nkb / p.ksplit), kb1 = (int)((long)(sp + 1) * p.nkb / p.ksplit);
                 for (int kb = kb0; kb < kb1; kb++) {
                     uint8_t *st = base + s * C::STAGE;
-                    mb_wait(&empty[s], ph ^ 1u);
-                    mb_expect_tx(&full[s], tx);
-                    tma_2d(st, &tmW, kb * BK, tile * BMW, &full[s]);
-                    tma_2d(st + A_BYTES, &tmA, kb * BK, 0, &full[s]);
-                    if (p.split) tma_2d(st + A_BYTES + C::B_BYTES, &tmA, Kw + kb * BK, 0, &full[s]);
+                    const bool prefetched = pre > 0;        // weight tile and expect_tx already issued above
+                    if (prefetched) pre--;
+                    else {
+                        mb_wait(&empty[s], ph ^ 1u);
+                        mb_expect_tx(&full[s], tx);
+                    }
+                    if (p.wt) {
+                        // tiled operands: one contiguous 16 KB weight tile + one contiguous [hi | lo] activation tile
+                        if (!prefetched) bulk_1d(st, p.wt + ((size_t)tile * p.nkb + kb) * A_BYTES, A_BYTES, &full[s]);
+                        bulk_1d(st + A_BYTES, p.at + (size_t)kb * (2 * C::B_BYTES), (p.split ? 2 : 1) * C::B_BYTES, &full[s]);
+                    } else {
+                        if (!prefetched) tma_2d(st, &tmW, kb * BK, tile * BMW, &full[s]);
+                        tma_2d(st + A_BYTES, &tmA, kb * BK, 0, &full[s]);
+                        if (p.split) tma_2d(st + A_BYTES + C::B_BYTES, &tmA, Kw + kb * BK, 0, &full[s]);
+                    }
                     if (++s == C::STAGES) { s = 0; ph ^= 1u; }
                 }
             }
@@ -129,6 +161,7 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
     } else {
         const int q = warp & 3;                             // TMEM lane quarter this warp may access
         int n = 0;
+        pdl_wait();                                         // outputs may still be read by an earlier kernel
         for (int it = blockIdx.x; it < total; it += gridDim.x, n++) {
             const int tile = it / p.ksplit, sp = it % p.ksplit;
             const int as = n & 1;
@@ -228,6 +261,7 @@ int gemm_wt_prepare(WtOp *op, int NB, int B, int N, int K, int split, const uint
     op->NB = NB; op->B = B; op->N = N; op->K = K; op->split = split; op->ksplit = ksplit;
     op->mode = WT_OUT_F32; op->out_f32 = nullptr; op->ldo = 0; op->split_stride = 0;
     op->out_bf16 = nullptr; op->ldb = 0; op->lo_off = 0;
+    op->w_tiled = nullptr; op->act_tiled = nullptr;
     return 0;
 }
 
@@ -236,6 +270,8 @@ int gemm_wt_launch(cudaStream_t st, const WtOp *op) {
     p.n_tiles = op->N / wt::BMW; p.nkb = op->K / wt::BK; p.ksplit = op->ksplit; p.B = op->B; p.split = op->split;
     p.mode = op->mode; p.out_f32 = op->out_f32; p.ldo = op->ldo; p.split_stride = op->split_stride;
     p.out_bf16 = op->out_bf16; p.ldb = op->ldb; p.lo_off = op->lo_off;
+    p.wt = (const uint8_t *)op->w_tiled; p.at = (const uint8_t *)op->act_tiled;
+    if ((p.wt == nullptr) != (p.at == nullptr)) { vox_set_error("gemm_wt: tiled weights need tiled activations"); return -1; }
     if ((p.mode == WT_OUT_F32 && !p.out_f32) || (p.mode == WT_OUT_SWIGLU_BF16X2 && (!p.out_bf16 || p.ksplit != 1))) {
         vox_set_error("gemm_wt: epilogue not set");
         return -1;
@@ -244,11 +280,10 @@ int gemm_wt_launch(cudaStream_t st, const WtOp *op) {
     const int grid = total < g_wt_sms ? total : g_wt_sms;
     const CUtensorMap &mw = *reinterpret_cast<const CUtensorMap *>(op->map_w);
     const CUtensorMap &ma = *reinterpret_cast<const CUtensorMap *>(op->map_a);
-    if (op->NB == 32) wt::gemm_wt_kernel<32><<<grid, wt::NT, wt::Cfg<32>::SMEM, st>>>(mw, ma, p);
-    else if (op->NB == 64) wt::gemm_wt_kernel<64><<<grid, wt::NT, wt::Cfg<64>::SMEM, st>>>(mw, ma, p);
-    else wt::gemm_wt_kernel<128><<<grid, wt::NT, wt::Cfg<128>::SMEM, st>>>(mw, ma, p);
+    if (op->NB == 32) CUDA_TRY(launch_pdl(wt::gemm_wt_kernel<32>, grid, wt::NT, wt::Cfg<32>::SMEM, st, mw, ma, p));
+    else if (op->NB == 64) CUDA_TRY(launch_pdl(wt::gemm_wt_kernel<64>, grid, wt::NT, wt::Cfg<64>::SMEM, st, mw, ma, p));
+    else CUDA_TRY(launch_pdl(wt::gemm_wt_kernel<128>, grid, wt::NT, wt::Cfg<128>::SMEM, st, mw, ma, p));
     LAUNCHED();
-    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 
@@ -324,4 +359,72 @@ done:
     free(hH);
     cudaFree(dA); cudaFree(dAb); cudaFree(dW); cudaFree(dP); cudaFree(dC); cudaFree(dH);
     return rc;
+}
+
+// C ABI (include/vox_cuda.h): device-resident timing of the multi-stream product alone.  Weights
+// rotate over enough copies (> 400 MB) that no launch finds its matrix in L2.  Returns the mean
+// microseconds per launch over iters launches (CUDA events), or a negative value on error.
+extern "C" float vox_cuda_bench_gemm_streams(int B, int N, int K, int ksplit, int swiglu, int iters) {
+    if (B <= 0 || B > 128 || iters < 1) return -1.f;
+    if (!vox_cuda_available() && !vox_cuda_init()) return -1.f;
+    const int NB = B <= 32 ? 32 : (B <= 64 ? 64 : 128);
+    const size_t wbytes = (size_t)N * K * 2;
+    int copies = (int)((400u << 20) / wbytes) + 1;
+    if (copies < 2) copies = 2;
+    if (copies > 64) copies = 64;
+    uint16_t *dW = nullptr, *dA = nullptr, *dH = nullptr;
+    float *dP = nullptr;
+    WtOp *ops = (WtOp *)aligned_alloc(64, sizeof(WtOp) * copies);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    float us = -1.f, ms = 0.f;
+    const int nout = swiglu ? N / 2 : N;
+    const char *tenv = getenv("VOX_WT_BENCH_TILED");
+    const bool tiled = tenv && atoi(tenv);
+    if (!ops) return -1.f;
+    if (cudaMalloc((void **)&dW, wbytes * copies) != cudaSuccess) goto done;
+    if (cudaMemset(dW, 0x3c, wbytes * copies) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dA, (size_t)NB * 2 * K * 2) != cudaSuccess) goto done;
+    if (cudaMemset(dA, 0x3c, (size_t)NB * 2 * K * 2) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dP, (size_t)ksplit * B * N * 4) != cudaSuccess) goto done;
+    if (cudaMalloc((void **)&dH, (size_t)B * 2 * nout * 2) != cudaSuccess) goto done;
+    for (int c = 0; c < copies; c++) {
+        if (gemm_wt_prepare(&ops[c], NB, B, N, K, 1, dA, 2L * K, dW + (size_t)c * N * K, ksplit)) goto done;
+        if (swiglu) { ops[c].mode = WT_OUT_SWIGLU_BF16X2; ops[c].out_bf16 = dH; ops[c].ldb = 2L * nout; ops[c].lo_off = nout; }
+        else { ops[c].out_f32 = dP; ops[c].ldo = N; ops[c].split_stride = (long)B * N; }
+        if (tiled) { ops[c].w_tiled = dW + (size_t)c * N * K; ops[c].act_tiled = dA; }   // same bytes read as tiles (timing only)
+    }
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) goto done;
+    for (int i = 0; i < copies; i++) if (gemm_wt_launch(0, &ops[i])) goto done;
+    if (cudaEventRecord(e0, 0) != cudaSuccess) goto done;
+    for (int i = 0; i < iters; i++) if (gemm_wt_launch(0, &ops[i % copies])) goto done;
+    if (cudaEventRecord(e1, 0) != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) goto done;
+    cudaEventElapsedTime(&ms, e0, e1);
+    us = ms * 1000.f / iters;
+done:
+    if (us < 0.f && !*vox_cuda_last_error()) vox_set_error("bench_gemm_streams: %s", cudaGetErrorString(cudaGetLastError()));
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(dW); cudaFree(dA); cudaFree(dP); cudaFree(dH);
+    free(ops);
+    return us;
+}
+
+// one thread per 16-byte chunk: (tile, kb, row, chunk j) <- W[tile*128 + row][kb*64 + 8j .. +8]
+__global__ void wt_tile_weights_kernel(const uint4 *__restrict__ W, uint4 *__restrict__ dst, int N, int K) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;          // chunk index in the row-major source
+    const size_t n_chunks = (size_t)N * K / 8;
+    if (i >= n_chunks) return;
+    const int cpr = K / 8;                                            // chunks per row
+    const int row = (int)(i / cpr), ck = (int)(i % cpr);
+    const int tile = row >> 7, r = row & 127, kb = ck >> 3, j = ck & 7;
+    const size_t o = (((size_t)tile * (K / 64) + kb) * 128 + r) * 8 + (j ^ (r & 7));
+    dst[o] = W[i];
+}
+int wt_tile_weights(cudaStream_t st, const uint16_t *W, uint16_t *dst, int N, int K) {
+    if (N % 128 || K % 64) { vox_set_error("wt_tile_weights: N %% 128 / K %% 64"); return -1; }
+    const size_t n_chunks = (size_t)N * K / 8;
+    wt_tile_weights_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, st>>>((const uint4 *)W, (uint4 *)dst, N, K);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return 0;
 }
