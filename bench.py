@@ -168,6 +168,45 @@ def run_cuda(args, rank, world):
     # ---- the roofline kernel in isolation: the persistent decoder-step kernel ----
     vc.check(L.vox_cuda_decoder_set_position(st, 38, 38), "set_position")
     ms_step = L.vox_cuda_bench_decoder_steps(st, 32, 38, n_tok, None)
+    # ---- config 5 leg: S independent clips per GPU through a stream group (lock-step decode, one pass
+    # over the weights per step); host PCM in, token ids out, inside the timed region ----
+    multi = None
+    if args.streams > 0:
+        S = args.streams
+        clips = [frame_buffer(synth_clip(args.clip_seconds, 100 + 4 * rank + i)) for i in range(min(S, 4))]
+        T = clips[0][1] // 8
+        g = vc.check(L.vox_cuda_group_create(model, S, T + 1), "group_create")
+        gtoks = np.empty((S, T), np.int32)
+        counts = np.zeros(S, np.int32)
+        gms = C.c_float()
+
+        def group_pass():
+            t0 = time.perf_counter()
+            for i in range(S):
+                b_, nf_ = clips[i % len(clips)]
+                vc.check(L.vox_cuda_group_encode(g, i, vc.fptr(b_), len(b_), nf_), "group_encode")
+            t1 = time.perf_counter()
+            steps_ = vc.check(L.vox_cuda_group_decode(g, PROMPT_LEN, vc.iptr(gtoks), T, vc.iptr(counts), C.byref(gms)), "group_decode")
+            return t1 - t0, time.perf_counter() - t1, steps_
+
+        group_pass()
+        launches_g0 = L.vox_cuda_launch_count()
+        barrier()
+        t0 = time.perf_counter()
+        enc_s, dec_s, gsteps = group_pass()
+        barrier()
+        t_group = max_over_ranks(time.perf_counter() - t0)
+        # the same clip through the single-stream call must give the same ids
+        b0, nf0 = clips[0]
+        n0 = vc.check(L.vox_cuda_transcribe(st, vc.fptr(b0), len(b0), nf0, PROMPT_LEN, vc.iptr(toks), max_tok, None), "transcribe")
+        multi = {"streams_per_gpu": S, "value": S * args.clip_seconds * world / t_group, "unit": UNIT,
+                 "ms_per_lock_step": float(gms.value) / gsteps, "lock_steps": int(gsteps),
+                 "encode_ms_per_clip": 1e3 * enc_s / S, "decode_s": dec_s,
+                 "decode_tok_per_s_per_gpu": float(counts.sum()) / dec_s,
+                 "gpu_launches": int(L.vox_cuda_launch_count() - launches_g0),
+                 "ids_equal_single_stream": bool(np.array_equal(toks[:n0], gtoks[0, :n0])),
+                 "api": "vox_cuda_group_encode(host PCM) x S + vox_cuda_group_decode -> ids on the host"}
+        L.vox_cuda_group_free(g)
     sampler.stop_flag = True
     sampler.join()
 
@@ -209,6 +248,8 @@ def run_cuda(args, rank, world):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)"},
             "decode_tok_per_s": 1e3 / ms_step,
         }
+        if multi is not None:
+            line["multi_stream"] = multi
         if not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(mdir)
         print(json.dumps(line), flush=True)
@@ -277,6 +318,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--streams", type=int, default=64,
+                    help="streams per GPU of the multi-stream leg (BASELINE config 5: 64 independent clips); 0 = skip")
     ap.add_argument("--clip-seconds", type=float, default=CLIP_SECONDS, help="profiling only; the headline is 60 s")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

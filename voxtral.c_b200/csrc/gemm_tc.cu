@@ -27,13 +27,21 @@
 
 namespace tc {
 
-constexpr int BM = 128, BN = 128, BK = 64;
-constexpr int STAGES = 6, ACC = 2;
-constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;       // 16 KB each
+constexpr int BM = 128, BK = 64;
+constexpr int ACC = 2;
+constexpr int A_BYTES = BM * BK * 2;                              // 16 KB per activation half (hi or lo)
 constexpr int NT = 192;
-constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;   // + barriers + alignment slack
-constexpr uint32_t IDESC = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
-                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);   // K-major A and B
+// One stage = [A hi | A lo | W]: the weight k-block is fetched once and multiplied by both activation
+// halves.  What bounds this kernel is the bytes an SM can take in per FLOP (measured ~60 GB/s per SM
+// whatever the source), so the tile is as wide as TMEM allows: BN = 256 -> 64 KB per 8.4 MFLOP.
+template <int BN> struct Cfg {
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE = 2 * A_BYTES + B_BYTES;
+    static constexpr int STAGES = 196608 / STAGE;                 // 3 (BN 256) or 4 (BN 128)
+    static constexpr int SMEM_BYTES = STAGES * STAGE + 256 + 1024; // + barriers + alignment slack
+    static constexpr uint32_t IDESC = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
+                                      ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);   // K-major A and B
+};
 
 __device__ __forceinline__ uint32_t s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mb_init(uint64_t *b, unsigned n) {
@@ -171,18 +179,19 @@ __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col,
     if (p.flags & TC_OUT_BF16) store_bf16<32>(p, row, col, v);
 }
 
+template <int BN>
 __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                         const __grid_constant__ CUtensorMap tmB, const KParams p) {
+    using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *base = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t *sA = base, *sB = base + STAGES * A_BYTES;
-    uint64_t *full = reinterpret_cast<uint64_t *>(base + STAGES * (A_BYTES + B_BYTES));
-    uint64_t *empty = full + STAGES, *tfull = empty + STAGES, *tempty = tfull + ACC;
+    uint64_t *full = reinterpret_cast<uint64_t *>(base + C::STAGES * C::STAGE);
+    uint64_t *empty = full + C::STAGES, *tfull = empty + C::STAGES, *tempty = tfull + ACC;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + ACC);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int i = 0; i < STAGES; i++) { mb_init(&full[i], 1); mb_init(&empty[i], 1); }
+        for (int i = 0; i < C::STAGES; i++) { mb_init(&full[i], 1); mb_init(&empty[i], 1); }
         for (int i = 0; i < ACC; i++) { mb_init(&tfull[i], 1); mb_init(&tempty[i], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -198,19 +207,23 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
     const uint32_t tmem_base = *tmem_slot;
 
     const int tiles_n = p.N / BN, tiles_m = (p.M + BM - 1) / BM;
-    const int total = tiles_n * tiles_m, nkb = p.K / BK;
+    const int total = tiles_n * tiles_m, nkb = p.Kw / BK;
+    const bool split = p.K != p.Kw;                         // A rows are [hi(Kw) | lo(Kw)]
 
     if (warp == 0) {
         if (lane == 0) {
             int s = 0; unsigned ph = 0;
+            const unsigned tx = (split ? 2 : 1) * A_BYTES + C::B_BYTES;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
                 for (int kb = 0; kb < nkb; kb++) {
+                    uint8_t *st = base + s * C::STAGE;
                     mb_wait(&empty[s], ph ^ 1u);
-                    mb_expect_tx(&full[s], A_BYTES + B_BYTES);
-                    tma_2d(sA + s * A_BYTES, &tmA, kb * BK, m0, &full[s]);
-                    tma_2d(sB + s * B_BYTES, &tmB, (kb * BK) % p.Kw, n0, &full[s]);
-                    if (++s == STAGES) { s = 0; ph ^= 1u; }
+                    mb_expect_tx(&full[s], tx);
+                    tma_2d(st, &tmA, kb * BK, m0, &full[s]);
+                    if (split) tma_2d(st + A_BYTES, &tmA, p.Kw + kb * BK, m0, &full[s]);
+                    tma_2d(st + 2 * A_BYTES, &tmB, kb * BK, n0, &full[s]);
+                    if (++s == C::STAGES) { s = 0; ph ^= 1u; }
                 }
             }
         }
@@ -227,15 +240,21 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
                 mb_wait(&full[s], ph);
                 tc_fence_after();
                 if (lane == 0) {
-                    const uint64_t da = umma_desc(s32(sA + s * A_BYTES)), db = umma_desc(s32(sB + s * B_BYTES));
+                    const uint32_t st = s32(base + s * C::STAGE);
+                    const uint64_t dh = umma_desc(st), dl = umma_desc(st + A_BYTES), db = umma_desc(st + 2 * A_BYTES);
                     #pragma unroll
                     for (int k = 0; k < BK / 16; k++)       // +32 B per K=16 step inside the 128 B swizzle row
-                        umma_f16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (kb | k) ? 1u : 0u);
+                        umma_f16(d, dh + (uint64_t)(2 * k), db + (uint64_t)(2 * k), C::IDESC, (kb | k) ? 1u : 0u);
+                    if (split) {
+                        #pragma unroll
+                        for (int k = 0; k < BK / 16; k++)
+                            umma_f16(d, dl + (uint64_t)(2 * k), db + (uint64_t)(2 * k), C::IDESC, 1u);
+                    }
                     umma_commit(&empty[s]);                 // stage reusable once these MMAs retire
                     if (kb == nkb - 1) umma_commit(&tfull[as]);
                 }
                 __syncwarp();
-                if (++s == STAGES) { s = 0; ph ^= 1u; }
+                if (++s == C::STAGES) { s = 0; ph ^= 1u; }
             }
         }
     } else {
@@ -286,15 +305,16 @@ static int tc_init(void) {
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     CUDA_TRY(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(cudaFuncSetAttribute(tc::gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+    CUDA_TRY(cudaFuncSetAttribute(tc::gemm_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::Cfg<128>::SMEM_BYTES));
+    CUDA_TRY(cudaFuncSetAttribute(tc::gemm_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::Cfg<256>::SMEM_BYTES));
     return 0;
 }
 
 // 2-D bf16 tensor map: dim0 = K (contiguous), dim1 = rows with byte stride ld*2; box 64 x 128, 128 B swizzle
-static int make_map(CUtensorMap *m, const uint16_t *ptr, int rows, int K, long ld) {
+static int make_map(CUtensorMap *m, const uint16_t *ptr, int rows, int K, long ld, int box_rows) {
     cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)tc::BM};
+    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *)ptr, dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -310,19 +330,24 @@ int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, lon
             const TcEpilogue &epi) {
     if (M <= 0) return 0;
     if (tc_init()) return -1;
-    if ((KA != K && KA != 2 * K) || N % tc::BN || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
+    if ((KA != K && KA != 2 * K) || N % 128 || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
         vox_set_error("gemm_tc: unsupported shape M=%d N=%d K=%d lda=%ld", M, N, K, lda);
         return -1;
     }
+    static int force128 = -1;
+    if (force128 < 0) { const char *e = getenv("VOX_CUDA_TC_BN128"); force128 = (e && atoi(e)) ? 1 : 0; }
+    // wide tiles only when they still fill the machine (small-M calls stream weights: more CTAs matter more)
+    const int BN = (N % 256 == 0 && !force128 && (N / 256) * ((M + tc::BM - 1) / tc::BM) >= 100) ? 256 : 128;
     CUtensorMap ma, mb;
-    if (make_map(&ma, A, M, KA, lda) || make_map(&mb, W, N, K, K)) return -1;
+    if (make_map(&ma, A, M, KA, lda, tc::BM) || make_map(&mb, W, N, K, K, BN)) return -1;
     tc::KParams p;
     p.M = M; p.N = N; p.K = KA; p.Kw = K; p.split_off = epi.split_off;
     p.out_f32 = epi.out_f32; p.ldo_f32 = epi.ldo_f32; p.out_bf16 = epi.out_bf16; p.ldo_bf16 = epi.ldo_bf16;
     p.bias = epi.bias; p.flags = epi.flags;
-    const int total = (N / tc::BN) * ((M + tc::BM - 1) / tc::BM);
+    const int total = (N / BN) * ((M + tc::BM - 1) / tc::BM);
     const int grid = total < g_sms ? total : g_sms;
-    tc::gemm_tc_kernel<<<grid, tc::NT, tc::SMEM_BYTES, st>>>(ma, mb, p);
+    if (BN == 256) tc::gemm_tc_kernel<256><<<grid, tc::NT, tc::Cfg<256>::SMEM_BYTES, st>>>(ma, mb, p);
+    else tc::gemm_tc_kernel<128><<<grid, tc::NT, tc::Cfg<128>::SMEM_BYTES, st>>>(ma, mb, p);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return 0;
