@@ -40,7 +40,8 @@ template <int NB> struct Cfg {
     static constexpr int B_BYTES = NB * BK * 2;             // one activation half (hi or lo)
     static constexpr int STAGE = A_BYTES + 2 * B_BYTES;
     static constexpr int STAGES = (196608 / STAGE) > 8 ? 8 : (196608 / STAGE);
-    static constexpr int TMEM_COLS = (ACC * NB) < 32 ? 32 : (ACC * NB);
+    static constexpr int ACC_COLS = 2 * NB;                 // [hi products | lo products], added in the epilogue
+    static constexpr int TMEM_COLS = ACC * ACC_COLS;        // 128 / 256 / 512
     static constexpr int SMEM = STAGES * STAGE + 512 + 1024;
 };
 
@@ -126,7 +127,9 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
             }
         }
     } else if (warp == 1) {
-        constexpr uint32_t IDESC = umma_idesc(BMW, NB);
+        // hi and lo activation tiles are adjacent in the stage, so one MMA with N = 2 NB multiplies the
+        // weight tile by both halves (the A-operand read, not N, sets the cost of a narrow MMA)
+        constexpr uint32_t IDESC2 = umma_idesc(BMW, 2 * NB), IDESC1 = umma_idesc(BMW, NB);
         int s = 0; unsigned ph = 0;
         int n = 0;
         for (int it = blockIdx.x; it < total; it += gridDim.x, n++) {
@@ -136,21 +139,17 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
             const unsigned aph = (unsigned)(n >> 1) & 1u;
             mb_wait(&tempty[as], aph ^ 1u);                 // epilogue has drained this accumulator
             tc_fence_after();
-            const uint32_t d = tmem_base + (uint32_t)(as * NB);
+            const uint32_t d = tmem_base + (uint32_t)(as * C::ACC_COLS);
+            const uint32_t idesc = p.split ? IDESC2 : IDESC1;
             for (int kb = kb0; kb < kb1; kb++) {
                 mb_wait(&full[s], ph);
                 tc_fence_after();
                 if (lane == 0) {
                     const uint32_t st = s32(base + s * C::STAGE);
-                    const uint64_t da = umma_desc(st), dh = umma_desc(st + A_BYTES), dl = umma_desc(st + A_BYTES + C::B_BYTES);
+                    const uint64_t da = umma_desc(st), dh = umma_desc(st + A_BYTES);
                     #pragma unroll
                     for (int k = 0; k < BK / 16; k++)       // +32 B per K=16 step inside the 128 B swizzle row
-                        umma_f16(d, da + (uint64_t)(2 * k), dh + (uint64_t)(2 * k), IDESC, (kb > kb0 || k) ? 1u : 0u);
-                    if (p.split) {
-                        #pragma unroll
-                        for (int k = 0; k < BK / 16; k++)
-                            umma_f16(d, da + (uint64_t)(2 * k), dl + (uint64_t)(2 * k), IDESC, 1u);
-                    }
+                        umma_f16(d, da + (uint64_t)(2 * k), dh + (uint64_t)(2 * k), idesc, (kb > kb0 || k) ? 1u : 0u);
                     umma_commit(&empty[s]);                 // stage reusable once these MMAs retire
                     if (kb == kb1 - 1) umma_commit(&tfull[as]);
                 }
@@ -172,23 +171,33 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
             #pragma unroll 1
             for (int cc = 0; cc < NB / 32; cc++) {
                 uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * NB + cc * 32), r);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_COLS + cc * 32), r);
+                if (p.split) {
+                    uint32_t r2[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_COLS + NB + cc * 32), r2);
+                    #pragma unroll
+                    for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) + __uint_as_float(r2[c]));
+                }
                 if (p.mode == 0) {
                     float *o = p.out_f32 + (size_t)sp * p.split_stride + row;
                     #pragma unroll
                     for (int c = 0; c < 32; c++)
                         if (cc * 32 + c < p.B) o[(size_t)(cc * 32 + c) * p.ldo] = __uint_as_float(r[c]);
                 } else {
-                    // SwiGLU (voxtral_decoder.c:747-757): even lane = gate row 2i, odd lane = up row 2i+1
+                    // SwiGLU (voxtral_decoder.c:747-757): even lane = gate row 2i, odd lane = up row 2i+1 of the
+                    // same feature.  The pair shares the work: the even lane finishes column c, the odd lane c + 1.
+                    const int odd = lane & 1;
                     #pragma unroll
-                    for (int c = 0; c < 32; c++) {
-                        const float v = __uint_as_float(r[c]);
-                        const float u = __shfl_xor_sync(0xffffffffu, v, 1);
-                        if (!(lane & 1) && cc * 32 + c < p.B) {
-                            const float h = silu(v) * u;
+                    for (int c = 0; c < 32; c += 2) {
+                        const float v0 = __uint_as_float(r[c]), v1 = __uint_as_float(r[c + 1]);
+                        const float recv = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
+                        const float gte = odd ? recv : v0, up = odd ? v1 : recv;
+                        const int col = cc * 32 + c + odd;
+                        if (col < p.B) {
+                            const float h = silu(gte) * up;
                             const __nv_bfloat16 hi = __float2bfloat16_rn(h);
                             const __nv_bfloat16 lo = __float2bfloat16_rn(h - __bfloat162float(hi));
-                            __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out_bf16) + (size_t)(cc * 32 + c) * p.ldb + (row >> 1);
+                            __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out_bf16) + (size_t)col * p.ldb + (row >> 1);
                             o[0] = hi;
                             o[p.lo_off] = lo;
                         }
