@@ -2,7 +2,8 @@
 checked against the oracle (oracle/_ref, the compiled reference BLAS path).
 
 Runs: log-mel of 1 s of audio, then prefill(38) + 2 greedy decoder steps on the
-random-init checkpoint, all through the C ABI (libvoxcuda.so).  Fails loudly if
+random-init checkpoint, then the same two steps for two streams in lock step
+(stream group), all through the C ABI (libvoxcuda.so).  Fails loudly if
 the CUDA library is missing - there is no CPU fallback.
 """
 import numpy as np
@@ -51,6 +52,7 @@ def run():
         vc.check(L.vox_cuda_decoder_prefill(st, vc.fptr(emb), 38), "prefill")
         prev = 32
         logits = np.empty(131072, np.float32)
+        ref_toks = []
         for i in range(2):
             xin = (adapter[38 + i] + ref.tok_embedding(prev)).astype(np.float32)
             tok_r, logits_r = ref.decoder_forward(xin)
@@ -58,7 +60,20 @@ def run():
             d = float(np.abs(logits - logits_r).max())
             print(f"smoke: step {i} ref token {tok_r} cuda token {tok_c} max|dlogit| {d:.2e}")
             assert tok_c == tok_r and d < 2e-2
+            ref_toks.append(tok_r)
             prev = tok_r
+        # ---- the same two steps for 2 streams in lock step (stream group, skinny tcgen05 GEMM) ----
+        g = vc.check(L.vox_cuda_group_create(model, 2, 64), "group_create")
+        try:
+            for i in range(2):
+                vc.check(L.vox_cuda_group_set_adapter(g, i, vc.fptr(adapter), 40), "group_set_adapter")
+            gt = np.empty((2, 8), np.int32)
+            counts = np.zeros(2, np.int32)
+            steps = vc.check(L.vox_cuda_group_decode(g, 39, vc.iptr(gt), 8, vc.iptr(counts), None), "group_decode")
+            print(f"smoke: group of 2 streams, {steps} lock steps, ids {gt[0, :2].tolist()} {gt[1, :2].tolist()}")
+            assert steps == 2 and gt[0, :2].tolist() == ref_toks and gt[1, :2].tolist() == ref_toks
+        finally:
+            L.vox_cuda_group_free(g)
         print("smoke: kernel launches so far:", L.vox_cuda_launch_count())
     finally:
         L.vox_cuda_state_free(st)
