@@ -107,6 +107,33 @@ def test_group_tokens_equal_single_stream(full_env):
         e.L.vox_cuda_group_free(g)
 
 
+def test_group_persistent_kernel_matches(full_env, monkeypatch):
+    """VOX_CUDA_GROUP_MEGA=1: the whole decode as one persistent cooperative kernel (grid barriers instead of
+    launches, csrc/group_mega.cu) must give the ids of the default kernel-per-op path."""
+    e = full_env
+    clips = [_clip(2.0, 5), _clip(2.7, 21)]
+
+    def run():
+        g = e.L.vox_cuda_group_create(e.model, 3, 64)
+        assert g, e.vc.last_error()
+        try:
+            for i, (buf, nf) in enumerate(clips):
+                assert e.L.vox_cuda_group_encode(g, 2 * i, e.vc.fptr(buf), len(buf), nf) > 39       # slots 0 and 2
+            toks = np.full((3, 32), -7, np.int32)
+            counts = np.zeros(3, np.int32)
+            assert e.L.vox_cuda_group_decode(g, 39, e.vc.iptr(toks), 32, e.vc.iptr(counts), None) > 0, e.vc.last_error()
+            return toks, counts.copy()
+        finally:
+            e.L.vox_cuda_group_free(g)
+
+    monkeypatch.delenv("VOX_CUDA_GROUP_MEGA", raising=False)
+    t0, c0 = run()
+    monkeypatch.setenv("VOX_CUDA_GROUP_MEGA", "1")
+    t1, c1 = run()
+    assert c0.tolist() == c1.tolist() and c0[1] == 0 and c0[0] > 0
+    assert np.array_equal(t0, t1)
+
+
 def test_group_64_streams_60s_properties(full_env):
     """Full bench size: 64 slots x 60 s.  Too large to diff on the CPU, so: (1) all 64 copies of one
     clip give identical ids (no cross-stream leakage, no dependence on the slot), and they equal the
