@@ -114,7 +114,7 @@ def test_group_persistent_kernel_matches(full_env, monkeypatch):
     clips = [_clip(2.0, 5), _clip(2.7, 21)]
 
     def run():
-        g = e.L.vox_cuda_group_create(e.model, 3, 64)
+        g = e.L.vox_cuda_group_create(e.model, 3, 128)
         assert g, e.vc.last_error()
         try:
             for i, (buf, nf) in enumerate(clips):

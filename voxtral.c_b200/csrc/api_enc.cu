@@ -8,6 +8,7 @@
 #include "vox_internal.h"
 #include "rows.h"
 #include "enc_state.h"
+#include "gemm_tc.h"
 #include <stdlib.h>
 #include <string.h>
 
@@ -40,6 +41,14 @@ int enc_state_create(vox_cuda_state *s) {
 }
 
 void enc_fast_free(vox_cuda_state *s);
+void enc_small_free(void *p);
+int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out);
+// VOX_CUDA_ENC_SMALL=0 keeps streaming chunks (M <= 128) on the large-tile GEMM (A/B runs)
+static int enc_small_mode(void) {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("VOX_CUDA_ENC_SMALL"); v = (e && !atoi(e)) ? 0 : 1; }
+    return v;
+}
 int adapter_fast(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *out);
 static int enc_precise_mode(void);
 
@@ -47,7 +56,9 @@ void enc_state_free(vox_cuda_state *s) {
     EncState *e = (EncState *)s->enc_priv;
     if (!e) return;
     enc_fast_free(s);
-    void *ptrs[] = {e->kv_k, e->kv_v, e->mel_in, e->c0, e->x, e->xn, e->qkv, e->att, e->gu, e->hh, e->encout, e->mid};
+    enc_small_free(e->small);
+    void *ptrs[] = {e->kv_k, e->kv_v, e->mel_in, e->c0, e->x, e->xn, e->qkv, e->att, e->gu, e->hh, e->encout, e->mid,
+                    e->mel_hi, e->mel_lo, e->c0_hi, e->c0_lo};
     for (void *p : ptrs) if (p) cudaFree(p);
     vox_mem_account(-(long)(2 * e->kv_bytes));
     if (e->h_stage) cudaFreeHost(e->h_stage);
@@ -82,6 +93,26 @@ __global__ void stem_mel_hist_one_kernel(float *mel_in) {
     mel_in[VOX_CUDA_MEL_BINS + i] = mel_in[2 * VOX_CUDA_MEL_BINS + i];
 }
 
+// bf16 planes for the tensor-core stem (allocated on first use)
+static int stem_planes(EncState *e) {
+    if (e->mel_hi) return 0;
+    const size_t mel_b = (size_t)(2 + ENC_MAXMEL) * VOX_CUDA_MEL_BINS * 2, c0_b = (size_t)(2 + ENC_MAXMEL) * ENC_DIM * 2;
+    if (cudaMalloc((void **)&e->mel_hi, mel_b) != cudaSuccess || cudaMalloc((void **)&e->mel_lo, mel_b) != cudaSuccess ||
+        cudaMalloc((void **)&e->c0_hi, c0_b) != cudaSuccess || cudaMalloc((void **)&e->c0_lo, c0_b) != cudaSuccess) {
+        vox_set_error("conv stem: plane buffers alloc failed");
+        return -1;
+    }
+    vox_mem_account((long)(2 * mel_b + 2 * c0_b));
+    return 0;
+}
+
+static TcEpilogue stem_epi(float *out, const float *bias) {
+    TcEpilogue t;
+    t.out_f32 = out; t.ldo_f32 = ENC_DIM; t.out_bf16 = nullptr; t.ldo_bf16 = 0; t.bias = bias;
+    t.flags = TC_BIAS | TC_GELU | TC_OUT_F32; t.split_off = 0;
+    return t;
+}
+
 static int stem_device(vox_cuda_state *s, int n_mel, int *out_len) {
     EncState *e = (EncState *)s->enc_priv;
     vox_cuda_model *m = s->m;
@@ -89,9 +120,17 @@ static int stem_device(vox_cuda_state *s, int n_mel, int *out_len) {
     *out_len = 0;
     if (n_mel <= 0) return 0;
     const int prev_res = e->c0_resid;
+    // Both convolutions are GEMMs over overlapping [3 x channels] row windows (no im2col copy).  Default:
+    // tcgen05 GEMM on split-bf16 planes of the rows (fp32-class); precise mode: fp32 CUDA-core GEMM.
+    const bool tcm = !enc_precise_mode();
+    if (tcm && stem_planes(e)) return -1;
     // conv0 (k=3, s=1, causal): out row t = gelu(W0 . mel[t-2..t] + b0); A rows overlap (lda = 128)
-    if (sgemm_bf16w(st, n_mel, ENC_DIM, 3 * VOX_CUDA_MEL_BINS, e->mel_in, VOX_CUDA_MEL_BINS, m->conv0_w,
-                    e->c0 + (size_t)(1 + prev_res) * ENC_DIM, ENC_DIM, m->conv0_b, EPI_BIAS | EPI_GELU)) return -1;
+    if (tcm) {
+        if (f32_to_bf16_planes(st, e->mel_in, e->mel_hi, e->mel_lo, (size_t)(n_mel + 2) * VOX_CUDA_MEL_BINS)) return -1;
+        if (gemm_tc_planes(st, n_mel, ENC_DIM, 3 * VOX_CUDA_MEL_BINS, e->mel_hi, e->mel_lo, VOX_CUDA_MEL_BINS, m->conv0_w,
+                           stem_epi(e->c0 + (size_t)(1 + prev_res) * ENC_DIM, m->conv0_b))) return -1;
+    } else if (sgemm_bf16w(st, n_mel, ENC_DIM, 3 * VOX_CUDA_MEL_BINS, e->mel_in, VOX_CUDA_MEL_BINS, m->conv0_w,
+                           e->c0 + (size_t)(1 + prev_res) * ENC_DIM, ENC_DIM, m->conv0_b, EPI_BIAS | EPI_GELU)) return -1;
     if (n_mel >= 2) {
         stem_shift_rows_kernel<<<1, 128, 0, st>>>(e->mel_in, VOX_CUDA_MEL_BINS, n_mel, n_mel + 1, 1);
     } else {
@@ -106,8 +145,12 @@ static int stem_device(vox_cuda_state *s, int n_mel, int *out_len) {
     if (feed_total <= 0) { e->c0_resid = new_res; return 0; }  // the lone row already sits at row 1
     // conv1 (k=3, s=2): out row j = gelu(W1 . c0[2j-1 .. 2j+1] + b1), row 0 of c0 is the history row
     const int L = feed_total / 2;
-    if (sgemm_bf16w(st, L, ENC_DIM, 3 * ENC_DIM, e->c0, 2 * ENC_DIM, m->conv1_w, e->x, ENC_DIM,
-                    m->conv1_b, EPI_BIAS | EPI_GELU)) return -1;
+    if (tcm) {
+        if (f32_to_bf16_planes(st, e->c0, e->c0_hi, e->c0_lo, (size_t)(feed_total + 1) * ENC_DIM)) return -1;
+        if (gemm_tc_planes(st, L, ENC_DIM, 3 * ENC_DIM, e->c0_hi, e->c0_lo, 2 * ENC_DIM, m->conv1_w,
+                           stem_epi(e->x, m->conv1_b))) return -1;
+    } else if (sgemm_bf16w(st, L, ENC_DIM, 3 * ENC_DIM, e->c0, 2 * ENC_DIM, m->conv1_w, e->x, ENC_DIM,
+                           m->conv1_b, EPI_BIAS | EPI_GELU)) return -1;
     stem_shift_rows_kernel<<<8, 256, 0, st>>>(e->c0, ENC_DIM, feed_total, feed_total + 1, new_res);
     LAUNCHED();
     e->c0_resid = new_res;
@@ -155,7 +198,8 @@ static int enc_precise_mode(void) {
 }
 
 static int enc_layers(vox_cuda_state *s, float *x, int M, float *out) {
-    return enc_precise_mode() ? enc_layers_precise(s, x, M, out) : enc_layers_fast(s, x, M, out);
+    if (enc_precise_mode()) return enc_layers_precise(s, x, M, out);
+    return (M <= 128 && enc_small_mode()) ? enc_layers_small(s, x, M, out) : enc_layers_fast(s, x, M, out);
 }
 
 // ---- adapter (vox_adapter_forward, voxtral_encoder.c:699-737) -----------------------

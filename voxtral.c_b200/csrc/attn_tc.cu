@@ -16,6 +16,7 @@
 #include "enc_state.h"
 #include "rows.h"
 #include "gemm_tc.h"
+#include "tc_ptx.cuh"
 #include <stdlib.h>
 
 namespace at {
@@ -74,6 +75,8 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
     const float *__restrict__ qkv, long ldq, const float *__restrict__ kc, const float *__restrict__ vc,
     int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split) {
     extern __shared__ __align__(16) uint16_t sm[];
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     uint16_t *Qh = sm, *Ql = sm + TILE, *Kh = sm + 2 * TILE, *Kl = sm + 3 * TILE, *Vh = sm + 4 * TILE, *Vl = sm + 5 * TILE;
     const int head = blockIdx.y, q0 = blockIdx.x * BQ;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -241,12 +244,11 @@ int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const fl
     }
     dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
     if (split)
-        at::enc_attn_kernel<3><<<grid, at::NT, at::SMEM_BYTES, st>>>(qkv, 3 * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
-                                                                    ENC_RING - 1, out_b, ldo, 1);
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
+                            ENC_RING - 1, out_b, ldo, 1));
     else
-        at::enc_attn_kernel<1><<<grid, at::NT, at::SMEM_BYTES, st>>>(qkv, 3 * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
-                                                                    ENC_RING - 1, out_b, ldo, 0);
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
+                            ENC_RING - 1, out_b, ldo, 0));
     LAUNCHED();
-    CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -126,3 +126,177 @@ int adapter_fast(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *
     return gemm_tc(st, k_tokens, DEC_DIM, DEC_DIM, mul * DEC_DIM, f->mid_b, mul * DEC_DIM, m->adapter_w1,
                    epi(out, DEC_DIM, nullptr, 0, nullptr, TC_OUT_F32));
 }
+
+// ---- small-M path (streaming chunks: M <= 128 new positions per call) -----------------------------
+// With M <= 128 rows the GEMMs above are weight-streaming problems (1.93 GB of encoder weights per
+// call) and a 128 x 128 tile grid gives only N/128 = 10..80 CTAs, each pulling its slab at one SM's
+// ingress rate: 5.9 ms per call, measured, against a 0.30 ms HBM floor.  Here the layers run on the
+// skinny swap-AB GEMM of the stream groups (gemm_wt.cu: weight tile = UMMA A operand, the M rows =
+// narrow B operand, K-range splits so that ~140 CTAs stream weights); K-range partials are summed
+// (+ bias, + residual) by the small kernels below, which also produce the next GEMM's split-bf16 rows.
+#include "gemm_wt.h"
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int SM_KS_QKV = 3, SM_KS_WO = 14, SM_KS_W2 = 14, SM_KS_MAX = 14;
+
+// out[m][n] = sum_s part[s][m][n] + bias[n]           (QKV + bias, voxtral_encoder.c:591-593)
+__global__ void __launch_bounds__(256) enc_sum_bias_kernel(const float *__restrict__ part, int ks, long stride,
+                                                           const float *__restrict__ bias, float *__restrict__ out, int N) {
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    const int m = blockIdx.x, col = (blockIdx.y * 256 + threadIdx.x) * 4;
+    if (col >= N) return;
+    float4 a = *reinterpret_cast<const float4 *>(bias + col);
+    const float *p = part + (size_t)m * N + col;
+    for (int s = 0; s < ks; s++) {
+        const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    *reinterpret_cast<float4 *>(out + (size_t)m * N + col) = a;
+}
+
+// x[m] += sum_s part[s][m] + bias; then RMSNorm(x[m]) * w -> split bf16 row (out_b) or fp32 row (out_f)
+// (wo / w2 + bias + residual, voxtral_encoder.c:644-646,677-679, followed by the next norm :562-566,652-656)
+__global__ void __launch_bounds__(320) enc_resid_norm_kernel(float *__restrict__ x, const float *__restrict__ part, int ks, long stride,
+                                                             const float *__restrict__ bias, const float *__restrict__ w,
+                                                             uint16_t *__restrict__ out_b, float *__restrict__ out_f) {
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    const int m = blockIdx.x, col = threadIdx.x * 4;
+    float *xr = x + (size_t)m * ENC_DIM;
+    float4 a = *reinterpret_cast<const float4 *>(xr + col);
+    const float4 b = *reinterpret_cast<const float4 *>(bias + col);
+    float4 acc = b;
+    const float *p = part + (size_t)m * ENC_DIM + col;
+    for (int s = 0; s < ks; s++) {
+        const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += acc.w;
+    *reinterpret_cast<float4 *>(xr + col) = a;
+    __shared__ float red[10];
+    float ss = warp_sum(a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+    #pragma unroll
+    for (int i = 0; i < 10; i++) tot += red[i];
+    const float rinv = 1.0f / sqrtf(tot / (float)ENC_DIM + NORM_EPS);
+    const float4 wv = *reinterpret_cast<const float4 *>(w + col);
+    const float y0 = a.x * rinv * wv.x, y1 = a.y * rinv * wv.y, y2 = a.z * rinv * wv.z, y3 = a.w * rinv * wv.w;
+    if (out_f) *reinterpret_cast<float4 *>(out_f + (size_t)m * ENC_DIM + col) = make_float4(y0, y1, y2, y3);
+    if (out_b) {
+        const __nv_bfloat162 h0 = __floats2bfloat162_rn(y0, y1), h1 = __floats2bfloat162_rn(y2, y3);
+        const __nv_bfloat162 l0 = __floats2bfloat162_rn(y0 - __bfloat162float(h0.x), y1 - __bfloat162float(h0.y));
+        const __nv_bfloat162 l1 = __floats2bfloat162_rn(y2 - __bfloat162float(h1.x), y3 - __bfloat162float(h1.y));
+        uint2 hv, lv;
+        hv.x = *reinterpret_cast<const uint32_t *>(&h0); hv.y = *reinterpret_cast<const uint32_t *>(&h1);
+        lv.x = *reinterpret_cast<const uint32_t *>(&l0); lv.y = *reinterpret_cast<const uint32_t *>(&l1);
+        uint16_t *orow = out_b + (size_t)m * 2 * ENC_DIM;
+        *reinterpret_cast<uint2 *>(orow + col) = hv;
+        *reinterpret_cast<uint2 *>(orow + ENC_DIM + col) = lv;
+    }
+}
+
+struct EncSmall {
+    uint16_t *xn_t, *att_t, *hh_t;      // [128][2*1280], [128][2*2048], [128][2*5120] split bf16 rows
+    float *part;                        // K-range partials, max(14*128*1280, 3*128*6144) floats
+    WtOp *ops[3];                       // per NB in {32, 64, 128}: [n_enc][4] prepared products (lazily)
+};
+
+}  // namespace
+
+void enc_small_free(void *p) {
+    EncSmall *q = (EncSmall *)p;
+    if (!q) return;
+    cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part);
+    for (int i = 0; i < 3; i++) free(q->ops[i]);
+    free(q);
+}
+
+static EncSmall *small_get(vox_cuda_state *s, int NB) {
+    EncState *e = (EncState *)s->enc_priv;
+    EncSmall *q = (EncSmall *)e->small;
+    vox_cuda_model *m = s->m;
+    if (!q) {
+        q = (EncSmall *)calloc(1, sizeof(EncSmall));
+        if (!q) return nullptr;
+        const size_t part_f = (size_t)SM_KS_QKV * 128 * 3 * ENC_QKV > (size_t)SM_KS_MAX * 128 * ENC_DIM
+                                  ? (size_t)SM_KS_QKV * 128 * 3 * ENC_QKV : (size_t)SM_KS_MAX * 128 * ENC_DIM;
+        const size_t bytes[4] = {(size_t)128 * 2 * ENC_DIM * 2, (size_t)128 * 2 * ENC_QKV * 2, (size_t)128 * 2 * ENC_HIDDEN * 2, part_f * 4};
+        void **ptrs[4] = {(void **)&q->xn_t, (void **)&q->att_t, (void **)&q->hh_t, (void **)&q->part};
+        for (int i = 0; i < 4; i++) {
+            if (cudaMalloc(ptrs[i], bytes[i]) != cudaSuccess || cudaMemset(*ptrs[i], 0, bytes[i]) != cudaSuccess) {
+                vox_set_error("enc_small: cudaMalloc(%zu) failed", bytes[i]);
+                enc_small_free(q);
+                return nullptr;
+            }
+        }
+        e->small = q;
+    }
+    const int idx = NB == 32 ? 0 : (NB == 64 ? 1 : 2);
+    if (!q->ops[idx]) {
+        WtOp *ops = (WtOp *)aligned_alloc(64, sizeof(WtOp) * 4 * m->n_enc);
+        if (!ops) return nullptr;
+        for (int l = 0; l < m->n_enc; l++) {
+            const EncLayerDev &L = m->enc[l];
+            WtOp *o = ops + 4 * l;
+            if (gemm_wt_prepare(&o[0], NB, 1, 3 * ENC_QKV, ENC_DIM, 1, q->xn_t, 2 * ENC_DIM, L.wqkv, SM_KS_QKV) ||
+                gemm_wt_prepare(&o[1], NB, 1, ENC_DIM, ENC_QKV, 1, q->att_t, 2 * ENC_QKV, L.wo, SM_KS_WO) ||
+                gemm_wt_prepare(&o[2], NB, 1, 2 * ENC_HIDDEN, ENC_DIM, 1, q->xn_t, 2 * ENC_DIM, L.w13, 1) ||
+                gemm_wt_prepare(&o[3], NB, 1, ENC_DIM, ENC_HIDDEN, 1, q->hh_t, 2 * ENC_HIDDEN, L.w2, SM_KS_W2)) {
+                free(ops);
+                return nullptr;
+            }
+            o[0].out_f32 = q->part; o[0].ldo = 3 * ENC_QKV;
+            o[1].out_f32 = q->part; o[1].ldo = ENC_DIM;
+            o[2].mode = WT_OUT_SWIGLU_BF16X2; o[2].out_bf16 = q->hh_t; o[2].ldb = 2 * ENC_HIDDEN; o[2].lo_off = ENC_HIDDEN;
+            o[3].out_f32 = q->part; o[3].ldo = ENC_DIM;
+        }
+        q->ops[idx] = ops;
+    }
+    return q;
+}
+
+// M <= 128 new positions: same layer arithmetic as enc_layers_fast (split-bf16 operands, fp32 accumulation)
+int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
+    EncState *e = (EncState *)s->enc_priv;
+    if (!split_mode()) return enc_layers_fast(s, x, M, out);    // single-bf16 A/B mode lives on the large-tile path
+    if (!fast_get(s)) return -1;
+    const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+    EncSmall *q = small_get(s, NB);
+    if (!q) return -1;
+    WtOp *ops = q->ops[NB == 32 ? 0 : (NB == 64 ? 1 : 2)];
+    vox_cuda_model *m = s->m;
+    cudaStream_t st = s->stream;
+    const size_t kv_layer = (size_t)ENC_RING * ENC_QKV;
+    const int pos0 = e->pos;
+    if (rows_rmsnorm_bf16(st, x, ENC_DIM, m->enc[0].attn_norm, nullptr, q->xn_t, 2 * ENC_DIM, M, ENC_DIM, 1)) return -1;
+    for (int l = 0; l < m->n_enc; l++) {
+        const EncLayerDev &L = m->enc[l];
+        float *kc = e->kv_k + l * kv_layer, *vc = e->kv_v + l * kv_layer;
+        WtOp *o = ops + 4 * l;
+        for (int i = 0; i < 4; i++) o[i].B = M;
+        o[0].split_stride = (long)M * 3 * ENC_QKV; o[1].split_stride = (long)M * ENC_DIM; o[3].split_stride = (long)M * ENC_DIM;
+        if (gemm_wt_launch(st, &o[0])) return -1;
+        CUDA_TRY(launch_pdl(enc_sum_bias_kernel, dim3(M, (3 * ENC_QKV + 1023) / 1024), 256, 0, st, (const float *)q->part, SM_KS_QKV,
+                            (long)M * 3 * ENC_QKV, L.bqkv, e->qkv, 3 * ENC_QKV));
+        LAUNCHED();
+        if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
+        if (enc_attention(s, e->qkv, kc, vc, M, pos0, q->att_t, 2 * ENC_QKV, 1)) return -1;
+        if (gemm_wt_launch(st, &o[1])) return -1;
+        CUDA_TRY(launch_pdl(enc_resid_norm_kernel, M, 320, 0, st, x, (const float *)q->part, SM_KS_WO, (long)M * ENC_DIM, L.bo, L.ffn_norm,
+                            q->xn_t, (float *)nullptr));
+        LAUNCHED();
+        if (gemm_wt_launch(st, &o[2])) return -1;
+        if (gemm_wt_launch(st, &o[3])) return -1;
+        const bool last = l == m->n_enc - 1;
+        CUDA_TRY(launch_pdl(enc_resid_norm_kernel, M, 320, 0, st, x, (const float *)q->part, SM_KS_W2, (long)M * ENC_DIM, L.b2,
+                            last ? m->enc_norm : m->enc[l + 1].attn_norm, last ? (uint16_t *)nullptr : q->xn_t, last ? out : (float *)nullptr));
+        LAUNCHED();
+    }
+    e->pos += M;
+    return 0;
+}

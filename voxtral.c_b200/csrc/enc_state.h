@@ -25,4 +25,7 @@ struct EncState {
     float *mid;                // adapter hidden [ENC_CHUNK/4 + 1][3072]
     float *h_stage;            // pinned host staging
     void *fast;                // EncFast*, enc_fast.cu
+    void *small;               // EncSmall*, enc_fast.cu (M <= 128 streaming path)
+    uint16_t *mel_hi, *mel_lo; // bf16 planes of mel_in (tensor-core conv stem)
+    uint16_t *c0_hi, *c0_lo;   // bf16 planes of c0
 };

@@ -21,6 +21,7 @@
 //            overlapping the next tile's main loop (double-buffered TMEM).
 #include "vox_internal.h"
 #include "gemm_tc.h"
+#include "tc_ptx.cuh"
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include <string.h>
@@ -106,6 +107,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 struct KParams {
+    int lo_sep;             // 1: the lo half of A is a separate array with its own tensor map (overlapping rows)
     int M, N, K, Kw;        // K = walked A columns (Kw or 2*Kw), Kw = weight columns
     long split_off;
     float *out_f32;
@@ -181,6 +183,7 @@ __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col,
 
 template <int BN>
 __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                        const __grid_constant__ CUtensorMap tmAlo,
                                                         const __grid_constant__ CUtensorMap tmB, const KParams p) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -210,10 +213,12 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
     const int total = tiles_n * tiles_m, nkb = p.Kw / BK;
     const bool split = p.K != p.Kw;                         // A rows are [hi(Kw) | lo(Kw)]
 
+    tcx::pdl_launch_dependents();                           // the next kernel may run its prologue now
     if (warp == 0) {
         if (lane == 0) {
             int s = 0; unsigned ph = 0;
             const unsigned tx = (split ? 2 : 1) * A_BYTES + C::B_BYTES;
+            tcx::pdl_wait();                                // A is produced by the previous kernel
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
                 for (int kb = 0; kb < nkb; kb++) {
@@ -221,7 +226,10 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
                     mb_wait(&empty[s], ph ^ 1u);
                     mb_expect_tx(&full[s], tx);
                     tma_2d(st, &tmA, kb * BK, m0, &full[s]);
-                    if (split) tma_2d(st + A_BYTES, &tmA, p.Kw + kb * BK, m0, &full[s]);
+                    if (split) {
+                        if (p.lo_sep) tma_2d(st + A_BYTES, &tmAlo, kb * BK, m0, &full[s]);
+                        else tma_2d(st + A_BYTES, &tmA, p.Kw + kb * BK, m0, &full[s]);
+                    }
                     tma_2d(st + 2 * A_BYTES, &tmB, kb * BK, n0, &full[s]);
                     if (++s == C::STAGES) { s = 0; ph ^= 1u; }
                 }
@@ -260,6 +268,7 @@ __global__ void __launch_bounds__(NT, 1) gemm_tc_kernel(const __grid_constant__ 
     } else {
         const int q = warp & 3;                             // TMEM lane quarter this warp may access
         int it = 0;
+        tcx::pdl_wait();                                    // outputs (and the residual read) order after earlier kernels
         for (int t = blockIdx.x; t < total; t += gridDim.x, it++) {
             const int as = it & 1;
             const unsigned aph = (unsigned)(it >> 1) & 1u;
@@ -326,28 +335,66 @@ static int make_map(CUtensorMap *m, const uint16_t *ptr, int rows, int K, long l
     return 0;
 }
 
-int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, long lda, const uint16_t *W,
-            const TcEpilogue &epi) {
+static int gemm_tc_impl(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, const uint16_t *A_lo, long lda,
+                        const uint16_t *W, const TcEpilogue &epi) {
     if (M <= 0) return 0;
     if (tc_init()) return -1;
-    if ((KA != K && KA != 2 * K) || N % 128 || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15)) {
+    if ((KA != K && KA != 2 * K) || N % 128 || K % tc::BK || (lda * 2) % 16 || ((uintptr_t)A & 15) || ((uintptr_t)W & 15) ||
+        ((uintptr_t)A_lo & 15)) {
         vox_set_error("gemm_tc: unsupported shape M=%d N=%d K=%d lda=%ld", M, N, K, lda);
         return -1;
     }
     static int force128 = -1;
     if (force128 < 0) { const char *e = getenv("VOX_CUDA_TC_BN128"); force128 = (e && atoi(e)) ? 1 : 0; }
-    // wide tiles only when they still fill the machine (small-M calls stream weights: more CTAs matter more)
-    const int BN = (N % 256 == 0 && !force128 && (N / 256) * ((M + tc::BM - 1) / tc::BM) >= 100) ? 256 : 128;
-    CUtensorMap ma, mb;
-    if (make_map(&ma, A, M, KA, lda, tc::BM) || make_map(&mb, W, N, K, K, BN)) return -1;
+    // 256-wide tiles carry twice the work of 128-wide ones at better operand reuse: take them unless the
+    // machine then needs more rounds of tiles than it saves (small-M calls stream weights: more CTAs matter more)
+    const int mt = (M + tc::BM - 1) / tc::BM;
+    const int t256 = (N / 256) * mt, t128 = (N / 128) * mt;
+    const int r256 = (t256 + g_sms - 1) / g_sms, r128 = (t128 + g_sms - 1) / g_sms;
+    const int BN = (N % 256 == 0 && !force128 && t256 >= 64 && 2 * r256 <= r128) ? 256 : 128;
+    CUtensorMap ma, mlo, mb;
+    if (make_map(&ma, A, M, A_lo ? K : KA, lda, tc::BM) || make_map(&mb, W, N, K, K, BN)) return -1;
+    if (A_lo) { if (make_map(&mlo, A_lo, M, K, lda, tc::BM)) return -1; }
+    else mlo = ma;
     tc::KParams p;
+    p.lo_sep = A_lo ? 1 : 0;
     p.M = M; p.N = N; p.K = KA; p.Kw = K; p.split_off = epi.split_off;
     p.out_f32 = epi.out_f32; p.ldo_f32 = epi.ldo_f32; p.out_bf16 = epi.out_bf16; p.ldo_bf16 = epi.ldo_bf16;
     p.bias = epi.bias; p.flags = epi.flags;
-    const int total = (N / BN) * ((M + tc::BM - 1) / tc::BM);
+    const int total = (N / BN) * mt;
     const int grid = total < g_sms ? total : g_sms;
-    if (BN == 256) tc::gemm_tc_kernel<256><<<grid, tc::NT, tc::Cfg<256>::SMEM_BYTES, st>>>(ma, mb, p);
-    else tc::gemm_tc_kernel<128><<<grid, tc::NT, tc::Cfg<128>::SMEM_BYTES, st>>>(ma, mb, p);
+    if (BN == 256) CUDA_TRY(launch_pdl(tc::gemm_tc_kernel<256>, grid, tc::NT, tc::Cfg<256>::SMEM_BYTES, st, ma, mlo, mb, p));
+    else CUDA_TRY(launch_pdl(tc::gemm_tc_kernel<128>, grid, tc::NT, tc::Cfg<128>::SMEM_BYTES, st, ma, mlo, mb, p));
+    LAUNCHED();
+    return 0;
+}
+
+int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, long lda, const uint16_t *W,
+            const TcEpilogue &epi) {
+    return gemm_tc_impl(st, M, N, K, KA, A, nullptr, lda, W, epi);
+}
+
+// split activations as two planes (hi and lo arrays of identical shape): rows may overlap (lda < K), which is how
+// the causal convolutions read their [3 x channels] windows without an im2col copy
+int gemm_tc_planes(cudaStream_t st, int M, int N, int K, const uint16_t *A_hi, const uint16_t *A_lo, long lda,
+                   const uint16_t *W, const TcEpilogue &epi) {
+    if (!A_lo) return -1;
+    return gemm_tc_impl(st, M, N, K, 2 * K, A_hi, A_lo, lda, W, epi);
+}
+
+// fp32 -> two bf16 planes (hi = rn(x), lo = rn(x - hi)), elementwise
+__global__ void f32_to_bf16_planes_kernel(const float *__restrict__ in, uint16_t *__restrict__ hi, uint16_t *__restrict__ lo, size_t n2) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n2) return;
+    const float2 v = reinterpret_cast<const float2 *>(in)[i];
+    const uint32_t h = tc::pack_bf16(v.x, v.y);
+    reinterpret_cast<uint32_t *>(hi)[i] = h;
+    reinterpret_cast<uint32_t *>(lo)[i] = tc::pack_bf16(v.x - bf16_lo(h), v.y - bf16_hi(h));
+}
+int f32_to_bf16_planes(cudaStream_t st, const float *in, uint16_t *hi, uint16_t *lo, size_t n) {
+    if (!n) return 0;
+    if (n & 1) { vox_set_error("f32_to_bf16_planes: odd element count"); return -1; }
+    f32_to_bf16_planes_kernel<<<(unsigned)((n / 2 + 255) / 256), 256, 0, st>>>(in, hi, lo, n / 2);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return 0;

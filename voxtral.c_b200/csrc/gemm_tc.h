@@ -34,3 +34,9 @@ int gemm_tc(cudaStream_t st, int M, int N, int K, int KA, const uint16_t *A, lon
             const TcEpilogue &epi);
 // fp32 -> bf16 rows; split != 0 writes [hi | lo] rows of 2*cols
 int f32_to_bf16_rows(cudaStream_t st, const float *in, long ldi, uint16_t *out, long ldo, int rows, int cols, int split);
+// Same product with the split activations as two planes (A_hi, A_lo: identical shape and row stride); rows may
+// overlap (lda < K) - the causal convolutions read their [3 x channels] windows this way, no im2col copy.
+int gemm_tc_planes(cudaStream_t st, int M, int N, int K, const uint16_t *A_hi, const uint16_t *A_lo, long lda,
+                   const uint16_t *W, const TcEpilogue &epi);
+// fp32 -> two bf16 planes (hi = rn(x), lo = rn(x - hi)); n even
+int f32_to_bf16_planes(cudaStream_t st, const float *in, uint16_t *hi, uint16_t *lo, size_t n);

@@ -2,6 +2,7 @@
 // RMSNorm, RoPE + KV-ring append, sliding-window causal attention, SwiGLU.
 #include "vox_internal.h"
 #include "rows.h"
+#include "tc_ptx.cuh"
 
 // ---- RMSNorm over rows (voxtral_kernels.c:475-492), optional (1+ada) ----------
 __global__ void __launch_bounds__(256) rows_rmsnorm_kernel(
@@ -30,6 +31,8 @@ __global__ void __launch_bounds__(256) rows_rmsnorm_kernel(
 __global__ void __launch_bounds__(256) rows_rmsnorm_bf16_kernel(
     const float *__restrict__ x, long ldx, const float *__restrict__ w, const float *__restrict__ ada,
     uint16_t *__restrict__ out, long ldo, int dim, int split) {
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     const float *xr = x + (size_t)blockIdx.x * ldx;
     uint16_t *orow = out + (size_t)blockIdx.x * ldo;
     __shared__ float red[8];
@@ -56,9 +59,8 @@ __global__ void __launch_bounds__(256) rows_rmsnorm_bf16_kernel(
 int rows_rmsnorm_bf16(cudaStream_t st, const float *x, long ldx, const float *w, const float *ada, uint16_t *out,
                       long ldo, int rows, int dim, int split) {
     if (rows <= 0) return 0;
-    rows_rmsnorm_bf16_kernel<<<rows, 256, 0, st>>>(x, ldx, w, ada, out, ldo, dim, split);
+    CUDA_TRY(launch_pdl(rows_rmsnorm_bf16_kernel, rows, 256, 0, st, x, ldx, w, ada, out, ldo, dim, split));
     LAUNCHED();
-    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 
@@ -79,6 +81,8 @@ __global__ void __launch_bounds__(256) rows_rope_kv_kernel(
     float *__restrict__ qkv, int q_dim, int kv_dim, int head_dim,
     const float *__restrict__ inv_freq, int pos0, int ring_mask,
     float *__restrict__ kc, float *__restrict__ vc) {
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     const int row = blockIdx.x;
     const int ld = q_dim + 2 * kv_dim;
     float *r = qkv + (size_t)row * ld;
@@ -103,10 +107,8 @@ __global__ void __launch_bounds__(256) rows_rope_kv_kernel(
 int rows_rope_kv(cudaStream_t st, float *qkv, int rows, int q_dim, int kv_dim, int head_dim,
                  const float *inv_freq, int pos0, int ring_mask, float *kc, float *vc) {
     if (rows <= 0) return 0;
-    rows_rope_kv_kernel<<<rows, 256, 0, st>>>(qkv, q_dim, kv_dim, head_dim, inv_freq, pos0,
-                                              ring_mask, kc, vc);
+    CUDA_TRY(launch_pdl(rows_rope_kv_kernel, rows, 256, 0, st, qkv, q_dim, kv_dim, head_dim, inv_freq, pos0, ring_mask, kc, vc));
     LAUNCHED();
-    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 
