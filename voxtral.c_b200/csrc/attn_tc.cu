@@ -73,10 +73,12 @@ __device__ __forceinline__ void load_tile(uint16_t *s_hi, uint16_t *s_lo, float 
 template <int TERMS>
 __global__ void __launch_bounds__(NT) enc_attn_kernel(
     const float *__restrict__ qkv, long ldq, const float *__restrict__ kc, const float *__restrict__ vc,
-    int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split) {
+    int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split,
+    const int *__restrict__ pos_dev) {
     extern __shared__ __align__(16) uint16_t sm[];
     tcx::pdl_launch_dependents();
     tcx::pdl_wait();
+    if (pos_dev) pos0 = *pos_dev;                 // replayed CUDA graphs keep the position in device memory
     uint16_t *Qh = sm, *Ql = sm + TILE, *Kh = sm + 2 * TILE, *Kl = sm + 3 * TILE, *Vh = sm + 4 * TILE, *Vl = sm + 5 * TILE;
     const int head = blockIdx.y, q0 = blockIdx.x * BQ;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -226,8 +228,15 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
 }  // namespace at
 
 // qkv: fp32 [M][3*2048] (q rotated in place by rows_rope_kv); kc / vc: this layer's fp32 ring.
+int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                      uint16_t *out_b, long ldo, int split, const int *pos_dev);
 int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                   uint16_t *out_b, long ldo, int split) {
+    return enc_attention_dev(s, qkv, kc, vc, M, pos0, out_b, ldo, split, nullptr);
+}
+// pos_dev (optional): device int holding pos0 (tensor-core path only)
+int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                      uint16_t *out_b, long ldo, int split, const int *pos_dev) {
     EncState *e = (EncState *)s->enc_priv;
     cudaStream_t st = s->stream;
     static int mode = -1;     // 0: tensor cores, 1: fp32 CUDA-core kernel + conversion (A/B debugging)
@@ -238,6 +247,7 @@ int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const fl
         cudaFuncSetAttribute(at::enc_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM_BYTES);
     }
     if (mode == 1) {
+        if (pos_dev) { vox_set_error("enc_attention: device position needs the tensor-core path"); return -1; }
         if (rows_attention(st, ENC_HD, qkv, 3 * ENC_QKV, kc, vc, ENC_QKV, ENC_RING - 1, ENC_HEADS, 1, M, pos0, 0,
                            ENC_WINDOW, e->att, ENC_QKV)) return -1;
         return f32_to_bf16_rows(st, e->att, ENC_QKV, out_b, ldo, M, ENC_QKV, split);
@@ -245,10 +255,10 @@ int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const fl
     dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
     if (split)
         CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
-                            ENC_RING - 1, out_b, ldo, 1));
+                            ENC_RING - 1, out_b, ldo, 1, pos_dev));
     else
         CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
-                            ENC_RING - 1, out_b, ldo, 0));
+                            ENC_RING - 1, out_b, ldo, 0, pos_dev));
     LAUNCHED();
     return 0;
 }

@@ -21,6 +21,8 @@
 // attn_tc.cu: sliding-window attention on tensor cores, output [hi | lo] bf16 rows
 int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                   uint16_t *out_b, long ldo, int split);
+int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                      uint16_t *out_b, long ldo, int split, const int *pos_dev);
 
 void vox_mem_account(long delta);
 
@@ -159,7 +161,8 @@ __global__ void __launch_bounds__(256) enc_sum_bias_kernel(const float *__restri
 
 // x[m] += sum_s part[s][m] + bias; then RMSNorm(x[m]) * w -> split bf16 row (out_b) or fp32 row (out_f)
 // (wo / w2 + bias + residual, voxtral_encoder.c:644-646,677-679, followed by the next norm :562-566,652-656)
-__global__ void __launch_bounds__(320) enc_resid_norm_kernel(float *__restrict__ x, const float *__restrict__ part, int ks, long stride,
+template <int KS>
+__global__ void __launch_bounds__(320) enc_resid_norm_kernel(float *__restrict__ x, const float *__restrict__ part, long stride,
                                                              const float *__restrict__ bias, const float *__restrict__ w,
                                                              uint16_t *__restrict__ out_b, float *__restrict__ out_f) {
     tcx::pdl_launch_dependents();
@@ -170,10 +173,11 @@ __global__ void __launch_bounds__(320) enc_resid_norm_kernel(float *__restrict__
     const float4 b = *reinterpret_cast<const float4 *>(bias + col);
     float4 acc = b;
     const float *p = part + (size_t)m * ENC_DIM + col;
-    for (int s = 0; s < ks; s++) {
-        const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-    }
+    float4 v[KS];
+    #pragma unroll
+    for (int s = 0; s < KS; s++) v[s] = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);   // all loads in flight
+    #pragma unroll
+    for (int s = 0; s < KS; s++) { acc.x += v[s].x; acc.y += v[s].y; acc.z += v[s].z; acc.w += v[s].w; }
     a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += acc.w;
     *reinterpret_cast<float4 *>(xr + col) = a;
     __shared__ float red[10];
@@ -200,10 +204,16 @@ __global__ void __launch_bounds__(320) enc_resid_norm_kernel(float *__restrict__
     }
 }
 
+constexpr int SM_GRAPHS = 16;
 struct EncSmall {
     uint16_t *xn_t, *att_t, *hh_t;      // [128][2*1280], [128][2*2048], [128][2*5120] split bf16 rows
     float *part;                        // K-range partials, max(14*128*1280, 3*128*6144) floats
     WtOp *ops[3];                       // per NB in {32, 64, 128}: [n_enc][4] prepared products (lazily)
+    // The call is launch bound on the host (~290 launches); a chunk shape seen twice is captured into a CUDA
+    // graph (position in device memory) and replayed.  Key = (M, x, out).
+    int *d_pos, *h_pos;                 // device position + pinned staging ring
+    unsigned h_pos_i;
+    struct { int M, seen; const float *x, *out; cudaGraphExec_t exec; } graphs[SM_GRAPHS];
 };
 
 }  // namespace
@@ -211,7 +221,9 @@ struct EncSmall {
 void enc_small_free(void *p) {
     EncSmall *q = (EncSmall *)p;
     if (!q) return;
-    cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part);
+    cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part); cudaFree(q->d_pos);
+    if (q->h_pos) cudaFreeHost(q->h_pos);
+    for (int i = 0; i < SM_GRAPHS; i++) if (q->graphs[i].exec) cudaGraphExecDestroy(q->graphs[i].exec);
     for (int i = 0; i < 3; i++) free(q->ops[i]);
     free(q);
 }
@@ -233,6 +245,11 @@ static EncSmall *small_get(vox_cuda_state *s, int NB) {
                 enc_small_free(q);
                 return nullptr;
             }
+        }
+        if (cudaMalloc((void **)&q->d_pos, 4) != cudaSuccess || cudaMallocHost((void **)&q->h_pos, 64 * 4) != cudaSuccess) {
+            vox_set_error("enc_small: position buffers alloc failed");
+            enc_small_free(q);
+            return nullptr;
         }
         e->small = q;
     }
@@ -260,19 +277,12 @@ static EncSmall *small_get(vox_cuda_state *s, int NB) {
     return q;
 }
 
-// M <= 128 new positions: same layer arithmetic as enc_layers_fast (split-bf16 operands, fp32 accumulation)
-int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
+// the 32 layers for M <= 128 rows; pos_dev: device position (graph capture) or null (pos0 by value)
+static int small_enqueue(vox_cuda_state *s, EncSmall *q, WtOp *ops, float *x, int M, float *out, int pos0, const int *pos_dev) {
     EncState *e = (EncState *)s->enc_priv;
-    if (!split_mode()) return enc_layers_fast(s, x, M, out);    // single-bf16 A/B mode lives on the large-tile path
-    if (!fast_get(s)) return -1;
-    const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
-    EncSmall *q = small_get(s, NB);
-    if (!q) return -1;
-    WtOp *ops = q->ops[NB == 32 ? 0 : (NB == 64 ? 1 : 2)];
     vox_cuda_model *m = s->m;
     cudaStream_t st = s->stream;
     const size_t kv_layer = (size_t)ENC_RING * ENC_QKV;
-    const int pos0 = e->pos;
     if (rows_rmsnorm_bf16(st, x, ENC_DIM, m->enc[0].attn_norm, nullptr, q->xn_t, 2 * ENC_DIM, M, ENC_DIM, 1)) return -1;
     for (int l = 0; l < m->n_enc; l++) {
         const EncLayerDev &L = m->enc[l];
@@ -284,19 +294,69 @@ int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
         CUDA_TRY(launch_pdl(enc_sum_bias_kernel, dim3(M, (3 * ENC_QKV + 1023) / 1024), 256, 0, st, (const float *)q->part, SM_KS_QKV,
                             (long)M * 3 * ENC_QKV, L.bqkv, e->qkv, 3 * ENC_QKV));
         LAUNCHED();
-        if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
-        if (enc_attention(s, e->qkv, kc, vc, M, pos0, q->att_t, 2 * ENC_QKV, 1)) return -1;
+        if (rows_rope_kv_dev(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc, pos_dev)) return -1;
+        if (enc_attention_dev(s, e->qkv, kc, vc, M, pos0, q->att_t, 2 * ENC_QKV, 1, pos_dev)) return -1;
         if (gemm_wt_launch(st, &o[1])) return -1;
-        CUDA_TRY(launch_pdl(enc_resid_norm_kernel, M, 320, 0, st, x, (const float *)q->part, SM_KS_WO, (long)M * ENC_DIM, L.bo, L.ffn_norm,
+        CUDA_TRY(launch_pdl(enc_resid_norm_kernel<SM_KS_WO>, M, 320, 0, st, x, (const float *)q->part, (long)M * ENC_DIM, L.bo, L.ffn_norm,
                             q->xn_t, (float *)nullptr));
         LAUNCHED();
         if (gemm_wt_launch(st, &o[2])) return -1;
         if (gemm_wt_launch(st, &o[3])) return -1;
         const bool last = l == m->n_enc - 1;
-        CUDA_TRY(launch_pdl(enc_resid_norm_kernel, M, 320, 0, st, x, (const float *)q->part, SM_KS_W2, (long)M * ENC_DIM, L.b2,
+        CUDA_TRY(launch_pdl(enc_resid_norm_kernel<SM_KS_W2>, M, 320, 0, st, x, (const float *)q->part, (long)M * ENC_DIM, L.b2,
                             last ? m->enc_norm : m->enc[l + 1].attn_norm, last ? (uint16_t *)nullptr : q->xn_t, last ? out : (float *)nullptr));
         LAUNCHED();
     }
+    return 0;
+}
+
+static int small_graph_mode(void) {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("VOX_CUDA_ENC_GRAPH"); v = (e && !atoi(e)) ? 0 : 1; }
+    return v;
+}
+
+// M <= 128 new positions: same layer arithmetic as enc_layers_fast (split-bf16 operands, fp32 accumulation)
+int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
+    EncState *e = (EncState *)s->enc_priv;
+    if (!split_mode()) return enc_layers_fast(s, x, M, out);    // single-bf16 A/B mode lives on the large-tile path
+    if (!fast_get(s)) return -1;
+    const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+    EncSmall *q = small_get(s, NB);
+    if (!q) return -1;
+    WtOp *ops = q->ops[NB == 32 ? 0 : (NB == 64 ? 1 : 2)];
+    cudaStream_t st = s->stream;
+    const int pos0 = e->pos;
+    int slot = -1;
+    if (small_graph_mode()) {
+        for (int i = 0; i < SM_GRAPHS; i++)
+            if (q->graphs[i].seen && q->graphs[i].M == M && q->graphs[i].x == x && q->graphs[i].out == out) { slot = i; break; }
+        if (slot < 0)
+            for (int i = 0; i < SM_GRAPHS; i++)
+                if (!q->graphs[i].seen) { q->graphs[i].M = M; q->graphs[i].x = x; q->graphs[i].out = out; q->graphs[i].seen = 1; break; }
+        // first sighting of a shape runs eagerly (slot stays -1); the second one is captured
+    }
+    if (slot >= 0) {
+        int *hp = q->h_pos + (q->h_pos_i++ & 63);
+        *hp = pos0;
+        CUDA_TRY(cudaMemcpyAsync(q->d_pos, hp, 4, cudaMemcpyHostToDevice, st));
+        if (!q->graphs[slot].exec) {
+            cudaGraph_t graph = nullptr;
+            CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            const int rc = small_enqueue(s, q, ops, x, M, out, 0, q->d_pos);
+            const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (rc || ce != cudaSuccess || !graph) {
+                if (graph) cudaGraphDestroy(graph);
+                vox_set_error("enc_small: graph capture failed (%s)", cudaGetErrorString(ce));
+                return -1;
+            }
+            const cudaError_t ie = cudaGraphInstantiate(&q->graphs[slot].exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ie != cudaSuccess) { vox_set_error("enc_small: graph instantiate failed (%s)", cudaGetErrorString(ie)); return -1; }
+        }
+        CUDA_TRY(cudaGraphLaunch(q->graphs[slot].exec, st));
+        LAUNCHED();
+    } else if (small_enqueue(s, q, ops, x, M, out, pos0, nullptr)) return -1;
     e->pos += M;
     return 0;
 }

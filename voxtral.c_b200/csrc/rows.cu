@@ -80,34 +80,40 @@ int rows_rmsnorm(cudaStream_t st, const float *x, long ldx, const float *w, cons
 __global__ void __launch_bounds__(256) rows_rope_kv_kernel(
     float *__restrict__ qkv, int q_dim, int kv_dim, int head_dim,
     const float *__restrict__ inv_freq, int pos0, int ring_mask,
-    float *__restrict__ kc, float *__restrict__ vc) {
+    float *__restrict__ kc, float *__restrict__ vc, const int *__restrict__ pos_dev) {
     tcx::pdl_launch_dependents();
     tcx::pdl_wait();
+    if (pos_dev) pos0 = *pos_dev;
     const int row = blockIdx.x;
     const int ld = q_dim + 2 * kv_dim;
     float *r = qkv + (size_t)row * ld;
     const int pos = pos0 + row;
     const size_t slot = (size_t)(pos & ring_mask) * kv_dim;
     const int half = head_dim >> 1;
-    const int npairs = (q_dim + kv_dim) >> 1;
-    for (int pr = threadIdx.x; pr < npairs; pr += 256) {
-        const int col = pr * 2;
-        const int d = (col % head_dim) >> 1;
-        (void)half;
-        const float angle = (float)pos * inv_freq[d];
-        const float c = cosf(angle), s = sinf(angle);
-        const float x0 = r[col], x1 = r[col + 1];
-        const float y0 = x0 * c - x1 * s, y1 = x0 * s + x1 * c;
-        if (col < q_dim) { r[col] = y0; r[col + 1] = y1; }
-        else { kc[slot + col - q_dim] = y0; kc[slot + col - q_dim + 1] = y1; }
+    // thread -> pair index d inside a head (one cosf/sinf per thread), then a stride over the q and k heads
+    const int d = threadIdx.x % half, hg = threadIdx.x / half, hstep = 256 / half;
+    const float angle = (float)pos * inv_freq[d];
+    const float c = cosf(angle), s = sinf(angle);
+    const int n_heads = (q_dim + kv_dim) / head_dim;
+    for (int h = hg; h < n_heads; h += hstep) {
+        const int col = h * head_dim + 2 * d;
+        const float2 x = *reinterpret_cast<const float2 *>(r + col);
+        const float y0 = x.x * c - x.y * s, y1 = x.x * s + x.y * c;
+        if (col < q_dim) *reinterpret_cast<float2 *>(r + col) = make_float2(y0, y1);
+        else *reinterpret_cast<float2 *>(kc + slot + col - q_dim) = make_float2(y0, y1);
     }
-    for (int i = threadIdx.x; i < kv_dim; i += 256) vc[slot + i] = r[q_dim + kv_dim + i];
+    for (int i = threadIdx.x * 4; i < kv_dim; i += 1024)
+        *reinterpret_cast<float4 *>(vc + slot + i) = *reinterpret_cast<const float4 *>(r + q_dim + kv_dim + i);
 }
 
 int rows_rope_kv(cudaStream_t st, float *qkv, int rows, int q_dim, int kv_dim, int head_dim,
                  const float *inv_freq, int pos0, int ring_mask, float *kc, float *vc) {
+    return rows_rope_kv_dev(st, qkv, rows, q_dim, kv_dim, head_dim, inv_freq, pos0, ring_mask, kc, vc, nullptr);
+}
+int rows_rope_kv_dev(cudaStream_t st, float *qkv, int rows, int q_dim, int kv_dim, int head_dim,
+                     const float *inv_freq, int pos0, int ring_mask, float *kc, float *vc, const int *pos_dev) {
     if (rows <= 0) return 0;
-    CUDA_TRY(launch_pdl(rows_rope_kv_kernel, rows, 256, 0, st, qkv, q_dim, kv_dim, head_dim, inv_freq, pos0, ring_mask, kc, vc));
+    CUDA_TRY(launch_pdl(rows_rope_kv_kernel, rows, 256, 0, st, qkv, q_dim, kv_dim, head_dim, inv_freq, pos0, ring_mask, kc, vc, pos_dev));
     LAUNCHED();
     return 0;
 }
