@@ -82,6 +82,7 @@ typedef struct {
 typedef struct vox_cuda_model vox_cuda_model_t;   /* weights in HBM, shared by streams */
 typedef struct vox_cuda_state vox_cuda_state_t;   /* one stream's device state */
 typedef struct vox_cuda_group vox_cuda_group_t;   /* B streams decoded in lock step (one weight pass per step) */
+typedef struct vox_cuda_tp vox_cuda_tp_t;         /* one stream decoded by G ranks (tensor-parallel decoder step) */
 
 /* ---- lifetime (replaces vox_metal_init/available/shutdown,
  *      voxtral_metal.h:20-26, call sites main.c:181-183,407-409) ---------- */
@@ -268,6 +269,43 @@ int vox_cuda_sgemm_bf16(vox_cuda_model_t *m, int M, int N, int K, const float *A
 #define VOX_CUDA_TC_SPLIT_A   128  /* A = hi + lo (two bf16 terms): fp32-class accuracy, 2x tensor work */
 int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const uint16_t *B_bf16,
                           const float *bias, int flags, float *C);
+
+/* ---- tensor-parallel single-stream decoder (csrc/dec_tp.cu) ----------
+ * vox_decoder_forward (voxtral_decoder.c:640-780) cut across G = 1/2/4/8 GPUs, one
+ * process per GPU: rank r owns kv heads [r*8/G, ...) with their query heads (rows of
+ * wq|wk|wv), rows of w1|w3, the matching column range of wo and w2, and a vocabulary
+ * slice of the logits.  Weights stay replicated (the shard is a view of the model this
+ * process already holds).  The sums after wo and w2 and the greedy (max, index) pairs are
+ * exchanged by the GEMV kernels themselves, which store into every peer's exchange window
+ * over NVLink (CUDA IPC peer memory) and publish a sequence number; the next kernel's
+ * prologue waits and adds the G partials in rank order, so all ranks hold identical rows.
+ * The reference has no multi-device path; this is the north star's optional TP decoder.
+ *
+ *   tp = vox_cuda_tp_create(model, rank, world);  vox_cuda_tp_export(tp, my_handle);
+ *   ... all-gather the handles between the processes (any transport) ...
+ *   vox_cuda_tp_connect(tp, all_handles);
+ *   s = vox_cuda_tp_state(tp);   encode + prefill s on EVERY rank with the usual calls
+ *   vox_cuda_tp_decode(tp, prev_token, adapter_index, n, ids, &ms);   (all ranks together)
+ * Before vox_cuda_tp_free every rank must have returned from its last decode (the peers
+ * write into the window being freed): put a barrier between them.
+ * After a TP decode the state's K/V ring holds only this rank's kv heads for the decoded
+ * positions: keep decoding it through vox_cuda_tp_decode. */
+#define VOX_CUDA_TP_MAX 8
+#define VOX_CUDA_TP_HANDLE_BYTES 80
+vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int world);
+/* all `world` ranks on THIS device, run kernel by kernel in lock step: checks the shard
+ * arithmetic and the exchange protocol on one GPU (not a fast path) */
+vox_cuda_tp_t *vox_cuda_tp_create_local(vox_cuda_model_t *m, int world);
+int  vox_cuda_tp_export(vox_cuda_tp_t *tp, void *handle_out /* VOX_CUDA_TP_HANDLE_BYTES */);
+int  vox_cuda_tp_connect(vox_cuda_tp_t *tp, const void *handles /* world x VOX_CUDA_TP_HANDLE_BYTES, rank order */);
+vox_cuda_state_t *vox_cuda_tp_state(vox_cuda_tp_t *tp);
+/* same contract as vox_cuda_decoder_run; ms_per_step (may be NULL) = CUDA-event time / n */
+int  vox_cuda_tp_decode(vox_cuda_tp_t *tp, int prev_token, int adapter_index, int n, int *tokens_out,
+                        float *ms_per_step);
+/* vox_cuda_transcribe with the greedy steps tensor-parallel (encoder + prefill replicated per rank) */
+int  vox_cuda_tp_transcribe(vox_cuda_tp_t *tp, const float *pcm, int n_samples, int n_frames,
+                            int prompt_len, int *tokens_out, int max_tokens, float *ms_per_step);
+void vox_cuda_tp_free(vox_cuda_tp_t *tp);
 
 /* ---- measurement helpers (bench.py / profiles) ------------------------ */
 /* vox_cuda_decoder_run timed with CUDA events on the launch stream: returns

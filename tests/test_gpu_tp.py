@@ -1,0 +1,99 @@
+"""Tensor-parallel single-stream decoder (csrc/dec_tp.cu) through the C ABI.
+
+One GPU: all G ranks on the device in lock step (vox_cuda_tp_create_local) - the shard arithmetic, the
+exchange windows and the sequence numbers are those of the multi-GPU run.  Greedy ids must equal the
+single-stream path, whose ids on this 2 s clip tests/test_gpu_golden.py pins to the reference BLAS path;
+logits within the north star's 2e-2 max-abs (summation order is the only difference).
+Two or more GPUs: tools/tp_probe.py under torchrun (one process per GPU, CUDA IPC windows over NVLink)."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+def _clip(seconds, seed):
+    import test_gpu_parity as tp
+    import vox_oracle as vo
+    x = tp.synth_audio(int(16000 * seconds), seed=seed)
+    return vo.stream_buffer(x)
+
+
+def _single(e, buf, nf):
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        toks = np.empty(nf // 8 + 8, np.int32)
+        n = e.L.vox_cuda_transcribe(st, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n > 0, e.vc.last_error()
+        logits = np.empty(131072, np.float32)
+        assert e.L.vox_cuda_decoder_read_logits(st, e.vc.fptr(logits)) == 0
+        return toks[:n].tolist(), logits
+    finally:
+        e.L.vox_cuda_state_free(st)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_tp_lockstep_ids_equal_single_stream(full_env, world):
+    e = full_env
+    buf, nf = _clip(2.0, 5)
+    want, want_logits = _single(e, buf, nf)
+    tp = e.L.vox_cuda_tp_create_local(e.model, world)
+    assert tp, e.vc.last_error()
+    try:
+        toks = np.empty(nf // 8 + 8, np.int32)
+        ms = C.c_float(0)
+        n = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), C.byref(ms))
+        assert n == len(want), e.vc.last_error()
+        assert toks[:n].tolist() == want
+        # in lock step the ranks share one logits buffer, each writing its vocabulary slice
+        logits = np.empty(131072, np.float32)
+        assert e.L.vox_cuda_decoder_read_logits(e.L.vox_cuda_tp_state(tp), e.vc.fptr(logits)) == 0
+        assert float(np.abs(logits - want_logits).max()) < 2e-2
+        # a second clip on the same handle: sequence numbers keep counting, state resets cleanly
+        buf2, nf2 = _clip(2.4, 12)
+        want2, _ = _single(e, buf2, nf2)
+        n2 = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf2), len(buf2), nf2, 39, e.vc.iptr(toks), len(toks), None)
+        assert n2 == len(want2), e.vc.last_error()
+        assert toks[:n2].tolist() == want2
+    finally:
+        e.L.vox_cuda_tp_free(tp)
+
+
+def test_tp_argument_errors(full_env):
+    e = full_env
+    assert not e.L.vox_cuda_tp_create_local(e.model, 3)
+    assert not e.L.vox_cuda_tp_create(e.model, 2, 2)
+    tp = e.L.vox_cuda_tp_create(e.model, 0, 2)
+    assert tp, e.vc.last_error()
+    try:
+        toks = np.empty(8, np.int32)
+        # peers never attached: decode must refuse instead of waiting for them
+        assert e.L.vox_cuda_tp_decode(tp, 32, 38, 1, e.vc.iptr(toks), None) == -1
+        h = (C.c_ubyte * e.vc.TP_HANDLE_BYTES)()
+        assert e.L.vox_cuda_tp_export(tp, h) == 0, e.vc.last_error()
+        bad = (C.c_ubyte * (2 * e.vc.TP_HANDLE_BYTES))()
+        assert e.L.vox_cuda_tp_connect(tp, bad) == -1
+    finally:
+        e.L.vox_cuda_tp_free(tp)
+
+
+def test_tp_two_processes_two_gpus(full_env):
+    """One process per GPU, windows mapped through CUDA IPC: ids equal on both ranks and equal to the
+    single-stream run (the probe checks and prints them)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533",
+                          os.path.join(ROOT, "tools", "tp_probe.py"), "--seconds", "2", "--model", full_env.mdir],
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "ids_equal_single_stream=True" in out.stdout

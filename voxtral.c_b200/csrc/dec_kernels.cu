@@ -161,8 +161,8 @@ constexpr int ATT_T = 128;
 __global__ void __launch_bounds__(ATT_T) dec_attn_kernel(
     const DecStepParams *__restrict__ p, const float *__restrict__ q,
     const float *__restrict__ kc, const float *__restrict__ vc,
-    float *__restrict__ part) {
-    const int kvh = blockIdx.x, split = blockIdx.y;
+    float *__restrict__ part, int kvh0) {
+    const int kvh = kvh0 + blockIdx.x, split = blockIdx.y;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     __shared__ float4 qs[4][DEC_HD / 4];
     __shared__ float ps[4][ATT_T];
@@ -272,8 +272,8 @@ __global__ void __launch_bounds__(ATT_T) dec_attn_kernel(
 
 // K3: merge the split partials: out = sum_s e^{m_s-M} acc_s / sum_s e^{m_s-M} l_s
 __global__ void __launch_bounds__(DEC_HD) dec_attn_combine_kernel(
-    const float *__restrict__ part, float *__restrict__ attn) {
-    const int h = blockIdx.x, d = threadIdx.x;
+    const float *__restrict__ part, float *__restrict__ attn, int h0) {
+    const int h = h0 + blockIdx.x, d = threadIdx.x;
     float M = -INFINITY;
     #pragma unroll
     for (int s = 0; s < ATTN_NSPLIT; s++)
@@ -419,6 +419,23 @@ __global__ void __launch_bounds__(1024) dec_argmax_final_kernel(
 }
 
 // ---------------------------------------------------------------------------
+// Launchers shared with the tensor-parallel step (dec_tp.cu): the step input and
+// the attention of a contiguous range of kv heads (a rank's shard).
+// ---------------------------------------------------------------------------
+void dec_launch_embed(cudaStream_t st, const DecStepParams *p, const float *embed_in, const float *adapter,
+                      const uint16_t *tok_emb, const float *inv_freq, float *x, float *rope) {
+    dec_embed_kernel<<<1, 256, 0, st>>>(p, embed_in, adapter, tok_emb, inv_freq, x, rope);
+    LAUNCHED();
+}
+
+void dec_launch_attn(cudaStream_t st, const DecStepParams *p, const float *q, const float *kc, const float *vc,
+                     float *part, float *attn, int kvh0, int n_kvh) {
+    dec_attn_kernel<<<dim3(n_kvh, ATTN_NSPLIT), ATT_T, 0, st>>>(p, q, kc, vc, part, kvh0);
+    dec_attn_combine_kernel<<<n_kvh * (DEC_HEADS / DEC_KVH), DEC_HD, 0, st>>>(part, attn, kvh0 * (DEC_HEADS / DEC_KVH));
+    g_launch_count += 2;
+}
+
+// ---------------------------------------------------------------------------
 // Host: enqueue one decoder step (captured once into a CUDA graph by the caller)
 // ---------------------------------------------------------------------------
 int dec_launch_step(vox_cuda_state *s, cudaStream_t st) {
@@ -440,8 +457,8 @@ int dec_launch_step(vox_cuda_state *s, cudaStream_t st) {
         dec_qkv_kernel<<<DEC_QKV / QKV_ROWS_PER_CTA, QKV_WARPS * 32, 0, st>>>(
             s->d_params, s->d_x, L.attn_norm, L.wqkv, s->d_rope, s->d_q, kc, vc);
         dec_attn_kernel<<<dim3(DEC_KVH, ATTN_NSPLIT), ATT_T, 0, st>>>(
-            s->d_params, s->d_q, kc, vc, s->d_attn_part);
-        dec_attn_combine_kernel<<<DEC_HEADS, DEC_HD, 0, st>>>(s->d_attn_part, s->d_attn);
+            s->d_params, s->d_q, kc, vc, s->d_attn_part, 0);
+        dec_attn_combine_kernel<<<DEC_HEADS, DEC_HD, 0, st>>>(s->d_attn_part, s->d_attn, 0);
         dec_gemv_residual_kernel<DEC_QDIM><<<DEC_DIM / RES_ROWS_PER_CTA, RES_WARPS * 32,
                                              sizeof(XSmem<DEC_QDIM>), st>>>(s->d_attn, L.wo, s->d_x);
         dec_ffn_gate_kernel<<<2 * DEC_HIDDEN / FFN_ROWS_PER_CTA, FFN_WARPS * 32, 0, st>>>(

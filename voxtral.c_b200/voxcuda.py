@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("VOX_CUDA_LIB") or os.path.join(HERE, "libvoxcuda.so")
 
 ENC_LAYERS, DEC_LAYERS = 32, 26
 ENC_DIM, DEC_DIM, VOCAB, MEL_BINS = 1280, 3072, 131072, 128
+TP_HANDLE_BYTES = 80
 
 f32p = C.POINTER(C.c_float)
 u16p = C.POINTER(C.c_uint16)
@@ -91,6 +92,14 @@ SIGNATURES = {
     "vox_cuda_transcribe": (C.c_int, [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, i32p, C.c_int, C.POINTER(C.c_float)]),
     "vox_cuda_gemm_bf16_tc": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, f32p, C.c_int, f32p]),
     "vox_cuda_bench_decoder_steps": (C.c_float, [C.c_void_p, C.c_int, C.c_int, C.c_int, i32p]),
+    "vox_cuda_tp_create": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
+    "vox_cuda_tp_create_local": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "vox_cuda_tp_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vox_cuda_tp_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "vox_cuda_tp_state": (C.c_void_p, [C.c_void_p]),
+    "vox_cuda_tp_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_float)]),
+    "vox_cuda_tp_transcribe": (C.c_int, [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, i32p, C.c_int, C.POINTER(C.c_float)]),
+    "vox_cuda_tp_free": (None, [C.c_void_p]),
 }
 
 
