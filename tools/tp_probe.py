@@ -71,7 +71,7 @@ def main():
     if rank == 0:
         print(json.dumps({"tp_gpus": world, "clip_s": args.seconds, "steps": int(n1), "ms_per_token_tp": best,
                           "tok_per_s_tp": 1e3 / best, "ms_per_token_single_gpu": ms_single,
-                          "kernel_launches_per_token_per_rank": 1 + 6 * hm.n_dec + 3}))
+                          "kernel_launches_per_token_per_rank": 1 + 5 * hm.n_dec + 3}))
         print(f"ids_equal_single_stream={bool(eq.item())}", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if eq.item() else 1)

@@ -7,13 +7,21 @@
 // and w2 (whose products are therefore partial sums of all 3072 outputs), and vocabulary rows
 // [r*131072/G, ...) of the tied embedding.  Weights are replicated (8.86 GB of 180 GB); a shard is a view.
 //
-// The reduction after wo / w2 is not a separate collective: the GEMV epilogue stores its 16 partial rows
-// straight into every peer's exchange window over NVLink (peer memory opened through CUDA IPC), the last
-// CTA publishes a sequence number in each peer's flag word, and the NEXT kernel's prologue (the RMSNorm of
-// the FFN / of the next layer / of the logits) waits for the G flags and adds the G partials in rank order
-// - so every rank holds bit-identical residual rows and no kernel is launched for the exchange.
-// The greedy token is exchanged the same way as (max, index) pairs of the vocabulary slices.
+// The reduction after wo / w2 is not a separate collective: as soon as a warp of the GEMV kernel has a row
+// sum, lanes 0..G-1 store it into the G ranks' exchange windows over NVLink (peer memory opened through
+// CUDA IPC) as ONE 8-byte word {value, sequence number} - the flag travels inside the data (the
+// low-latency protocol NCCL calls LL), so there is no fence, no arrival counter and no flag round trip.
+// The NEXT kernel's prologue (the RMSNorm of the FFN / of the next layer / of the logits) polls the words
+// until they carry the expected sequence number and adds the G partials in rank order - every rank holds
+// bit-identical residual rows and no kernel is launched for the exchange.  The greedy token is exchanged
+// the same way as (max, index) words of the vocabulary slices.
+//
+// Every kernel is latency-bound at these sizes (a rank's share of a matrix is 2-28 MB), so: each warp
+// issues ALL weight loads of its row batch before anything else (before the programmatic-dependent-launch
+// wait and before the exchange wait, which then overlap the HBM fetch); kernels are chained with PDL;
+// attention is one kernel (key splits across CTAs, the last CTA of a kv head merges the splits).
 #include "vox_internal.h"
+#include "tc_ptx.cuh"
 #include <cuda.h>
 #include <stdlib.h>
 #include <string.h>
@@ -21,15 +29,17 @@
 constexpr int TP_MAX = VOX_CUDA_TP_MAX;   // 8
 constexpr int TP_WARPS = 8;
 constexpr int TP_THREADS = TP_WARPS * 32;
-constexpr int TP_RES_RPW = 2;                              // rows per warp of the wo / w2 partial GEMV
-constexpr int TP_RES_ROWS = TP_WARPS * TP_RES_RPW;         // 16 rows per CTA -> 192 CTAs
+constexpr int TP_ATT_SPLITS = 32;                          // max key splits per kv head of the attention kernel
+constexpr int TP_ATT_PART = DEC_HD + 4;                    // floats per (split, head) partial: acc[128], m, l, pad
 
 // One rank's exchange window.  Same layout on every rank; peers write into it, the owner only reads.
+// Every element is an 8-byte word {payload bits, sequence number of the exchange that wrote it}: 8-byte
+// aligned stores are single transactions, locally and over NVLink, so a reader that sees the sequence
+// number sees the payload.  Slots alternate with the sequence parity: a writer of exchange s can only run
+// ahead of a reader by one exchange (it needs every rank's s-1 to get there), so s-2's slot is free.
 struct TpComm {
-    float part[2][TP_MAX][DEC_DIM];   // [sequence parity][source rank][row]  partial sums of wo / w2
-    float amax[2][TP_MAX][2];         // [step parity][source rank] (max logit, index bits) of a vocabulary slice
-    unsigned flag[TP_MAX];            // flag[src] = sequence number of the last exchange src published here
-    unsigned pad[24];
+    uint2 part[2][TP_MAX][DEC_DIM];   // [sequence parity][source rank][row]  partial sums of wo / w2
+    uint2 amax[2][TP_MAX][2];         // [sequence parity][source rank] {max logit bits, seq}, {index, seq}
 };
 
 struct TpDev {                        // by-value kernel argument
@@ -37,76 +47,72 @@ struct TpDev {                        // by-value kernel argument
     int ars;                          // exchanges per step = 2 * layers + 1
     TpComm *self;
     TpComm *peer[TP_MAX];             // peer[p] = rank p's window as mapped here (peer[rank] == self)
-    unsigned *done;                   // local arrival counter of the producing kernel's CTAs
+    unsigned *done;                   // done[1 + k]: arrival counter of the attention CTAs of local kv head k
     unsigned *epoch;                  // steps completed since creation (device resident; graphs are replayed)
 };
 
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-
-// Wait until every rank has published exchange `seq` in this rank's window.  Bounded: a peer that died
-// must not leave this GPU spinning (the pool counts a hung box as a strike).
-__device__ __forceinline__ void tp_wait_all(const TpDev &td, unsigned seq) {
-    if ((int)threadIdx.x < td.world) {
-        const unsigned *f = &td.self->flag[threadIdx.x];
-        if ((int)(ld_acquire_sys(f) - seq) < 0) {
-            const unsigned long long t0 = globaltimer_ns();
-            while ((int)(ld_acquire_sys(f) - seq) < 0) {
-                __nanosleep(64);
-                if (globaltimer_ns() - t0 > 8000000000ull) {
-                    printf("vox_cuda tp: rank %d waited 8 s for rank %d, exchange %u (flag %u)\n", td.rank,
-                           (int)threadIdx.x, seq, *(volatile const unsigned *)f);
-                    __trap();
-                }
-            }
-        }
-    }
-    __syncthreads();
+// two exchange words per load / one per store; volatile = served by L2, where the peers' writes land
+__device__ __forceinline__ uint4 ld_ll2(const uint2 *p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
 }
-
-// Publish: every thread that stored into peer windows has fenced; the CTA that arrives last raises the flags.
-__device__ __forceinline__ void tp_publish(const TpDev &td, unsigned seq, unsigned n_cta) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence_system();
-        const unsigned old = atomicAdd(td.done, 1u);
-        if (old == n_cta - 1) {
-            *td.done = 0;                       // every CTA of this kernel has arrived; the next producer is a later kernel
-            __threadfence_system();
-            for (int p = 0; p < td.world; p++) st_release_sys(&td.peer[p]->flag[td.rank], seq);
-        }
+__device__ __forceinline__ void st_ll(uint2 *p, unsigned payload, unsigned seq) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(payload), "r"(seq) : "memory");
+}
+// Bounded wait: a peer that died must not leave this GPU spinning (the pool counts a hung box as a strike).
+__device__ __noinline__ void tp_timeout(int rank, int peer, unsigned seq) {
+    printf("vox_cuda tp: rank %d waited 8 s for exchange %u of rank %d\n", rank, seq, peer);
+    __trap();
+}
+// 8 consecutive values of source rank p, exchange seq: v holds a first read; spins until all 8 words carry seq
+__device__ __forceinline__ void tp_ll_settle8(const TpDev &td, const uint2 *src, int p, unsigned seq, uint4 (&v)[4]) {
+    bool ok = true;
+    #pragma unroll
+    for (int k = 0; k < 4; k++) ok = ok && v[k].y == seq && v[k].w == seq;
+    if (ok) return;
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        ok = true;
+        #pragma unroll
+        for (int k = 0; k < 4; k++) { v[k] = ld_ll2(src + 2 * k); ok = ok && v[k].y == seq && v[k].w == seq; }
+        if (ok) return;
+        if (globaltimer_ns() - t0 > 8000000000ull) tp_timeout(td.rank, p, seq);
     }
 }
 
-// y[r] = sum_k W[row r][k] * x[k] over a slice of ks columns (ks % 8 == 0); x is in shared memory as
-// A[c] = x[8c..8c+3], B[c] = x[8c+4..8c+7].  W points at the slice start of the first row.
-template <int NW>
-__device__ __forceinline__ void tp_warp_gemv(const uint16_t *__restrict__ W, size_t stride, int ks,
-                                             const float4 *xA, const float4 *xB, float (&acc)[NW]) {
+// ---- row-batch GEMV: a warp owns NW rows x NCH chunks of 256 columns, all loads issued at once ----------
+// x is in shared memory as A[c] = x[8c..8c+3], B[c] = x[8c+4..8c+7]; ks = slice length (ks % 8 == 0,
+// ks <= NCH * 256; lanes past the slice load nothing).  W points at the slice start of the batch's first row.
+template <int NW, int NCH>
+__device__ __forceinline__ void tp_wload(uint4 (&w)[NW][NCH], const uint16_t *__restrict__ W, size_t stride, int ks) {
+    const int lane = threadIdx.x & 31;
+    #pragma unroll
+    for (int j = 0; j < NCH; j++) {
+        const int col = j * 256 + lane * 8;
+        #pragma unroll
+        for (int r = 0; r < NW; r++)
+            w[r][j] = col < ks ? ldg_stream(W + (size_t)r * stride + col) : make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+template <int NW, int NCH>
+__device__ __forceinline__ void tp_wdot(const uint4 (&w)[NW][NCH], const float4 *xA, const float4 *xB, int ks, float (&acc)[NW]) {
     const int lane = threadIdx.x & 31;
     #pragma unroll
     for (int r = 0; r < NW; r++) acc[r] = 0.f;
-    const uint16_t *base = W + lane * 8;
-    #pragma unroll 4
-    for (int col = lane * 8; col < ks; col += 256) {
-        uint4 w[NW];
-        #pragma unroll
-        for (int r = 0; r < NW; r++) w[r] = ldg_stream(base + (size_t)r * stride);
-        base += 256;
-        const float4 a = xA[col >> 3], b = xB[col >> 3];
-        #pragma unroll
-        for (int r = 0; r < NW; r++) acc[r] = dot8(w[r], a, b, acc[r]);
+    #pragma unroll
+    for (int j = 0; j < NCH; j++) {
+        const int col = j * 256 + lane * 8;
+        if (col < ks) {
+            const float4 a = xA[col >> 3], b = xB[col >> 3];
+            #pragma unroll
+            for (int r = 0; r < NW; r++) acc[r] = dot8(w[r][j], a, b, acc[r]);
+        }
     }
     #pragma unroll
     for (int r = 0; r < NW; r++) acc[r] = warp_sum(acc[r]);
@@ -117,35 +123,68 @@ __device__ __forceinline__ float f4sq(float4 a) { return a.x * a.x + a.y * a.y +
 
 // Prologue of the three consuming kernels: x = x_in (+ the G partials of exchange a_idx, in rank order),
 // CTA 0 keeps the new residual row in x_out, then RMSNorm (voxtral_kernels.c:475-492) and the (1 + ada)
-// scale (voxtral_decoder.c:742-745) in shared memory.
+// scale (voxtral_decoder.c:742-745) into shared memory.  A thread owns at most two 8-float chunks and
+// keeps them in registers; every independent load (x, norm weight, ada, the first read of the exchange
+// words) is issued before anything is waited for.
 template <bool REDUCE>
 __device__ __forceinline__ void tp_load_x_norm(float4 *xA, float4 *xB, float *red, const TpDev &td, int a_idx,
                                                const float *__restrict__ x_in, float *__restrict__ x_out,
                                                const float *__restrict__ nw, const float *__restrict__ ada) {
+    constexpr int NC = (DEC_DIM / 8 + TP_THREADS - 1) / TP_THREADS;   // 2
     const int t = threadIdx.x;
-    unsigned seq = 0;
-    if (REDUCE) {
-        seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
-        tp_wait_all(td, seq);
-    }
-    float ss = 0.f;
-    for (int c = t; c < DEC_DIM / 8; c += TP_THREADS) {
-        float4 a = *reinterpret_cast<const float4 *>(x_in + c * 8);
-        float4 b = *reinterpret_cast<const float4 *>(x_in + c * 8 + 4);
-        if (REDUCE) {
-            for (int p = 0; p < td.world; p++) {
-                const float *src = td.self->part[seq & 1][p] + c * 8;
-                a = f4add(a, __ldcg(reinterpret_cast<const float4 *>(src)));
-                b = f4add(b, __ldcg(reinterpret_cast<const float4 *>(src + 4)));
-            }
-            if (blockIdx.x == 0 && x_out) {
-                *reinterpret_cast<float4 *>(x_out + c * 8) = a;
-                *reinterpret_cast<float4 *>(x_out + c * 8 + 4) = b;
+    float4 a[NC], b[NC], wa[NC], wb[NC], da[NC], db[NC];
+    #pragma unroll
+    for (int i = 0; i < NC; i++) {
+        const int c = t + i * TP_THREADS;
+        if (c < DEC_DIM / 8) {
+            a[i] = *reinterpret_cast<const float4 *>(x_in + c * 8);
+            b[i] = *reinterpret_cast<const float4 *>(x_in + c * 8 + 4);
+            wa[i] = *reinterpret_cast<const float4 *>(nw + c * 8);
+            wb[i] = *reinterpret_cast<const float4 *>(nw + c * 8 + 4);
+            if (ada) {
+                da[i] = *reinterpret_cast<const float4 *>(ada + c * 8);
+                db[i] = *reinterpret_cast<const float4 *>(ada + c * 8 + 4);
             }
         }
-        xA[c] = a; xB[c] = b;
-        ss += f4sq(a) + f4sq(b);
     }
+    float ss = 0.f;
+    if (REDUCE) {
+        const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
+        #pragma unroll
+        for (int i = 0; i < NC; i++) {
+            const int c = t + i * TP_THREADS;
+            if (c < DEC_DIM / 8) {
+                for (int p0 = 0; p0 < td.world; p0 += 4) {
+                    uint4 v[4][4];
+                    #pragma unroll
+                    for (int pp = 0; pp < 4; pp++) {
+                        if (p0 + pp < td.world) {
+                            const uint2 *src = td.self->part[a_idx & 1][p0 + pp] + c * 8;
+                            #pragma unroll
+                            for (int k = 0; k < 4; k++) v[pp][k] = ld_ll2(src + 2 * k);
+                        }
+                    }
+                    #pragma unroll
+                    for (int pp = 0; pp < 4; pp++) {
+                        if (p0 + pp < td.world) {
+                            tp_ll_settle8(td, td.self->part[a_idx & 1][p0 + pp] + c * 8, p0 + pp, seq, v[pp]);
+                            a[i].x += __uint_as_float(v[pp][0].x); a[i].y += __uint_as_float(v[pp][0].z);
+                            a[i].z += __uint_as_float(v[pp][1].x); a[i].w += __uint_as_float(v[pp][1].z);
+                            b[i].x += __uint_as_float(v[pp][2].x); b[i].y += __uint_as_float(v[pp][2].z);
+                            b[i].z += __uint_as_float(v[pp][3].x); b[i].w += __uint_as_float(v[pp][3].z);
+                        }
+                    }
+                }
+                if (blockIdx.x == 0 && x_out) {
+                    *reinterpret_cast<float4 *>(x_out + c * 8) = a[i];
+                    *reinterpret_cast<float4 *>(x_out + c * 8 + 4) = b[i];
+                }
+            }
+        }
+    }
+    #pragma unroll
+    for (int i = 0; i < NC; i++)
+        if (t + i * TP_THREADS < DEC_DIM / 8) ss += f4sq(a[i]) + f4sq(b[i]);
     ss = warp_sum(ss);
     if ((t & 31) == 0) red[t >> 5] = ss;
     __syncthreads();
@@ -153,50 +192,60 @@ __device__ __forceinline__ void tp_load_x_norm(float4 *xA, float4 *xB, float *re
     #pragma unroll
     for (int w = 0; w < TP_WARPS; w++) tot += red[w];
     const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
-    for (int c = t; c < DEC_DIM / 8; c += TP_THREADS) {
-        float4 a = xA[c], b = xB[c];
-        const float4 wa = *reinterpret_cast<const float4 *>(nw + c * 8);
-        const float4 wb = *reinterpret_cast<const float4 *>(nw + c * 8 + 4);
-        a.x = a.x * rinv * wa.x; a.y = a.y * rinv * wa.y; a.z = a.z * rinv * wa.z; a.w = a.w * rinv * wa.w;
-        b.x = b.x * rinv * wb.x; b.y = b.y * rinv * wb.y; b.z = b.z * rinv * wb.z; b.w = b.w * rinv * wb.w;
-        if (ada) {
-            const float4 da = *reinterpret_cast<const float4 *>(ada + c * 8);
-            const float4 db = *reinterpret_cast<const float4 *>(ada + c * 8 + 4);
-            a.x *= (1.0f + da.x); a.y *= (1.0f + da.y); a.z *= (1.0f + da.z); a.w *= (1.0f + da.w);
-            b.x *= (1.0f + db.x); b.y *= (1.0f + db.y); b.z *= (1.0f + db.z); b.w *= (1.0f + db.w);
+    #pragma unroll
+    for (int i = 0; i < NC; i++) {
+        const int c = t + i * TP_THREADS;
+        if (c < DEC_DIM / 8) {
+            float4 u = a[i], v = b[i];
+            u.x = u.x * rinv * wa[i].x; u.y = u.y * rinv * wa[i].y; u.z = u.z * rinv * wa[i].z; u.w = u.w * rinv * wa[i].w;
+            v.x = v.x * rinv * wb[i].x; v.y = v.y * rinv * wb[i].y; v.z = v.z * rinv * wb[i].z; v.w = v.w * rinv * wb[i].w;
+            if (ada) {
+                u.x *= (1.0f + da[i].x); u.y *= (1.0f + da[i].y); u.z *= (1.0f + da[i].z); u.w *= (1.0f + da[i].w);
+                v.x *= (1.0f + db[i].x); v.y *= (1.0f + db[i].y); v.z *= (1.0f + db[i].z); v.w *= (1.0f + db[i].w);
+            }
+            xA[c] = u; xB[c] = v;
         }
-        xA[c] = a; xB[c] = b;
     }
     __syncthreads();
 }
+
+constexpr int FULL_NW = 2, FULL_NCH = DEC_DIM / 256;      // K = 3072 kernels: 2 rows x 12 chunks = 24 loads per lane
 
 // ---------------------------------------------------------------------------
 // T1: this rank's rows of wq|wk|wv on rmsnorm(x); RoPE; q -> q_out, K/V -> ring slot
 // (voxtral_decoder.c:710-725).  Buffers keep GLOBAL row / head indices; a rank touches its slice only.
 // ---------------------------------------------------------------------------
-template <int RPW, bool REDUCE>
+template <bool REDUCE>
 __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     TpDev td, int a_idx, const DecStepParams *__restrict__ p, const float *__restrict__ x_in,
     float *__restrict__ x_out, const float *__restrict__ attn_norm, const uint16_t *__restrict__ wqkv,
     const float *__restrict__ rope, float *__restrict__ q_out, float *__restrict__ kc, float *__restrict__ vc) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float red[TP_WARPS];
-    tp_load_x_norm<REDUCE>(xA, xB, red, td, a_idx, x_in, x_out, attn_norm, nullptr);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = DEC_QDIM / td.world, nk = DEC_KVDIM / td.world;
-    const int lrow0 = blockIdx.x * (TP_WARPS * RPW) + warp * RPW;
-    int grow0;
-    if (lrow0 < nq) grow0 = td.rank * nq + lrow0;
-    else if (lrow0 < nq + nk) grow0 = DEC_QDIM + td.rank * nk + (lrow0 - nq);
-    else grow0 = DEC_QDIM + DEC_KVDIM + td.rank * nk + (lrow0 - nq - nk);
-    float acc[RPW];
-    tp_warp_gemv<RPW>(wqkv + (size_t)grow0 * DEC_DIM, DEC_DIM, DEC_DIM, xA, xB, acc);
-    if (lane == 0) {
-        const int slot = p->pos & (DEC_WINDOW - 1);
-        #pragma unroll
-        for (int r = 0; r < RPW; r += 2) {
-            const int row = grow0 + r;
-            float v0 = acc[r], v1 = acc[r + 1];
+    const int nbatch = (nq + 2 * nk) / FULL_NW, nwarps = gridDim.x * TP_WARPS;
+    auto grow_of = [&](int b) {
+        const int lrow = b * FULL_NW;
+        if (lrow < nq) return td.rank * nq + lrow;
+        if (lrow < nq + nk) return DEC_QDIM + td.rank * nk + (lrow - nq);
+        return DEC_QDIM + DEC_KVDIM + td.rank * nk + (lrow - nq - nk);
+    };
+    int b = blockIdx.x * TP_WARPS + warp;
+    uint4 w[FULL_NW][FULL_NCH];
+    if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, wqkv + (size_t)grow_of(b) * DEC_DIM, DEC_DIM, DEC_DIM);
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    tp_load_x_norm<REDUCE>(xA, xB, red, td, a_idx, x_in, x_out, attn_norm, nullptr);
+    const int slot = p->pos & (DEC_WINDOW - 1);
+    while (b < nbatch) {
+        float acc[FULL_NW];
+        tp_wdot<FULL_NW, FULL_NCH>(w, xA, xB, DEC_DIM, acc);
+        const int row = grow_of(b);
+        b += nwarps;
+        if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, wqkv + (size_t)grow_of(b) * DEC_DIM, DEC_DIM, DEC_DIM);
+        if (lane == 0) {
+            float v0 = acc[0], v1 = acc[1];
             if (row < DEC_QDIM + DEC_KVDIM) {     // interleaved-pair rotation, voxtral_kernels.c:631-655
                 const int d = (row & (DEC_HD - 1)) >> 1;
                 const float c = rope[2 * d], s = rope[2 * d + 1];
@@ -207,72 +256,226 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
             if (row < DEC_QDIM) dst = q_out + row;
             else if (row < DEC_QDIM + DEC_KVDIM) dst = kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM);
             else dst = vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM);
-            dst[0] = v0; dst[1] = v1;
+            *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
         }
     }
 }
 
 // ---------------------------------------------------------------------------
-// T2 / T4: partial[row] = W[row][r*ks .. (r+1)*ks) . v[r*ks ..)  for all 3072 rows (wo: K = 4096,
-// voxtral_decoder.c:738-739; w2: K = 9216, :758-760), stored into every rank's window, then published.
-// The residual add happens in the consumer's prologue, so x is not touched here.
+// T2: GQA attention of this rank's kv heads over the ring (vox_causal_attention with seq_q = 1,
+// voxtral_kernels.c:541-611; call voxtral_decoder.c:731-733).  grid = (local kv heads, key splits).
+// A warp takes 8 keys at a time with all 16 K/V row loads in flight (lanes own 4 of the 128 dims; the
+// 8 x 4 scores are reduced across lanes by a transposed butterfly) - the scheme of the single-stream
+// kernel (dec_mega.cu) and of group_dev.cuh.  The CTA that arrives last for a kv head merges the splits.
 // ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(TP_THREADS) tp_attn_kernel(
+    TpDev td, const DecStepParams *__restrict__ p, const float *__restrict__ q, const float *__restrict__ kc,
+    const float *__restrict__ vc, float *__restrict__ part, float *__restrict__ attn_out) {
+    __shared__ __align__(16) float qs[4][DEC_HD];
+    __shared__ __align__(16) float wsm[TP_WARPS][4][DEC_HD + 4];
+    __shared__ int s_last;
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    const int lk = blockIdx.x, kvh = td.rank * (DEC_KVH / td.world) + lk, split = blockIdx.y, ns = gridDim.y;
+    const int pos = p->pos;
+    const int n_keys = min(p->n_valid, DEC_WINDOW - 1) + 1;
+    const int first = pos - n_keys + 1;                  // logical position of key 0
+    const int ng = (n_keys + 7) >> 3;
+    int gps = (ng + ns - 1) / ns;
+    gps = (gps + TP_WARPS - 1) / TP_WARPS * TP_WARPS;    // whole rounds of the 8 warps
+    const int g0 = split * gps, g1 = min(ng, g0 + gps);
+    if (tid < 4 * DEC_HD / 4)
+        reinterpret_cast<float4 *>(&qs[0][0])[tid] = reinterpret_cast<const float4 *>(q + (size_t)kvh * 4 * DEC_HD)[tid];
+    __syncthreads();
+    const float scale = 0.08838834764831845f;            // 1/sqrt(128)
+    float4 qv[4];
+    #pragma unroll
+    for (int h = 0; h < 4; h++) qv[h] = reinterpret_cast<const float4 *>(&qs[h][0])[lane];
+    float m = -INFINITY, l = 0.f;                        // lanes 0..3 matter: running max / sum of head (lane & 3)
+    float4 acc[4];
+    #pragma unroll
+    for (int h = 0; h < 4; h++) acc[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const size_t hoff = (size_t)kvh * DEC_HD + 4 * lane;
+    for (int g = g0 + w; g < g1; g += TP_WARPS) {
+        const int j0 = g * 8;
+        const int nv = min(8, n_keys - j0);
+        float4 kf[8], vf[8];
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamped: always a valid row
+            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
+            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+        }
+        float v[32];
+        #pragma unroll
+        for (int i = 0; i < 8; i++)
+            #pragma unroll
+            for (int h = 0; h < 4; h++)
+                v[i * 4 + h] = kf[i].x * qv[h].x + kf[i].y * qv[h].y + kf[i].z * qv[h].z + kf[i].w * qv[h].w;
+        #pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {              // score (key i, head h) ends in lane 4i + h
+            const bool up = (lane & o) != 0;
+            #pragma unroll
+            for (int k = 0; k < o; k++) {
+                const float keep = up ? v[k + o] : v[k];
+                const float send = up ? v[k] : v[k + o];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
+        }
+        const bool valid = (lane >> 2) < nv;
+        const float sc = valid ? v[0] * scale : -INFINITY;
+        float mx = sc;
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        const float mn = fmaxf(m, mx);                   // finite: every group has >= 1 valid key
+        const float corr = (m == -INFINITY) ? 0.f : expf(m - mn);
+        const float pr = valid ? expf(sc - mn) : 0.f;
+        float ps = pr;
+        ps += __shfl_xor_sync(0xffffffffu, ps, 4);
+        ps += __shfl_xor_sync(0xffffffffu, ps, 8);
+        ps += __shfl_xor_sync(0xffffffffu, ps, 16);
+        l = l * corr + ps;
+        m = mn;
+        #pragma unroll
+        for (int h = 0; h < 4; h++) {
+            const float ch = __shfl_sync(0xffffffffu, corr, h);
+            acc[h].x *= ch; acc[h].y *= ch; acc[h].z *= ch; acc[h].w *= ch;
+        }
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
+            #pragma unroll
+            for (int h = 0; h < 4; h++) {
+                const float ph = __shfl_sync(0xffffffffu, pr, i * 4 + h);       // 0 for padded keys
+                acc[h].x = fmaf(ph, vf[i].x, acc[h].x); acc[h].y = fmaf(ph, vf[i].y, acc[h].y);
+                acc[h].z = fmaf(ph, vf[i].z, acc[h].z); acc[h].w = fmaf(ph, vf[i].w, acc[h].w);
+            }
+        }
+    }
+    #pragma unroll
+    for (int h = 0; h < 4; h++) reinterpret_cast<float4 *>(&wsm[w][h][0])[lane] = acc[h];
+    if (lane < 4) { wsm[w][lane][DEC_HD] = m; wsm[w][lane][DEC_HD + 1] = l; }
+    __syncthreads();
+    const int h = tid >> 6, d = (tid & 63) * 2;          // thread -> (head, two dims)
+    {   // merge the 8 warps into this split's partial (relative to its own maximum, not normalised)
+        float M = -INFINITY;
+        #pragma unroll
+        for (int k = 0; k < TP_WARPS; k++) M = fmaxf(M, wsm[k][h][DEC_HD]);
+        float n0 = 0.f, n1 = 0.f, den = 0.f;
+        #pragma unroll
+        for (int k = 0; k < TP_WARPS; k++) {
+            const float mk = wsm[k][h][DEC_HD];
+            const float e = (mk == -INFINITY) ? 0.f : expf(mk - M);
+            n0 = fmaf(e, wsm[k][h][d], n0);
+            n1 = fmaf(e, wsm[k][h][d + 1], n1);
+            den = fmaf(e, wsm[k][h][DEC_HD + 1], den);
+        }
+        float *o = part + ((size_t)(kvh * TP_ATT_SPLITS + split) * 4 + h) * TP_ATT_PART;
+        *reinterpret_cast<float2 *>(o + d) = make_float2(n0, n1);
+        if ((tid & 63) == 0) { o[DEC_HD] = M; o[DEC_HD + 1] = den; }
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned old = atomicAdd(&td.done[1 + lk], 1u);
+        s_last = (old == (unsigned)ns - 1u);
+        if (s_last) td.done[1 + lk] = 0;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        const float *base = part + ((size_t)kvh * TP_ATT_SPLITS * 4 + h) * TP_ATT_PART;
+        float M = -INFINITY;
+        for (int s = 0; s < ns; s++) M = fmaxf(M, __ldcg(base + (size_t)s * 4 * TP_ATT_PART + DEC_HD));
+        float n0 = 0.f, n1 = 0.f, den = 0.f;
+        for (int s = 0; s < ns; s++) {
+            const float *o = base + (size_t)s * 4 * TP_ATT_PART;
+            const float ms = __ldcg(o + DEC_HD);
+            if (ms == -INFINITY) continue;
+            const float e = expf(ms - M);
+            const float2 a = __ldcg(reinterpret_cast<const float2 *>(o + d));
+            n0 = fmaf(e, a.x, n0); n1 = fmaf(e, a.y, n1);
+            den = fmaf(e, __ldcg(o + DEC_HD + 1), den);
+        }
+        const float inv = den > 0.f ? 1.0f / den : 0.f;
+        *reinterpret_cast<float2 *>(attn_out + (size_t)(kvh * 4 + h) * DEC_HD + d) = make_float2(n0 * inv, n1 * inv);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// T3 / T5: partial[row] = W[row][r*ks .. (r+1)*ks) . v[r*ks ..)  for all 3072 rows (wo: K = 4096,
+// voxtral_decoder.c:738-739; w2: K = 9216, :758-760).  Lane p of the warp that owns a row stores the sum
+// into rank p's window (its own included) the moment it exists.  The residual add happens in the
+// consumer's prologue, so x is not touched here.
+// ---------------------------------------------------------------------------
+template <int NW, int NCH>
 __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
     TpDev td, int a_idx, const float *__restrict__ v, const uint16_t *__restrict__ W, int K) {
     extern __shared__ __align__(16) unsigned char tp_smem[];
-    __shared__ __align__(16) float rows[TP_RES_ROWS];
     const int ks = K / td.world;
     float4 *xA = reinterpret_cast<float4 *>(tp_smem);
     float4 *xB = xA + ks / 8;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int nbatch = DEC_DIM / NW, nwarps = gridDim.x * TP_WARPS;
+    const uint16_t *Ws = W + (size_t)td.rank * ks;
+    int b = blockIdx.x * TP_WARPS + warp;
+    uint4 w[NW][NCH];
+    if (b < nbatch) tp_wload<NW, NCH>(w, Ws + (size_t)b * NW * K, (size_t)K, ks);
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
     const float *vs = v + (size_t)td.rank * ks;
     for (int c = t; c < ks / 8; c += TP_THREADS) {
         xA[c] = *reinterpret_cast<const float4 *>(vs + c * 8);
         xB[c] = *reinterpret_cast<const float4 *>(vs + c * 8 + 4);
     }
     __syncthreads();
-    const int row0 = blockIdx.x * TP_RES_ROWS + warp * TP_RES_RPW;
-    float acc[TP_RES_RPW];
-    tp_warp_gemv<TP_RES_RPW>(W + (size_t)row0 * K + (size_t)td.rank * ks, (size_t)K, ks, xA, xB, acc);
-    if (lane == 0) {
-        #pragma unroll
-        for (int r = 0; r < TP_RES_RPW; r++) rows[warp * TP_RES_RPW + r] = acc[r];
-    }
-    __syncthreads();
     const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
-    if (t < td.world * (TP_RES_ROWS / 4)) {          // 64 B of rows per peer, one float4 per thread
-        const int peer = t / (TP_RES_ROWS / 4), q4 = t % (TP_RES_ROWS / 4);
-        float *dst = td.peer[peer]->part[seq & 1][td.rank] + blockIdx.x * TP_RES_ROWS + q4 * 4;
-        *reinterpret_cast<float4 *>(dst) = reinterpret_cast<const float4 *>(rows)[q4];
-        __threadfence_system();
+    uint2 *dst = lane < td.world ? td.peer[lane]->part[a_idx & 1][td.rank] : nullptr;
+    while (b < nbatch) {
+        float acc[NW];
+        tp_wdot<NW, NCH>(w, xA, xB, ks, acc);
+        const int row0 = b * NW;
+        b += nwarps;
+        if (b < nbatch) tp_wload<NW, NCH>(w, Ws + (size_t)b * NW * K, (size_t)K, ks);
+        if (dst) {                              // lane p sends the sums to rank p: value and flag in one 8-byte word
+            #pragma unroll
+            for (int r = 0; r < NW; r++) st_ll(dst + row0 + r, __float_as_uint(acc[r]), seq);
+        }
     }
-    tp_publish(td, seq, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------
-// T3: h[i] = silu(w1[i] . xn) * (w3[i] . xn) for this rank's rows of the interleaved w1|w3, xn =
+// T4: h[i] = silu(w1[i] . xn) * (w3[i] . xn) for this rank's rows of the interleaved w1|w3, xn =
 // rmsnorm(x + sum of the wo partials) * (1 + ada)   (voxtral_decoder.c:741-757)
 // ---------------------------------------------------------------------------
-template <int RPW>
 __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
     TpDev td, int a_idx, const float *__restrict__ x_in, float *__restrict__ x_out,
     const float *__restrict__ ffn_norm, const float *__restrict__ ada, const uint16_t *__restrict__ w13,
     float *__restrict__ h) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float red[TP_WARPS];
-    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, x_out, ffn_norm, ada);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row0 = td.rank * (2 * DEC_HIDDEN / td.world) + blockIdx.x * (TP_WARPS * RPW) + warp * RPW;
-    float acc[RPW];
-    tp_warp_gemv<RPW>(w13 + (size_t)row0 * DEC_DIM, DEC_DIM, DEC_DIM, xA, xB, acc);
-    if (lane == 0) {
-        #pragma unroll
-        for (int r = 0; r < RPW; r += 2) h[(row0 + r) >> 1] = silu(acc[r]) * acc[r + 1];
+    const int nrows = 2 * DEC_HIDDEN / td.world, row_base = td.rank * nrows;
+    const int nbatch = nrows / FULL_NW, nwarps = gridDim.x * TP_WARPS;
+    int b = blockIdx.x * TP_WARPS + warp;
+    uint4 w[FULL_NW][FULL_NCH];
+    if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, w13 + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, x_out, ffn_norm, ada);
+    while (b < nbatch) {
+        float acc[FULL_NW];
+        tp_wdot<FULL_NW, FULL_NCH>(w, xA, xB, DEC_DIM, acc);
+        const int row = row_base + b * FULL_NW;
+        b += nwarps;
+        if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, w13 + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
+        if (lane == 0) h[row >> 1] = silu(acc[0]) * acc[1];
     }
 }
 
 // ---------------------------------------------------------------------------
-// T5: logits of this rank's vocabulary rows + per-CTA first maximum (voxtral_decoder.c:765-779)
+// T6: logits of this rank's vocabulary rows + per-CTA first maximum (voxtral_decoder.c:765-779)
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ void tp_argmax_merge(float &bv, int &bi, float v, int i) {
     if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }   // first maximum; NaN never wins
@@ -285,30 +488,39 @@ __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
     __shared__ float red[TP_WARPS];
     __shared__ float bvs[TP_WARPS];
     __shared__ int bis[TP_WARPS];
-    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, nullptr, norm, nullptr);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nrows = VOCAB / td.world, row_base = td.rank * nrows;
+    const int nbatch = nrows / FULL_NW, nwarps = gridDim.x * TP_WARPS;
+    int b = blockIdx.x * TP_WARPS + warp;
+    uint4 w[FULL_NW][FULL_NCH];
+    if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, tok_emb + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, nullptr, norm, nullptr);
     float bv = -INFINITY; int bi = 0x7fffffff;
-    const int base = td.rank * (VOCAB / td.world) + blockIdx.x * LOGITS_ROWS_PER_CTA;
-    for (int it = 0; it < LOGITS_ROWS_PER_CTA / (TP_WARPS * 4); it++) {
-        const int row0 = base + (it * TP_WARPS + warp) * 4;
-        float acc[4];
-        tp_warp_gemv<4>(tok_emb + (size_t)row0 * DEC_DIM, DEC_DIM, DEC_DIM, xA, xB, acc);
+    while (b < nbatch) {
+        float acc[FULL_NW];
+        tp_wdot<FULL_NW, FULL_NCH>(w, xA, xB, DEC_DIM, acc);
+        const int row = row_base + b * FULL_NW;
+        b += nwarps;
+        if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, tok_emb + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
         if (lane == 0) {
-            #pragma unroll
-            for (int r = 0; r < 4; r++) { logits[row0 + r] = acc[r]; tp_argmax_merge(bv, bi, acc[r], row0 + r); }
+            *reinterpret_cast<float2 *>(logits + row) = make_float2(acc[0], acc[1]);
+            tp_argmax_merge(bv, bi, acc[0], row);
+            tp_argmax_merge(bv, bi, acc[1], row + 1);
         }
     }
     if (lane == 0) { bvs[warp] = bv; bis[warp] = bi; }
     __syncthreads();
     if (threadIdx.x == 0) {
         #pragma unroll
-        for (int w = 1; w < TP_WARPS; w++) tp_argmax_merge(bv, bi, bvs[w], bis[w]);
+        for (int k = 1; k < TP_WARPS; k++) tp_argmax_merge(bv, bi, bvs[k], bis[k]);
         blockmax[2 * blockIdx.x] = bv;
         blockmax[2 * blockIdx.x + 1] = __int_as_float(bi);
     }
 }
 
-// T6: first maximum of this rank's slice -> every rank's window (exchange index 2 * layers)
+// T7: first maximum of this rank's slice -> every rank's window (exchange index 2 * layers)
 __global__ void __launch_bounds__(1024) tp_argmax_pub_kernel(TpDev td, const float *__restrict__ blockmax, int nblk) {
     __shared__ float bvs[32];
     __shared__ int bis[32];
@@ -328,25 +540,37 @@ __global__ void __launch_bounds__(1024) tp_argmax_pub_kernel(TpDev td, const flo
         const unsigned e = *td.epoch;
         const unsigned seq = e * (unsigned)td.ars + (unsigned)td.ars;     // a_idx = ars - 1
         for (int p = 0; p < td.world; p++) {
-            float *dst = td.peer[p]->amax[e & 1][td.rank];
-            *reinterpret_cast<float2 *>(dst) = make_float2(bv, __int_as_float(bi));
+            uint2 *dst = td.peer[p]->amax[seq & 1][td.rank];
+            st_ll(dst, __float_as_uint(bv), seq);
+            st_ll(dst + 1, (unsigned)bi, seq);
         }
-        __threadfence_system();
-        for (int p = 0; p < td.world; p++) st_release_sys(&td.peer[p]->flag[td.rank], seq);
     }
 }
 
-// T7: merge the G slice maxima (same order on every rank), write the token, advance the step scalars
+// T8: merge the G slice maxima (same order on every rank), write the token, advance the step scalars
 __global__ void __launch_bounds__(32) tp_argmax_fin_kernel(TpDev td, DecStepParams *__restrict__ p,
                                                            int *__restrict__ tokens) {
+    __shared__ float vals[TP_MAX];
+    __shared__ int idxs[TP_MAX];
     const unsigned e = *td.epoch;
-    tp_wait_all(td, e * (unsigned)td.ars + (unsigned)td.ars);
+    const unsigned seq = e * (unsigned)td.ars + (unsigned)td.ars;
+    if ((int)threadIdx.x < td.world) {
+        const uint2 *src = td.self->amax[seq & 1][threadIdx.x];
+        uint4 v = ld_ll2(src);
+        if (v.y != seq || v.w != seq) {
+            const unsigned long long t0 = globaltimer_ns();
+            do {
+                v = ld_ll2(src);
+                if (globaltimer_ns() - t0 > 8000000000ull) tp_timeout(td.rank, threadIdx.x, seq);
+            } while (v.y != seq || v.w != seq);
+        }
+        vals[threadIdx.x] = __uint_as_float(v.x);
+        idxs[threadIdx.x] = (int)v.z;
+    }
+    __syncwarp();
     if (threadIdx.x == 0) {
         float bv = -INFINITY; int bi = 0x7fffffff;
-        for (int r = 0; r < td.world; r++) {
-            const float2 m = __ldcg(reinterpret_cast<const float2 *>(td.self->amax[e & 1][r]));
-            tp_argmax_merge(bv, bi, m.x, __float_as_int(m.y));
-        }
+        for (int r = 0; r < td.world; r++) tp_argmax_merge(bv, bi, vals[r], idxs[r]);
         if (bi == 0x7fffffff) bi = 0;    // all-NaN logits: the reference returns index 0
         p->out_token = bi;
         p->prev_token = bi;
@@ -365,7 +589,7 @@ __global__ void __launch_bounds__(32) tp_argmax_fin_kernel(TpDev td, DecStepPara
 struct TpRank {
     TpDev dev;
     TpComm *comm;
-    unsigned *ctr;            // [0] = done, [1] = epoch
+    unsigned *ctr;            // [1..8] = attention arrivals per local kv head, [16] = epoch
     float *xbuf;              // [2][3072] residual row, ping-pong across exchanges
     float *blockmax;          // (value, index) per logits CTA
     DecStepParams *d_params;
@@ -376,6 +600,8 @@ struct TpRank {
 struct vox_cuda_tp {
     vox_cuda_model *m;
     vox_cuda_state *s;        // the stream's replicated state: encoder, adapter rows, prefill, K/V ring
+    float *attn_part;         // [8 kv heads][TP_ATT_SPLITS][4][TP_ATT_PART] split partials (global head index)
+    int att_splits;
     int world, n_local, connected;
     TpRank r[TP_MAX];
     cudaGraphExec_t graph;
@@ -401,16 +627,16 @@ static void tp_rank_free(TpRank &R) {
 static int tp_rank_init(vox_cuda_tp *tp, TpRank &R, int rank) {
     memset(&R, 0, sizeof(R));
     CUDA_TRY(cudaMalloc((void **)&R.comm, sizeof(TpComm)));
-    CUDA_TRY(cudaMalloc((void **)&R.ctr, 64));
+    CUDA_TRY(cudaMalloc((void **)&R.ctr, 128));
     CUDA_TRY(cudaMalloc((void **)&R.xbuf, 2 * DEC_DIM * 4));
     CUDA_TRY(cudaMalloc((void **)&R.blockmax, (size_t)2 * (VOCAB / LOGITS_ROWS_PER_CTA) * 4));
     CUDA_TRY(cudaMalloc((void **)&R.d_params, sizeof(DecStepParams)));
     CUDA_TRY(cudaMalloc((void **)&R.d_tokens, (size_t)TOKENS_RING * 4));
     CUDA_TRY(cudaMemset(R.comm, 0, sizeof(TpComm)));
-    CUDA_TRY(cudaMemset(R.ctr, 0, 64));
+    CUDA_TRY(cudaMemset(R.ctr, 0, 128));
     CUDA_TRY(cudaMemset(R.d_tokens, 0, (size_t)TOKENS_RING * 4));
     R.dev.rank = rank; R.dev.world = tp->world; R.dev.ars = 2 * tp->m->n_dec + 1;
-    R.dev.self = R.comm; R.dev.done = R.ctr; R.dev.epoch = R.ctr + 1;
+    R.dev.self = R.comm; R.dev.done = R.ctr; R.dev.epoch = R.ctr + 16;
     R.dev.peer[rank] = R.comm;
     return 0;
 }
@@ -421,6 +647,13 @@ static vox_cuda_tp *tp_alloc(vox_cuda_model *m, int world) {
     tp->m = m; tp->world = world;
     tp->s = vox_cuda_state_create(m);
     if (!tp->s) { free(tp); return nullptr; }
+    // key splits: enough CTAs to pull a long context at HBM speed, few enough that the merge stays short
+    const int kh = DEC_KVH / world;
+    tp->att_splits = kh >= 4 ? 16 : TP_ATT_SPLITS;
+    if (cudaMalloc((void **)&tp->attn_part, (size_t)DEC_KVH * TP_ATT_SPLITS * 4 * TP_ATT_PART * 4) != cudaSuccess) {
+        vox_set_error("tp: attention scratch alloc failed");
+        vox_cuda_state_free(tp->s); free(tp); return nullptr;
+    }
     return tp;
 }
 
@@ -430,6 +663,7 @@ extern "C" void vox_cuda_tp_free(vox_cuda_tp_t *tp) {
     if (tp->graph) cudaGraphExecDestroy(tp->graph);
     for (int i = 0; i < tp->n_local; i++) tp_rank_free(tp->r[i]);
     if (tp->h_check) cudaFreeHost(tp->h_check);
+    cudaFree(tp->attn_part);
     vox_cuda_state_free(tp->s);
     free(tp);
 }
@@ -506,15 +740,47 @@ extern "C" int vox_cuda_tp_connect(vox_cuda_tp_t *tp, const void *handles) {
     return 0;
 }
 
-static inline int tp_step_kernels(const vox_cuda_tp *tp) { return 1 + 6 * tp->m->n_dec + 3; }
+static inline int tp_step_kernels(const vox_cuda_tp *tp) { return 1 + 5 * tp->m->n_dec + 3; }
+
+// wo / w2 slices: (rows per warp, 256-column chunks) so that a lane has 32-40 loads of 16 B in flight
+template <int NW, int NCH>
+static cudaError_t tp_launch_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K) {
+    const int ks = K / td.world;
+    const size_t smem = (size_t)ks * 4;
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(tp_gemv_partial_kernel<NW, NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 40 * 1024);
+        attr = true;
+    }
+    int grid = (DEC_DIM / NW + TP_WARPS - 1) / TP_WARPS;
+    if (grid > 148) grid = 148;     // 170-240 registers per thread: one CTA per SM, warps loop over row batches
+    return launch_pdl(tp_gemv_partial_kernel<NW, NCH>, grid, TP_THREADS, smem, st, td, a_idx, v, W, K);
+}
+
+static cudaError_t tp_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K) {
+    const int G = td.world;
+    if (K == DEC_QDIM) {
+        if (G == 1) return tp_launch_partial<2, 16>(st, td, a_idx, v, W, K);
+        if (G == 2) return tp_launch_partial<4, 8>(st, td, a_idx, v, W, K);
+        if (G == 4) return tp_launch_partial<8, 4>(st, td, a_idx, v, W, K);
+        return tp_launch_partial<8, 2>(st, td, a_idx, v, W, K);
+    }
+    if (G == 1) return tp_launch_partial<1, 36>(st, td, a_idx, v, W, K);
+    if (G == 2) return tp_launch_partial<2, 18>(st, td, a_idx, v, W, K);
+    if (G == 4) return tp_launch_partial<4, 9>(st, td, a_idx, v, W, K);
+    return tp_launch_partial<8, 5>(st, td, a_idx, v, W, K);
+}
+
+static inline int tp_grid(int rows) {
+    int g = (rows / FULL_NW + TP_WARPS - 1) / TP_WARPS;
+    return g > 148 ? 148 : g;
+}
 
 static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
     vox_cuda_model *m = tp->m;
     vox_cuda_state *s = tp->s;
     const int G = tp->world, NL = tp->n_local, L = m->n_dec;
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
-    const int qkv_rows = DEC_QKV / G, ffn_rows = 2 * DEC_HIDDEN / G;
-    const int rpw = G <= 1 ? 4 : 2;               // keep >= 96 CTAs per GEMV as the shard shrinks
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
         dec_launch_embed(st, R.d_params, s->d_embed_in, s->adapter_buf, m->tok_emb, m->inv_freq_dec, R.xbuf, s->d_rope);
@@ -525,38 +791,32 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
             const int a = 2 * l - 1;              // consumes the w2 exchange of the previous layer
-            float *xin = l == 0 ? R.xbuf : R.xbuf + DEC_DIM, *xout = R.xbuf;
-            const int grid = qkv_rows / (TP_WARPS * rpw);
-            if (l == 0) {
-                if (rpw == 4) tp_qkv_kernel<4, false><<<grid, TP_THREADS, 0, st>>>(R.dev, a, R.d_params, xin, nullptr, W.attn_norm, W.wqkv, s->d_rope, s->d_q, kc, vc);
-                else          tp_qkv_kernel<2, false><<<grid, TP_THREADS, 0, st>>>(R.dev, a, R.d_params, xin, nullptr, W.attn_norm, W.wqkv, s->d_rope, s->d_q, kc, vc);
-            } else {
-                if (rpw == 4) tp_qkv_kernel<4, true><<<grid, TP_THREADS, 0, st>>>(R.dev, a, R.d_params, xin, xout, W.attn_norm, W.wqkv, s->d_rope, s->d_q, kc, vc);
-                else          tp_qkv_kernel<2, true><<<grid, TP_THREADS, 0, st>>>(R.dev, a, R.d_params, xin, xout, W.attn_norm, W.wqkv, s->d_rope, s->d_q, kc, vc);
-            }
+            const DecStepParams *pp = R.d_params;
+            if (l == 0)
+                CUDA_TRY(launch_pdl(tp_qkv_kernel<false>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
+                                    (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc));
+            else
+                CUDA_TRY(launch_pdl(tp_qkv_kernel<true>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
+                                    R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc));
         }
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
-            dec_launch_attn(st, R.d_params, s->d_q, kc, vc, s->d_attn_part, s->d_attn, R.dev.rank * (DEC_KVH / G), DEC_KVH / G);
+            CUDA_TRY(launch_pdl(tp_attn_kernel, dim3(DEC_KVH / G, tp->att_splits), TP_THREADS, 0, st, R.dev, (const DecStepParams *)R.d_params,
+                                (const float *)s->d_q, (const float *)kc, (const float *)vc, tp->attn_part, s->d_attn));
         }
-        for (int i = 0; i < NL; i++)
-            tp_gemv_partial_kernel<<<DEC_DIM / TP_RES_ROWS, TP_THREADS, (size_t)(DEC_QDIM / G) * 4, st>>>(
-                tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM);
+        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM));
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
-            const int grid = ffn_rows / (TP_WARPS * rpw);
-            const float *ada = m->ada_scale + (size_t)l * DEC_DIM;
-            if (rpw == 4) tp_ffn_kernel<4><<<grid, TP_THREADS, 0, st>>>(R.dev, 2 * l, R.xbuf, R.xbuf + DEC_DIM, W.ffn_norm, ada, W.w13, s->d_h);
-            else          tp_ffn_kernel<2><<<grid, TP_THREADS, 0, st>>>(R.dev, 2 * l, R.xbuf, R.xbuf + DEC_DIM, W.ffn_norm, ada, W.w13, s->d_h);
+            CUDA_TRY(launch_pdl(tp_ffn_kernel, tp_grid(2 * DEC_HIDDEN / G), TP_THREADS, 0, st, R.dev, 2 * l, (const float *)R.xbuf, R.xbuf + DEC_DIM,
+                                W.ffn_norm, (const float *)(m->ada_scale + (size_t)l * DEC_DIM), W.w13, s->d_h));
         }
-        for (int i = 0; i < NL; i++)
-            tp_gemv_partial_kernel<<<DEC_DIM / TP_RES_ROWS, TP_THREADS, (size_t)(DEC_HIDDEN / G) * 4, st>>>(
-                tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN);
+        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN));
     }
-    const int nblk = VOCAB / G / LOGITS_ROWS_PER_CTA;
+    const int nblk = tp_grid(VOCAB / G);
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
-        tp_logits_kernel<<<nblk, TP_THREADS, 0, st>>>(R.dev, 2 * L - 1, R.xbuf + DEC_DIM, m->dec_norm, m->tok_emb, s->d_logits, R.blockmax);
+        CUDA_TRY(launch_pdl(tp_logits_kernel, nblk, TP_THREADS, 0, st, R.dev, 2 * L - 1, (const float *)(R.xbuf + DEC_DIM), m->dec_norm,
+                            m->tok_emb, s->d_logits, R.blockmax));
     }
     for (int i = 0; i < NL; i++) tp_argmax_pub_kernel<<<1, 1024, 0, st>>>(tp->r[i].dev, tp->r[i].blockmax, nblk);
     for (int i = 0; i < NL; i++) tp_argmax_fin_kernel<<<1, 32, 0, st>>>(tp->r[i].dev, tp->r[i].d_params, tp->r[i].d_tokens);
