@@ -20,6 +20,15 @@
 // issues ALL weight loads of its row batch before anything else (before the programmatic-dependent-launch
 // wait and before the exchange wait, which then overlap the HBM fetch); kernels are chained with PDL;
 // attention is one kernel (key splits across CTAs, the last CTA of a kv head merges the splits).
+//
+// PDL ordering.  Kernels that read what the previous kernel of the stream wrote (attention: q/K/V; the
+// wo / w2 GEMVs: attention output / h; layer 0's qkv: the embedding) call griddepcontrol.wait and only
+// THEN griddepcontrol.launch_dependents.  The three consumers of an exchange (ffn, qkv of layers >= 1,
+// logits) do not wait at all: their only input from the previous kernel (the partial GEMV) are the
+// exchange words, which carry their own flags, so they run beside it - weights fetched, x loaded, polling
+// - and the NVLink hop overlaps the GEMV's tail.  They cannot start before every CTA of that GEMV has
+// passed ITS wait, i.e. before the kernel two back (which wrote their x_in) has completed; every buffer
+// they write (x_out, q/K/V, h, logits) was last read by a kernel at least that old.
 #include "vox_internal.h"
 #include "tc_ptx.cuh"
 #include <cuda.h>
@@ -234,8 +243,8 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     int b = blockIdx.x * TP_WARPS + warp;
     uint4 w[FULL_NW][FULL_NCH];
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, wqkv + (size_t)grow_of(b) * DEC_DIM, DEC_DIM, DEC_DIM);
+    if (!REDUCE) tcx::pdl_wait();        // layer 0: x comes from the embed kernel; else see "PDL ordering" above
     tcx::pdl_launch_dependents();
-    tcx::pdl_wait();
     tp_load_x_norm<REDUCE>(xA, xB, red, td, a_idx, x_in, x_out, attn_norm, nullptr);
     const int slot = p->pos & (DEC_WINDOW - 1);
     while (b < nbatch) {
@@ -274,8 +283,8 @@ __global__ void __launch_bounds__(TP_THREADS) tp_attn_kernel(
     __shared__ __align__(16) float qs[4][DEC_HD];
     __shared__ __align__(16) float wsm[TP_WARPS][4][DEC_HD + 4];
     __shared__ int s_last;
-    tcx::pdl_launch_dependents();
     tcx::pdl_wait();
+    tcx::pdl_launch_dependents();
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const int lk = blockIdx.x, kvh = td.rank * (DEC_KVH / td.world) + lk, split = blockIdx.y, ns = gridDim.y;
     const int pos = p->pos;
@@ -422,8 +431,8 @@ __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
     int b = blockIdx.x * TP_WARPS + warp;
     uint4 w[NW][NCH];
     if (b < nbatch) tp_wload<NW, NCH>(w, Ws + (size_t)b * NW * K, (size_t)K, ks);
-    tcx::pdl_launch_dependents();
     tcx::pdl_wait();
+    tcx::pdl_launch_dependents();
     const float *vs = v + (size_t)td.rank * ks;
     for (int c = t; c < ks / 8; c += TP_THREADS) {
         xA[c] = *reinterpret_cast<const float4 *>(vs + c * 8);
@@ -461,8 +470,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
     int b = blockIdx.x * TP_WARPS + warp;
     uint4 w[FULL_NW][FULL_NCH];
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, w13 + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
-    tcx::pdl_launch_dependents();
-    tcx::pdl_wait();
+    tcx::pdl_launch_dependents();        // no PDL wait: the exchange words are the dependency ("PDL ordering" above)
     tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, x_out, ffn_norm, ada);
     while (b < nbatch) {
         float acc[FULL_NW];
@@ -494,8 +502,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
     int b = blockIdx.x * TP_WARPS + warp;
     uint4 w[FULL_NW][FULL_NCH];
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, tok_emb + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
-    tcx::pdl_launch_dependents();
-    tcx::pdl_wait();
+    tcx::pdl_launch_dependents();        // no PDL wait: the exchange words are the dependency
     tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, nullptr, norm, nullptr);
     float bv = -INFINITY; int bi = 0x7fffffff;
     while (b < nbatch) {
