@@ -207,6 +207,42 @@ def run_cuda(args, rank, world):
                  "ids_equal_single_stream": bool(np.array_equal(toks[:n0], gtoks[0, :n0])),
                  "api": "vox_cuda_group_encode(host PCM) x S + vox_cuda_group_decode -> ids on the host"}
         L.vox_cuda_group_free(g)
+    # ---- tensor-parallel single-stream decode over the N GPUs of this run (north star: "reported at
+    # 2/4/8 GPUs"): every rank encodes + prefills the SAME clip, the greedy steps are sharded by kv head /
+    # FFN rows / vocabulary with the wo / w2 sums exchanged through NVLink peer memory (csrc/dec_tp.cu) ----
+    tp_res = None
+    if world in (2, 4, 8) and not args.no_tp:
+        import torch
+        import tp as tpmod
+        b1, nf1 = frame_buffer(synth_clip(args.clip_seconds, 1))
+        n_ref = vc.check(L.vox_cuda_transcribe(st, vc.fptr(b1), len(b1), nf1, PROMPT_LEN, vc.iptr(toks), max_tok, None), "transcribe")
+        ref_ids = toks[:n_ref].copy()
+        tph = tpmod.create_attached(L, model, rank, world, dist)
+        tp_ms = C.c_float()
+        tp_toks = np.empty(max_tok, np.int32)
+        best_ms, wall = 1e9, 0.0
+        equal = True
+        for it in range(1 + max(1, args.steps)):          # first pass = warm-up (graph instantiation)
+            barrier()
+            t0 = time.perf_counter()
+            n_tp = vc.check(L.vox_cuda_tp_transcribe(tph, vc.fptr(b1), len(b1), nf1, PROMPT_LEN, vc.iptr(tp_toks), max_tok,
+                                                     C.byref(tp_ms)), "tp_transcribe")
+            barrier()
+            if it > 0:
+                wall = max_over_ranks(time.perf_counter() - t0)
+                best_ms = min(best_ms, max_over_ranks(float(tp_ms.value)))
+            equal = equal and n_tp == n_ref and bool(np.array_equal(tp_toks[:n_tp], ref_ids))
+        eq = torch.tensor([1 if equal else 0], device="cuda")
+        dist.all_reduce(eq, op=dist.ReduceOp.MIN)
+        barrier()
+        L.vox_cuda_tp_free(tph)
+        tp_res = {"gpus": world, "ms_per_token": best_ms, "tok_per_s": 1e3 / best_ms, "steps": int(n_ref),
+                  "single_gpu_ms_per_token": ms_step, "speedup_vs_single_gpu": ms_step / best_ms,
+                  "clip_wall_ms": 1e3 * wall, "ids_equal_single_stream": bool(eq.item()),
+                  "hbm_gbs_per_gpu": DEC_BYTES_PER_TOKEN / world / (best_ms * 1e-3) / 1e9,
+                  "exchange": "52 sums of 3072 fp32 + 1 (max, index) pair per token, stored by the GEMV warps into every "
+                              "peer's window over NVLink (CUDA IPC) as {value, sequence} words; no NCCL on the data path",
+                  "api": "vox_cuda_tp_create/export/connect + vox_cuda_tp_transcribe (encoder + prefill replicated per rank)"}
     sampler.stop_flag = True
     sampler.join()
 
@@ -250,6 +286,8 @@ def run_cuda(args, rank, world):
         }
         if multi is not None:
             line["multi_stream"] = multi
+        if tp_res is not None:
+            line["tp_decode"] = tp_res
         if not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(mdir)
         print(json.dumps(line), flush=True)
@@ -320,6 +358,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--streams", type=int, default=64,
                     help="streams per GPU of the multi-stream leg (BASELINE config 5: 64 independent clips); 0 = skip")
+    ap.add_argument("--no-tp", action="store_true", help="skip the tensor-parallel decode leg of an N > 1 run")
     ap.add_argument("--clip-seconds", type=float, default=CLIP_SECONDS, help="profiling only; the headline is 60 s")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
