@@ -207,6 +207,20 @@ def run_cuda(args, rank, world):
                  "ids_equal_single_stream": bool(np.array_equal(toks[:n0], gtoks[0, :n0])),
                  "api": "vox_cuda_group_encode(host PCM) x S + vox_cuda_group_decode -> ids on the host"}
         L.vox_cuda_group_free(g)
+        # the same pass with fp16 K/V rings (the reference's GPU default): reported beside, not as, the number above
+        g16 = vc.check(L.vox_cuda_group_create_ex(model, S, T + 1, 16), "group_create_ex")
+        gtoks32 = gtoks.copy()
+        g = g16
+        group_pass()
+        barrier()
+        t0 = time.perf_counter()
+        enc_s, dec_s, gsteps = group_pass()
+        barrier()
+        t_group16 = max_over_ranks(time.perf_counter() - t0)
+        multi["fp16_kv"] = {"value": S * args.clip_seconds * world / t_group16, "unit": UNIT,
+                            "ms_per_lock_step": float(gms.value) / gsteps, "decode_s": dec_s,
+                            "ids_equal_fp32_kv": bool(np.array_equal(gtoks, gtoks32))}
+        L.vox_cuda_group_free(g16)
     # ---- tensor-parallel single-stream decode over the N GPUs of this run (north star: "reported at
     # 2/4/8 GPUs"): every rank encodes + prefills the SAME clip, the greedy steps are sharded by kv head /
     # FFN rows / vocabulary with the wo / w2 sums exchanged through NVLink peer memory (csrc/dec_tp.cu) ----

@@ -225,6 +225,11 @@ int   vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, 
  *                              [n_streams][max_tokens], counts_out[i] = ids written for stream i
  *                              (the caller truncates at EOS = 2); returns the number of steps */
 vox_cuda_group_t *vox_cuda_group_create(vox_cuda_model_t *m, int n_streams, int max_positions);
+/* kv_bits 32 = the call above; 16 = K/V rings in fp16, the reference's GPU default ("fp16 KV",
+ * voxtral.c:189-190): rows are rounded once when appended, scores / softmax / output
+ * stay fp32.  Half the K/V bytes per lock step.  Not bit-comparable with the fp32 BLAS oracle:
+ * tests assert equal greedy ids on the test clips (top-2 margins ~1e-1 vs ~1e-3 of rounding). */
+vox_cuda_group_t *vox_cuda_group_create_ex(vox_cuda_model_t *m, int n_streams, int max_positions, int kv_bits);
 void vox_cuda_group_free(vox_cuda_group_t *g);
 int  vox_cuda_group_streams(const vox_cuda_group_t *g);
 int  vox_cuda_group_encode(vox_cuda_group_t *g, int stream, const float *pcm, int n_samples, int n_frames);

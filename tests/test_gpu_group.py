@@ -169,3 +169,35 @@ def test_group_64_streams_60s_properties(full_env):
             assert np.array_equal(toks[i, :761], ref), i
     finally:
         e.L.vox_cuda_group_free(g)
+
+
+def test_group_fp16_kv_ids_equal_fp32_kv(full_env):
+    """K/V rings in fp16 (the reference's GPU default, voxtral.c:189-190).  Not bit-comparable
+    with the fp32 BLAS oracle, so the statement is on ids: rows are rounded once (relative 2^-11), scores /
+    softmax / output stay fp32, and on the test clips (top-2 logit margins ~1e-1 on this checkpoint) the
+    greedy ids equal those of the fp32 rings - which test_group_tokens_equal_single_stream ties to the
+    single-stream path and test_gpu_golden.py to the reference.  Ragged lengths + an empty slot as there."""
+    e = full_env
+    clips = [_clip(2.0, 5), _clip(3.1, 11), _clip(2.4, 12)]
+    assert not e.L.vox_cuda_group_create_ex(e.model, 4, 128, 8)           # only 32 and 16 exist
+
+    def run(bits):
+        g = e.L.vox_cuda_group_create_ex(e.model, 4, 128, bits)
+        assert g, e.vc.last_error()
+        try:
+            for i, (buf, nf) in enumerate(clips):
+                assert e.L.vox_cuda_group_encode(g, i if i < 2 else 3, e.vc.fptr(buf), len(buf), nf) > 39
+            toks = np.full((4, 64), -7, np.int32)
+            counts = np.zeros(4, np.int32)
+            assert e.L.vox_cuda_group_decode(g, 39, e.vc.iptr(toks), 64, e.vc.iptr(counts), None) > 0, e.vc.last_error()
+            toks2 = np.full((4, 64), -7, np.int32)                        # second decode: clean slate
+            assert e.L.vox_cuda_group_decode(g, 39, e.vc.iptr(toks2), 64, e.vc.iptr(counts), None) > 0
+            assert np.array_equal(toks, toks2)
+            return toks, counts.copy()
+        finally:
+            e.L.vox_cuda_group_free(g)
+
+    t32, c32 = run(32)
+    t16, c16 = run(16)
+    assert c32.tolist() == c16.tolist() and c32[2] == 0 and c32[0] > 0
+    assert np.array_equal(t32, t16)

@@ -44,9 +44,10 @@ __global__ void __launch_bounds__(256) group_norm_kernel(
              out, red, SyncThreads());
 }
 
+template <class KV>
 __global__ void __launch_bounds__(256, 2) group_attn_kernel(
     const float *__restrict__ part, int n_split, long split_stride, const Slot *__restrict__ slots,
-    const float *__restrict__ inv_freq, float *__restrict__ kv_k, float *__restrict__ kv_v, size_t stream_stride,
+    const float *__restrict__ inv_freq, KV *__restrict__ kv_k, KV *__restrict__ kv_v, size_t stream_stride,
     int ring_mask, uint16_t *__restrict__ out) {
     __shared__ __align__(16) AttnSmem sm;
     tcx::pdl_launch_dependents();
@@ -64,6 +65,18 @@ __global__ void __launch_bounds__(1024) group_argmax_kernel(const float *__restr
     argmax_row<1024>(blockIdx.x, threadIdx.x, logits, slots, tokens, step, n_streams, sv, si, SyncThreads());
 }
 
+// kv16: prompt rows written by the prefill as fp32 [n_dec][128][1024] -> the stream's fp16 ring
+__global__ void __launch_bounds__(256) group_kv_round_kernel(const float *__restrict__ src_k, const float *__restrict__ src_v,
+                                                             __half *__restrict__ dst_k, __half *__restrict__ dst_v,
+                                                             size_t kv_layer, int ring_mask) {
+    const int l = blockIdx.y, row = blockIdx.x;
+    const size_t s = ((size_t)l * 128 + row) * DEC_KVDIM, d = (size_t)l * kv_layer + (size_t)(row & ring_mask) * DEC_KVDIM;
+    for (int i = threadIdx.x; i < DEC_KVDIM; i += 256) {
+        dst_k[d + i] = __float2half_rn(src_k[s + i]);
+        dst_v[d + i] = __float2half_rn(src_v[s + i]);
+    }
+}
+
 __global__ void __launch_bounds__(256) group_embed_rows_kernel(const int *__restrict__ tokens, const float *__restrict__ adapter,
                                                                const uint16_t *__restrict__ tok_emb, float *__restrict__ x) {
     const int r = blockIdx.x;
@@ -77,7 +90,8 @@ __global__ void __launch_bounds__(256) group_embed_rows_kernel(const int *__rest
 
 extern "C" void vox_cuda_group_free(vox_cuda_group_t *g) {
     if (!g) return;
-    cudaFree(g->kv_k); cudaFree(g->kv_v); cudaFree(g->adapter); cudaFree(g->d_slots); cudaFree(g->x);
+    cudaFree(g->kv_k); cudaFree(g->kv_v); cudaFree(g->kv_k16); cudaFree(g->kv_v16); cudaFree(g->pf_k); cudaFree(g->pf_v);
+    cudaFree(g->adapter); cudaFree(g->d_slots); cudaFree(g->x);
     cudaFree(g->xn_b); cudaFree(g->att_b); cudaFree(g->hh_b); cudaFree(g->part); cudaFree(g->logits);
     cudaFree(g->d_tokens); cudaFree(g->pf_x); cudaFree(g->pf_tok);
     if (g->ev0) cudaEventDestroy(g->ev0);
@@ -94,13 +108,20 @@ static int galloc(void **p, size_t bytes, bool zero) {
 }
 
 extern "C" vox_cuda_group_t *vox_cuda_group_create(vox_cuda_model_t *m, int n_streams, int max_positions) {
-    if (!m || n_streams < 1 || n_streams > MAX_STREAMS || max_positions < 2) {
-        vox_set_error("group_create: need 1..%d streams and max_positions >= 2", MAX_STREAMS);
+    return vox_cuda_group_create_ex(m, n_streams, max_positions, 32);
+}
+
+// kv_bits = 32: K/V rings in fp32 (the reference's CPU / BLAS layout: ids equal the reference);
+// kv_bits = 16: fp16 rings, the reference's GPU default (voxtral.c:189-190, kv_cache_switch_to_fp32 is the
+// opt-out there): half the K/V bytes per step; see DESIGN.md 4.8 for the tolerance statement.
+extern "C" vox_cuda_group_t *vox_cuda_group_create_ex(vox_cuda_model_t *m, int n_streams, int max_positions, int kv_bits) {
+    if (!m || n_streams < 1 || n_streams > MAX_STREAMS || max_positions < 2 || (kv_bits != 32 && kv_bits != 16)) {
+        vox_set_error("group_create: need 1..%d streams, max_positions >= 2, kv_bits 32 or 16", MAX_STREAMS);
         return nullptr;
     }
     vox_cuda_group *g = (vox_cuda_group *)calloc(1, sizeof(vox_cuda_group));
     if (!g) return nullptr;
-    g->m = m; g->B = n_streams; g->max_pos = max_positions;
+    g->m = m; g->B = n_streams; g->max_pos = max_positions; g->kv16 = kv_bits == 16;
     g->NB = n_streams <= 32 ? 32 : (n_streams <= 64 ? 64 : 128);
     int cap = 64;
     while (cap < max_positions && cap < DEC_WINDOW) cap <<= 1;      // ring of min(window, pow2 >= positions) rows
@@ -110,7 +131,13 @@ extern "C" vox_cuda_group_t *vox_cuda_group_create(vox_cuda_model_t *m, int n_st
     g->eng = vox_cuda_state_create(m);
     bool ok = g->eng != nullptr;
     const size_t B = n_streams, NB = g->NB;
-    ok = ok && !galloc((void **)&g->kv_k, g->kv_stream * B * 4, false) && !galloc((void **)&g->kv_v, g->kv_stream * B * 4, false);
+    if (g->kv16) {
+        ok = ok && !galloc((void **)&g->kv_k16, g->kv_stream * B * 2, false) && !galloc((void **)&g->kv_v16, g->kv_stream * B * 2, false);
+        ok = ok && !galloc((void **)&g->pf_k, (size_t)m->n_dec * 128 * DEC_KVDIM * 4, false) &&
+             !galloc((void **)&g->pf_v, (size_t)m->n_dec * 128 * DEC_KVDIM * 4, false);
+    } else {
+        ok = ok && !galloc((void **)&g->kv_k, g->kv_stream * B * 4, false) && !galloc((void **)&g->kv_v, g->kv_stream * B * 4, false);
+    }
     ok = ok && !galloc((void **)&g->adapter, B * max_positions * DEC_DIM * 4, false);
     ok = ok && !galloc((void **)&g->d_slots, B * sizeof(Slot), true);
     ok = ok && !galloc((void **)&g->x, B * DEC_DIM * 4, true);
@@ -137,7 +164,7 @@ extern "C" vox_cuda_group_t *vox_cuda_group_create(vox_cuda_model_t *m, int n_st
         g->op_logits.out_f32 = g->logits; g->op_logits.ldo = VOCAB; g->op_logits.split_stride = 0;
     }
     if (!ok) { vox_cuda_group_free(g); return nullptr; }
-    group_mega_init(g);          // persistent step kernel, opt-in (VOX_CUDA_GROUP_MEGA=1); default: kernel per op + PDL
+    if (!g->kv16) group_mega_init(g);   // persistent step kernel, opt-in (VOX_CUDA_GROUP_MEGA=1, fp32 rings only); default: kernel per op + PDL
     return g;
 }
 
@@ -180,8 +207,14 @@ static int group_step(vox_cuda_group *g, int step) {
                                 L.attn_norm, nullptr, g->xn_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_qkv[l])) return -1;
-        CUDA_TRY(launch_pdl(group_attn_kernel, dim3(B, DEC_KVH), 256, 0, st, g->part, KS_QKV, (long)B * DEC_QKV, g->d_slots,
-                            m->inv_freq_dec, g->kv_k + l * g->kv_layer, g->kv_v + l * g->kv_layer, g->kv_stream, g->mask, g->att_b));
+        if (g->kv16)
+            CUDA_TRY(launch_pdl(group_attn_kernel<__half>, dim3(B, DEC_KVH), 256, 0, st, (const float *)g->part, KS_QKV, (long)B * DEC_QKV,
+                                (const Slot *)g->d_slots, (const float *)m->inv_freq_dec, g->kv_k16 + l * g->kv_layer,
+                                g->kv_v16 + l * g->kv_layer, g->kv_stream, g->mask, g->att_b));
+        else
+            CUDA_TRY(launch_pdl(group_attn_kernel<float>, dim3(B, DEC_KVH), 256, 0, st, (const float *)g->part, KS_QKV, (long)B * DEC_QKV,
+                                (const Slot *)g->d_slots, (const float *)m->inv_freq_dec, g->kv_k + l * g->kv_layer,
+                                g->kv_v + l * g->kv_layer, g->kv_stream, g->mask, g->att_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_wo[l])) return -1;
         CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_WO, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
@@ -233,19 +266,31 @@ extern "C" int vox_cuda_group_decode(vox_cuda_group_t *g, int prompt_len, int *t
     CUDA_TRY(cudaMemcpyAsync(g->pf_tok, prompt, (size_t)n_pre * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(g->d_slots, h_slots, (size_t)B * sizeof(Slot), cudaMemcpyHostToDevice, st));
     for (int b = 0; b < B; b++) {
-        float *kb = g->kv_k + (size_t)b * g->kv_stream, *vb = g->kv_v + (size_t)b * g->kv_stream;
+        float *kb = g->kv16 ? g->pf_k : g->kv_k + (size_t)b * g->kv_stream;
+        float *vb = g->kv16 ? g->pf_v : g->kv_v + (size_t)b * g->kv_stream;
         if (!g->count[b]) {
             // idle slot: one zero K/V row per layer so that its (ignored) attention reads initialised memory
             for (int l = 0; l < m->n_dec; l++) {
-                CUDA_TRY(cudaMemsetAsync(kb + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 4, st));
-                CUDA_TRY(cudaMemsetAsync(vb + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 4, st));
+                if (g->kv16) {
+                    CUDA_TRY(cudaMemsetAsync(g->kv_k16 + (size_t)b * g->kv_stream + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 2, st));
+                    CUDA_TRY(cudaMemsetAsync(g->kv_v16 + (size_t)b * g->kv_stream + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 2, st));
+                } else {
+                    CUDA_TRY(cudaMemsetAsync(kb + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 4, st));
+                    CUDA_TRY(cudaMemsetAsync(vb + l * g->kv_layer, 0, (size_t)(n_pre + 1) * DEC_KVDIM * 4, st));
+                }
             }
             continue;
         }
         group_embed_rows_kernel<<<n_pre, 256, 0, st>>>(g->pf_tok, g->adapter + (size_t)b * g->max_pos * DEC_DIM, m->tok_emb, g->pf_x);
         LAUNCHED();
         int pos = 0, n_valid = 0;
-        if (dec_prefill_into(g->eng, g->pf_x, n_pre, kb, vb, g->kv_layer, g->mask, &pos, &n_valid)) return -1;
+        if (g->kv16) {
+            // the prompt rows attend to each other in fp32 (38 rows; nothing is re-read from the ring), then are rounded once
+            if (dec_prefill_into(g->eng, g->pf_x, n_pre, kb, vb, (size_t)128 * DEC_KVDIM, 127, &pos, &n_valid)) return -1;
+            group_kv_round_kernel<<<dim3(n_pre, m->n_dec), 256, 0, st>>>(kb, vb, g->kv_k16 + (size_t)b * g->kv_stream,
+                                                                         g->kv_v16 + (size_t)b * g->kv_stream, g->kv_layer, g->mask);
+            LAUNCHED();
+        } else if (dec_prefill_into(g->eng, g->pf_x, n_pre, kb, vb, g->kv_layer, g->mask, &pos, &n_valid)) return -1;
     }
     if (g->mega) {
         if (group_mega_run(g, n_steps)) return -1;

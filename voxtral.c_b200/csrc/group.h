@@ -1,5 +1,6 @@
 // group.h - host-side state of a stream group (api_group.cu, group_mega.cu)
 #pragma once
+#include <cuda_fp16.h>
 #include "vox_internal.h"
 #include "gemm_wt.h"
 #include "group_dev.cuh"
@@ -8,8 +9,11 @@ struct vox_cuda_group {
     vox_cuda_model *m;
     vox_cuda_state *eng;         // encoder engine + prefill scratch; its stream orders all group work
     int B, NB, max_pos, cap, mask;
-    float *kv_k, *kv_v;          // [B][n_dec][cap][1024]
-    size_t kv_layer, kv_stream;  // floats
+    float *kv_k, *kv_v;          // [B][n_dec][cap][1024] fp32 rings (kv16 == 0)
+    __half *kv_k16, *kv_v16;     // the same rings as fp16 (kv16 == 1: vox_cuda_group_create_ex(..., 16))
+    float *pf_k, *pf_v;          // kv16: fp32 rows [n_dec][128][1024] the prompt prefill writes before they are rounded into the ring
+    int kv16;
+    size_t kv_layer, kv_stream;  // elements
     float *adapter;              // [B][max_pos][3072]
     int count[grp::MAX_STREAMS];      // adapter rows per stream (0 = not encoded)
     grp::Slot *d_slots;

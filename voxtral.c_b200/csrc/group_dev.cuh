@@ -4,6 +4,7 @@
 // kernel, a named barrier among the worker warps of the persistent kernel).  Data another CTA may have
 // written during the same kernel is read with ld.global.cg.
 #pragma once
+#include <cuda_fp16.h>
 #include "vox_internal.h"
 
 namespace grp {
@@ -98,16 +99,29 @@ struct AttnSmem {
     float qs[4][DEC_HD];
     float wsm[AT_WARPS][4][DEC_HD + 4];
 };
-template <class Sync>
+// K/V element type: float (the reference's CPU / BLAS layout, voxtral_decoder.c:703-705) or __half (the
+// reference's GPU default, "fp16 KV", voxtral.c:189-190): rows are rounded once when appended and widened
+// in registers when read; scores, softmax and the output stay fp32.
+__device__ __forceinline__ float4 ld_kv4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ float4 ld_kv4(const __half *p) {
+    const uint2 u = __ldcg(reinterpret_cast<const uint2 *>(p));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st_kv(float *p, float v) { *p = v; }
+__device__ __forceinline__ void st_kv(__half *p, float v) { *p = __float2half_rn(v); }
+
+template <class Sync, class KV>
 __device__ __forceinline__ void attn_task(
     int b, int kvh, int tid, const float *__restrict__ part, int n_split, long split_stride, const Slot *__restrict__ slots,
-    const float *__restrict__ inv_freq, float *__restrict__ kv_k, float *__restrict__ kv_v, size_t stream_stride,
+    const float *__restrict__ inv_freq, KV *__restrict__ kv_k, KV *__restrict__ kv_v, size_t stream_stride,
     int ring_mask, uint16_t *__restrict__ out, AttnSmem &sm, Sync sync) {
     const int w = tid >> 5, lane = tid & 31;
     float (*qs)[DEC_HD] = sm.qs;
     float (*wsm)[4][DEC_HD + 4] = sm.wsm;
     const int pos = __ldcg(&slots[b].pos);
-    float *kc = kv_k + (size_t)b * stream_stride, *vc = kv_v + (size_t)b * stream_stride;
+    KV *kc = kv_k + (size_t)b * stream_stride, *vc = kv_v + (size_t)b * stream_stride;
     const size_t slot_new = (size_t)(pos & ring_mask) * DEC_KVDIM + (size_t)kvh * DEC_HD;
     {
         // 256 q pairs (4 heads), 64 k pairs, 128 v values of this kv head; partial sums in split order
@@ -125,12 +139,12 @@ __device__ __forceinline__ void attn_task(
                 const float c = cosf(angle), sn = sinf(angle);
                 const float y0 = x0 * c - x1 * sn, y1 = x0 * sn + x1 * c;
                 if (i < 256) { qs[i >> 6][2 * (i & 63)] = y0; qs[i >> 6][2 * (i & 63) + 1] = y1; }
-                else { kc[slot_new + 2 * (i - 256)] = y0; kc[slot_new + 2 * (i - 256) + 1] = y1; }
+                else { st_kv(kc + slot_new + 2 * (i - 256), y0); st_kv(kc + slot_new + 2 * (i - 256) + 1, y1); }
             } else {
                 const int d = i - 320;
                 float x0 = 0.f;
                 for (int s = 0; s < n_split; s++) x0 += __ldcg(pr + (size_t)s * split_stride + DEC_QDIM + DEC_KVDIM + kvh * DEC_HD + d);
-                vc[slot_new + d] = x0;
+                st_kv(vc + slot_new + d, x0);
             }
         }
     }
@@ -154,8 +168,8 @@ __device__ __forceinline__ void attn_task(
         #pragma unroll
         for (int i = 0; i < 8; i++) {
             const int slot = (first + j0 + min(i, nv - 1)) & ring_mask;     // clamp: always a valid row
-            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
-            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+            kf[i] = ld_kv4(kc + (size_t)slot * DEC_KVDIM + hoff);
+            vf[i] = ld_kv4(vc + (size_t)slot * DEC_KVDIM + hoff);
         }
         float v[32];
         #pragma unroll

@@ -71,6 +71,7 @@ SIGNATURES = {
     "vox_cuda_gemm_bf16_streams": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, C.c_int, C.c_int, f32p]),
     "vox_cuda_bench_gemm_streams": (C.c_float, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "vox_cuda_group_create": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
+    "vox_cuda_group_create_ex": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "vox_cuda_group_free": (None, [C.c_void_p]),
     "vox_cuda_group_streams": (C.c_int, [C.c_void_p]),
     "vox_cuda_group_encode": (C.c_int, [C.c_void_p, C.c_int, f32p, C.c_int, C.c_int]),
