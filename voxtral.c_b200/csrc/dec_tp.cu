@@ -778,9 +778,14 @@ static cudaError_t tp_partial(cudaStream_t st, const TpDev &td, int a_idx, const
     return tp_launch_partial<8, 5>(st, td, a_idx, v, W, K);
 }
 
+static int tp_grid_cap(void) {
+    static int cap = 0;
+    if (!cap) { const char *e = getenv("VOX_CUDA_TP_GRID"); cap = e && atoi(e) > 0 ? atoi(e) : 148; }
+    return cap;
+}
 static inline int tp_grid(int rows) {
     int g = (rows / FULL_NW + TP_WARPS - 1) / TP_WARPS;
-    return g > 148 ? 148 : g;
+    return g > tp_grid_cap() ? tp_grid_cap() : g;
 }
 
 static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
@@ -819,7 +824,8 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
         }
         for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN));
     }
-    const int nblk = tp_grid(VOCAB / G);
+    int nblk = (VOCAB / G / FULL_NW + TP_WARPS - 1) / TP_WARPS;      // 100-400 MB: bandwidth-bound, one CTA per SM
+    if (nblk > 148) nblk = 148;
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
         CUDA_TRY(launch_pdl(tp_logits_kernel, nblk, TP_THREADS, 0, st, R.dev, 2 * L - 1, (const float *)(R.xbuf + DEC_DIM), m->dec_norm,
