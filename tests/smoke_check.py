@@ -3,7 +3,7 @@ checked against the oracle (oracle/_ref, the compiled reference BLAS path).
 
 Runs: log-mel of 1 s of audio, then prefill(38) + 2 greedy decoder steps on the
 random-init checkpoint, then the same two steps for two streams in lock step
-(stream group), all through the C ABI (libvoxcuda.so).  Fails loudly if
+(stream group) and as a 2-rank tensor-parallel decode, all through the C ABI (libvoxcuda.so).  Fails loudly if
 the CUDA library is missing - there is no CPU fallback.
 """
 import numpy as np
@@ -74,6 +74,18 @@ def run():
             assert steps == 2 and gt[0, :2].tolist() == ref_toks and gt[1, :2].tolist() == ref_toks
         finally:
             L.vox_cuda_group_free(g)
+        # ---- and tensor-parallel: 2 ranks on this GPU in lock step (the multi-GPU shard arithmetic + exchange windows) ----
+        tp = vc.check(L.vox_cuda_tp_create_local(model, 2), "tp_create_local")
+        try:
+            ts = L.vox_cuda_tp_state(tp)
+            vc.check(L.vox_cuda_adapter_append(ts, vc.fptr(adapter), 40), "adapter_append")
+            vc.check(L.vox_cuda_decoder_prefill(ts, vc.fptr(emb), 38), "tp prefill")
+            tt = np.empty(2, np.int32)
+            vc.check(L.vox_cuda_tp_decode(tp, 32, 38, 2, vc.iptr(tt), None), "tp_decode")
+            print(f"smoke: tensor-parallel (2 ranks, lock step) ids {tt.tolist()}")
+            assert tt.tolist() == ref_toks
+        finally:
+            L.vox_cuda_tp_free(tp)
         print("smoke: kernel launches so far:", L.vox_cuda_launch_count())
     finally:
         L.vox_cuda_state_free(st)
