@@ -275,6 +275,18 @@ int vox_cuda_sgemm_bf16(vox_cuda_model_t *m, int M, int N, int K, const float *A
 int vox_cuda_gemm_bf16_tc(int M, int N, int K, const float *A, const uint16_t *B_bf16,
                           const float *bias, int flags, float *C);
 
+/* ---- audio ingestion on the device --------------------------------------
+ * The arithmetic of vox_parse_wav_buffer (voxtral_audio.c:94-137) and of the raw s16le stdin reader
+ * (:199-202) without the container parsing: interleaved s16 frames -> mono (mean of the channels)
+ * / 32768 -> 16 kHz by linear interpolation when sample_rate != 16000.  Bit-identical to the
+ * reference compiled in strict IEEE mode.  Host pointers in and out; returns the number of output
+ * samples (vox_cuda_pcm_resampled_len) or -1. */
+int vox_cuda_pcm_resampled_len(int n_frames, int sample_rate);
+int vox_cuda_pcm_from_s16(const int16_t *pcm, int n_frames, int channels, int sample_rate, float *out, int out_cap);
+/* the microphone silence gate's energy (main.c:262-292): rms_out[w] = sqrt(mean(x^2)) of consecutive
+ * windows of `window` samples (160 = 10 ms there); returns n / window */
+int vox_cuda_window_rms(const float *samples, int n, int window, float *rms_out);
+
 /* ---- tensor-parallel single-stream decoder (csrc/dec_tp.cu) ----------
  * vox_decoder_forward (voxtral_decoder.c:640-780) cut across G = 1/2/4/8 GPUs, one
  * process per GPU: rank r owns kv heads [r*8/G, ...) with their query heads (rows of

@@ -172,3 +172,25 @@ def strict_stream_mel(samples, delay_tokens=6, chunk=0):
     a = np.ctypeslib.as_array(p, shape=(n.value, 128)).copy()
     L.refshim_free(p)
     return a
+
+
+def make_wav(frames_s16, channels, sample_rate):
+    """A minimal RIFF/WAVE file image (16-bit PCM) around interleaved s16 frames."""
+    import struct
+    data = np.asarray(frames_s16, np.int16).tobytes()
+    hdr = b"RIFF" + struct.pack("<I", 36 + len(data)) + b"WAVE" + b"fmt " + struct.pack(
+        "<IHHIIHH", 16, 1, channels, sample_rate, sample_rate * channels * 2, channels * 2, 16)
+    return hdr + b"data" + struct.pack("<I", len(data)) + data
+
+
+def ref_parse_wav(wav_bytes, strict=True):
+    """vox_parse_wav_buffer of the compiled reference (voxtral_audio.c:49-141) -> f32 samples."""
+    L = C.CDLL(REF_STRICT_SO if strict else REF_SO)
+    L.vox_parse_wav_buffer.restype = f32p
+    L.vox_parse_wav_buffer.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
+    n = C.c_int(0)
+    p = L.vox_parse_wav_buffer(wav_bytes, len(wav_bytes), C.byref(n))
+    assert p, "reference rejected the WAV image"
+    out = np.ctypeslib.as_array(p, shape=(n.value,)).copy()
+    C.CDLL(None).free(C.cast(p, C.c_void_p))
+    return out

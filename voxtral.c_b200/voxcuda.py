@@ -93,6 +93,9 @@ SIGNATURES = {
     "vox_cuda_transcribe": (C.c_int, [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, i32p, C.c_int, C.POINTER(C.c_float)]),
     "vox_cuda_gemm_bf16_tc": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, f32p, C.c_int, f32p]),
     "vox_cuda_bench_decoder_steps": (C.c_float, [C.c_void_p, C.c_int, C.c_int, C.c_int, i32p]),
+    "vox_cuda_pcm_resampled_len": (C.c_int, [C.c_int, C.c_int]),
+    "vox_cuda_pcm_from_s16": (C.c_int, [C.POINTER(C.c_int16), C.c_int, C.c_int, C.c_int, f32p, C.c_int]),
+    "vox_cuda_window_rms": (C.c_int, [f32p, C.c_int, C.c_int, f32p]),
     "vox_cuda_tp_create": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_tp_create_local": (C.c_void_p, [C.c_void_p, C.c_int]),
     "vox_cuda_tp_export": (C.c_int, [C.c_void_p, C.c_void_p]),
