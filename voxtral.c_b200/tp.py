@@ -33,14 +33,20 @@ def gather_handles(mine, dist, world):
     return b"".join(bytes(o.cpu().numpy().tobytes()) for o in outs)
 
 
-def create_attached(L, model, rank, world, dist):
+def create_attached(L, model, rank, world, dist, barrier=True):
+    """Create this process's rank and map every peer's window.  Collective: all ranks call it together (the
+    handle all-gather happens even on a rank whose export failed, so nobody is left waiting)."""
     tp = vc.check(L.vox_cuda_tp_create(model, rank, world), "tp_create")
     if world > 1:
         h = (C.c_ubyte * vc.TP_HANDLE_BYTES)()
-        vc.check(L.vox_cuda_tp_export(tp, h), "tp_export")
+        rc = L.vox_cuda_tp_export(tp, h)
         allh = gather_handles(bytes(h), dist, world)
         assert len(allh) == world * vc.TP_HANDLE_BYTES
         buf = (C.c_ubyte * len(allh)).from_buffer_copy(allh)
-        vc.check(L.vox_cuda_tp_connect(tp, buf), "tp_connect")
-        dist.barrier()
+        if rc != 0 or L.vox_cuda_tp_connect(tp, buf) != 0:
+            err = vc.last_error()
+            L.vox_cuda_tp_free(tp)
+            raise RuntimeError("tp attach failed: " + err)
+        if barrier:
+            dist.barrier()
     return tp
