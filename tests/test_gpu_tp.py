@@ -97,3 +97,27 @@ def test_tp_two_processes_two_gpus(full_env):
                          capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "ids_equal_single_stream=True" in out.stdout
+
+
+@pytest.mark.parametrize("mega", ["1", "0"])
+def test_tp_single_rank_world_paths(full_env, monkeypatch, mega):
+    """world = 1 through vox_cuda_tp_create: the persistent cooperative step kernel (dec_tp_mega.cu, default) and
+    the kernel-per-op graph (VOX_CUDA_TP_MEGA=0) both give the single-stream ids; a second clip on the same
+    handle continues the exchange sequence numbers and the barrier generation."""
+    e = full_env
+    monkeypatch.setenv("VOX_CUDA_TP_MEGA", mega)
+    tp = e.L.vox_cuda_tp_create(e.model, 0, 1)
+    assert tp, e.vc.last_error()
+    try:
+        for seconds, seed in ((2.0, 5), (2.4, 12), (6.0, 3)):
+            buf, nf = _clip(seconds, seed)
+            want, want_logits = _single(e, buf, nf)
+            toks = np.empty(nf // 8 + 8, np.int32)
+            n = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+            assert n == len(want), e.vc.last_error()
+            assert toks[:n].tolist() == want
+            logits = np.empty(131072, np.float32)
+            assert e.L.vox_cuda_decoder_read_logits(e.L.vox_cuda_tp_state(tp), e.vc.fptr(logits)) == 0
+            assert float(np.abs(logits - want_logits).max()) < 2e-2
+    finally:
+        e.L.vox_cuda_tp_free(tp)
