@@ -459,9 +459,14 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
     tp->n_local = 1;
     if (tp_rank_init(tp, tp->r[0], rank)) { vox_cuda_tp_free(tp); return nullptr; }
     tp->connected = (world == 1);
-    {   // one persistent cooperative kernel per rank unless VOX_CUDA_TP_MEGA=0 (then: kernel-per-op CUDA graph)
+    {   // Two step engines with the same arithmetic and exchange protocol: one persistent cooperative kernel per rank
+        // (dec_tp_mega.cu) or the kernel-per-op CUDA graph above.  Measured (profiles/r01_j_tp_decode.md): the persistent
+        // kernel wins at 2 GPUs (1.08 vs 1.12 ms per token), the PDL-chained graph at 4 (0.82 vs 0.87): with a quarter of
+        // the bytes per phase a grid barrier costs more than a kernel boundary whose successor already runs beside it.
+        // VOX_CUDA_TP_MEGA=1 / 0 forces one or the other.
         const char *env = getenv("VOX_CUDA_TP_MEGA");
-        if (!(env && atoi(env) == 0)) tp->mega = tp_mega_create(m, world);
+        const bool want = env ? atoi(env) != 0 : world <= 2;
+        if (want) tp->mega = tp_mega_create(m, world);
     }
     return tp;
 }

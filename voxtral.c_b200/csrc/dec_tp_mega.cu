@@ -104,8 +104,7 @@ __device__ __forceinline__ void grid_barrier(const Args &a, unsigned long long &
     __syncthreads();
     if (threadIdx.x == 0) {
         target += gridDim.x;
-        __threadfence();
-        atomicAdd(a.bar, 1ull);
+        asm volatile("red.release.gpu.global.add.u64 [%0], %1;" :: "l"(a.bar), "l"(1ull) : "memory");
         if (ld_acquire_gpu_u64(a.bar) < target) {
             const unsigned long long t0 = globaltimer_ns();
             while (ld_acquire_gpu_u64(a.bar) < target)
@@ -115,42 +114,69 @@ __device__ __forceinline__ void grid_barrier(const Args &a, unsigned long long &
     __syncthreads();
 }
 
+// 4 consecutive values of one source rank: v holds a first read; spins until all 4 words carry seq
+__device__ __forceinline__ void ll_settle4(const TpDev &td, const uint2 *src, int p, unsigned seq, uint4 (&v)[2]) {
+    if (v[0].y == seq && v[0].w == seq && v[1].y == seq && v[1].w == seq) return;
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        v[0] = ld_ll2(src); v[1] = ld_ll2(src + 2);
+        if (v[0].y == seq && v[0].w == seq && v[1].y == seq && v[1].w == seq) return;
+        if (globaltimer_ns() - t0 > 8000000000ull) tp_timeout(td.rank, p, seq);
+    }
+}
+
 // x (shared, kept) += the G partials of exchange a_idx (rank order); RMSNorm * w (* (1 + ada)) -> vA / vB.
-// Written for few live registers (a prefetched row batch of up to 96 registers sits beside it): one 8-float
-// chunk and two peers at a time, x goes back to shared memory between the passes.
-template <bool REDUCE>
+// A thread owns three 4-float pieces of x (768 pieces over 256 threads) and reads the exchange words of all
+// its pieces from up to 4 source ranks in ONE round of loads (24 x 16 B in flight per thread, which is what
+// fits beside a prefetched row batch of 96 registers); 8 ranks take two rounds, still in rank order.
+template <bool REDUCE, int G>
 __device__ __forceinline__ void x_reduce_norm(Smem &sm, const TpDev &td, int a_idx, unsigned seq,
                                               const float *__restrict__ nw, const float *__restrict__ ada) {
+    constexpr int NP = DEC_DIM / 4 / TP_THREADS;       // 3 pieces per thread
+    constexpr int PG = G < 4 ? G : 4;                  // source ranks per round
     const int t = threadIdx.x;
-    float ss = 0.f;
-    #pragma unroll 1
-    for (int c = t; c < DEC_DIM / 8; c += TP_THREADS) {
-        float4 a = sm.xrA[c], b = sm.xrB[c];
-        if (REDUCE) {
-            #pragma unroll 1
-            for (int p0 = 0; p0 < td.world; p0 += 2) {
-                uint4 v[2][4];
-                #pragma unroll
-                for (int pp = 0; pp < 2; pp++)
-                    if (p0 + pp < td.world) {
-                        const uint2 *src = td.self->part[a_idx & 1][p0 + pp] + c * 8;
-                        #pragma unroll
-                        for (int k = 0; k < 4; k++) v[pp][k] = ld_ll2(src + 2 * k);
-                    }
-                #pragma unroll
-                for (int pp = 0; pp < 2; pp++)
-                    if (p0 + pp < td.world) {
-                        tp_ll_settle8(td, td.self->part[a_idx & 1][p0 + pp] + c * 8, p0 + pp, seq, v[pp]);
-                        a.x += __uint_as_float(v[pp][0].x); a.y += __uint_as_float(v[pp][0].z);
-                        a.z += __uint_as_float(v[pp][1].x); a.w += __uint_as_float(v[pp][1].z);
-                        b.x += __uint_as_float(v[pp][2].x); b.y += __uint_as_float(v[pp][2].z);
-                        b.z += __uint_as_float(v[pp][3].x); b.w += __uint_as_float(v[pp][3].z);
-                    }
-            }
-            sm.xrA[c] = a; sm.xrB[c] = b;
-        }
-        ss += f4sq(a) + f4sq(b);
+    float4 x[NP];
+    #pragma unroll
+    for (int i = 0; i < NP; i++) {
+        const int hc = t + i * TP_THREADS;
+        x[i] = (hc & 1) ? sm.xrB[hc >> 1] : sm.xrA[hc >> 1];
     }
+    if (REDUCE) {
+        #pragma unroll
+        for (int p0 = 0; p0 < G; p0 += PG) {
+            uint4 v[NP][PG][2];
+            #pragma unroll
+            for (int i = 0; i < NP; i++)
+                #pragma unroll
+                for (int pp = 0; pp < PG; pp++) {
+                    const uint2 *src = td.self->part[a_idx & 1][p0 + pp] + (t + i * TP_THREADS) * 4;
+                    v[i][pp][0] = ld_ll2(src); v[i][pp][1] = ld_ll2(src + 2);
+                }
+            #pragma unroll
+            for (int i = 0; i < NP; i++)
+                #pragma unroll
+                for (int pp = 0; pp < PG; pp++) {
+                    ll_settle4(td, td.self->part[a_idx & 1][p0 + pp] + (t + i * TP_THREADS) * 4, p0 + pp, seq, v[i][pp]);
+                    x[i].x += __uint_as_float(v[i][pp][0].x); x[i].y += __uint_as_float(v[i][pp][0].z);
+                    x[i].z += __uint_as_float(v[i][pp][1].x); x[i].w += __uint_as_float(v[i][pp][1].z);
+                }
+        }
+        #pragma unroll
+        for (int i = 0; i < NP; i++) {
+            const int hc = t + i * TP_THREADS;
+            if (hc & 1) sm.xrB[hc >> 1] = x[i]; else sm.xrA[hc >> 1] = x[i];
+        }
+    }
+    // norm weights after the poll (registers); their L2 latency hides behind the two block syncs below
+    float4 wn[NP], wd[NP];
+    #pragma unroll
+    for (int i = 0; i < NP; i++) {
+        wn[i] = *reinterpret_cast<const float4 *>(nw + (t + i * TP_THREADS) * 4);
+        if (ada) wd[i] = *reinterpret_cast<const float4 *>(ada + (t + i * TP_THREADS) * 4);
+    }
+    float ss = 0.f;
+    #pragma unroll
+    for (int i = 0; i < NP; i++) ss += f4sq(x[i]);
     ss = warp_sum(ss);
     __syncthreads();                                   // sm.red and vA / vB of the previous phase are no longer read
     if ((t & 31) == 0) sm.red[t >> 5] = ss;
@@ -159,20 +185,13 @@ __device__ __forceinline__ void x_reduce_norm(Smem &sm, const TpDev &td, int a_i
     #pragma unroll
     for (int w = 0; w < TP_WARPS; w++) tot += sm.red[w];
     const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
-    #pragma unroll 1
-    for (int c = t; c < DEC_DIM / 8; c += TP_THREADS) {
-        float4 u = sm.xrA[c], v = sm.xrB[c];
-        const float4 wa = *reinterpret_cast<const float4 *>(nw + c * 8);
-        const float4 wb = *reinterpret_cast<const float4 *>(nw + c * 8 + 4);
-        u.x = u.x * rinv * wa.x; u.y = u.y * rinv * wa.y; u.z = u.z * rinv * wa.z; u.w = u.w * rinv * wa.w;
-        v.x = v.x * rinv * wb.x; v.y = v.y * rinv * wb.y; v.z = v.z * rinv * wb.z; v.w = v.w * rinv * wb.w;
-        if (ada) {
-            const float4 da = *reinterpret_cast<const float4 *>(ada + c * 8);
-            const float4 db = *reinterpret_cast<const float4 *>(ada + c * 8 + 4);
-            u.x *= (1.0f + da.x); u.y *= (1.0f + da.y); u.z *= (1.0f + da.z); u.w *= (1.0f + da.w);
-            v.x *= (1.0f + db.x); v.y *= (1.0f + db.y); v.z *= (1.0f + db.z); v.w *= (1.0f + db.w);
-        }
-        sm.vA[c] = u; sm.vB[c] = v;
+    #pragma unroll
+    for (int i = 0; i < NP; i++) {
+        const int hc = t + i * TP_THREADS;
+        float4 u = x[i];
+        u.x = u.x * rinv * wn[i].x; u.y = u.y * rinv * wn[i].y; u.z = u.z * rinv * wn[i].z; u.w = u.w * rinv * wn[i].w;
+        if (ada) { u.x *= (1.0f + wd[i].x); u.y *= (1.0f + wd[i].y); u.z *= (1.0f + wd[i].z); u.w *= (1.0f + wd[i].w); }
+        if (hc & 1) sm.vB[hc >> 1] = u; else sm.vA[hc >> 1] = u;
     }
     __syncthreads();
 }
@@ -240,8 +259,8 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tp_mega_kernel(const Args a) {
             const DecLayerDev &Wl = a.layers[l];
             float *kc = a.kv_k + l * kv_layer, *vc = a.kv_v + l * kv_layer;
             // ---- P1: qkv (voxtral_decoder.c:710-725) ----
-            if (l == 0) x_reduce_norm<false>(sm, td, 0, 0u, Wl.attn_norm, nullptr);
-            else        x_reduce_norm<true>(sm, td, 2 * l - 1, seq0 + 2 * l, Wl.attn_norm, nullptr);
+            if (l == 0) x_reduce_norm<false, G>(sm, td, 0, 0u, Wl.attn_norm, nullptr);
+            else        x_reduce_norm<true, G>(sm, td, 2 * l - 1, seq0 + 2 * l, Wl.attn_norm, nullptr);
             for (int b = gw; b < QKV_BATCHES;) {
                 float acc[F_NW];
                 wdot<F_NW, F_NCH, C::WMAX>(w, sm.vA, sm.vB, DEC_DIM, acc);
@@ -285,7 +304,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tp_mega_kernel(const Args a) {
             }
             // ---- P4: FFN gate / up (voxtral_decoder.c:741-757) ----
             wload<F_NW, F_NCH, C::WMAX>(w, Wl.w13 + (size_t)(td.rank * FFN_ROWS + gw * F_NW) * DEC_DIM, DEC_DIM, DEC_DIM, gw < FFN_BATCHES);
-            x_reduce_norm<true>(sm, td, 2 * l, seq0 + 2 * l + 1, Wl.ffn_norm, a.ada_scale + (size_t)l * DEC_DIM);
+            x_reduce_norm<true, G>(sm, td, 2 * l, seq0 + 2 * l + 1, Wl.ffn_norm, a.ada_scale + (size_t)l * DEC_DIM);
             for (int b = gw; b < FFN_BATCHES;) {
                 float acc[F_NW];
                 wdot<F_NW, F_NCH, C::WMAX>(w, sm.vA, sm.vB, DEC_DIM, acc);
@@ -318,7 +337,7 @@ __global__ void __launch_bounds__(TP_THREADS, 1) tp_mega_kernel(const Args a) {
             }
         }
         // ---- logits of this rank's vocabulary rows + first maximum (voxtral_decoder.c:765-779) ----
-        x_reduce_norm<true>(sm, td, 2 * L - 1, seq0 + 2 * L, a.dec_norm, nullptr);
+        x_reduce_norm<true, G>(sm, td, 2 * L - 1, seq0 + 2 * L, a.dec_norm, nullptr);
         float bv = -INFINITY; int bi = 0x7fffffff;
         for (int b = gw; b < VOC_BATCHES;) {
             float acc[F_NW];
