@@ -117,6 +117,8 @@ def run_cuda(args, rank, world):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # NCCL prints its version banner on stdout; stdout carries ONE JSON line
         dist.init_process_group("nccl")
 
     def barrier():
