@@ -121,3 +121,53 @@ def test_tp_single_rank_world_paths(full_env, monkeypatch, mega):
             assert float(np.abs(logits - want_logits).max()) < 2e-2
     finally:
         e.L.vox_cuda_tp_free(tp)
+
+
+@pytest.mark.parametrize("mode", ["lockstep2", "lockstep8", "persistent1"])
+def test_tp_window_wrap_matches_single_stream(full_env, monkeypatch, mode):
+    """BASELINE config 4 for the tensor-parallel step: start right before the 8192-position ring wraps with the
+    SAME injected K/V state and adapter rows as a single-stream state (whose wrap behaviour
+    tests/test_gpu_kvwrap.py pins to the reference's cache compaction) and step across the wrap: ids equal,
+    logits within 2e-2.  Exercises the sharded attention's ring arithmetic (full window, key splits, first
+    logical key) in the kernel-per-op engine (2 and 8 ranks in lock step) and in the persistent kernel."""
+    e = full_env
+    rng = np.random.default_rng(33)
+    start, n_steps = 8192 + 1060, 6
+    K = (0.3 * rng.standard_normal((26, 8192, 1024), dtype=np.float32))
+    V = (0.3 * rng.standard_normal((26, 8192, 1024), dtype=np.float32))
+    ad = (0.5 * rng.standard_normal((n_steps, 3072))).astype(np.float32)
+
+    def inject(s):
+        for l in range(26):
+            assert e.L.vox_cuda_decoder_kv_write(s, l, start - 8192, 8192, e.vc.fptr(K[l]), e.vc.fptr(V[l])) == 0
+        assert e.L.vox_cuda_decoder_set_position(s, start, 8192) == 0
+        assert e.L.vox_cuda_adapter_append(s, e.vc.fptr(ad), n_steps) >= 0, e.vc.last_error()
+
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        inject(st)
+        want = np.empty(n_steps, np.int32)
+        assert e.L.vox_cuda_decoder_run(st, 32, 0, n_steps, e.vc.iptr(want)) == n_steps, e.vc.last_error()
+        want_logits = np.empty(131072, np.float32)
+        assert e.L.vox_cuda_decoder_read_logits(st, e.vc.fptr(want_logits)) == 0
+    finally:
+        e.L.vox_cuda_state_free(st)
+    if mode == "persistent1":
+        monkeypatch.setenv("VOX_CUDA_TP_MEGA", "1")
+        tp = e.L.vox_cuda_tp_create(e.model, 0, 1)
+    else:
+        tp = e.L.vox_cuda_tp_create_local(e.model, int(mode[len("lockstep"):]))
+    assert tp, e.vc.last_error()
+    try:
+        ts = e.L.vox_cuda_tp_state(tp)
+        inject(ts)
+        got = np.empty(n_steps, np.int32)
+        assert e.L.vox_cuda_tp_decode(tp, 32, 0, n_steps, e.vc.iptr(got), None) == n_steps, e.vc.last_error()
+        assert got.tolist() == want.tolist()
+        assert e.L.vox_cuda_decoder_position(ts) == start + n_steps
+        logits = np.empty(131072, np.float32)
+        assert e.L.vox_cuda_decoder_read_logits(ts, e.vc.fptr(logits)) == 0
+        assert float(np.abs(logits - want_logits).max()) < 2e-2
+    finally:
+        e.L.vox_cuda_tp_free(tp)
