@@ -36,68 +36,65 @@
 
 // Prologue of the three consuming kernels: x = x_in (+ the G partials of exchange a_idx, in rank order),
 // CTA 0 keeps the new residual row in x_out, then RMSNorm (voxtral_kernels.c:475-492) and the (1 + ada)
-// scale (voxtral_decoder.c:742-745) into shared memory.  A thread owns at most two 8-float chunks and
-// keeps them in registers; every independent load (x, norm weight, ada, the first read of the exchange
-// words) is issued before anything is waited for.
+// scale (voxtral_decoder.c:742-745) into shared memory.  A thread owns three 4-float pieces of x (768 pieces
+// over 256 threads) and reads the exchange words of all its pieces from up to 4 source ranks in ONE round of
+// loads (24 x 16 B in flight per thread); 8 ranks take two rounds, still added in rank order.  Every
+// independent load (x, norm weight, ada, the first read of the exchange words) is issued before anything is
+// waited for.
+__device__ __forceinline__ void tp_ll_settle4(const TpDev &td, const uint2 *src, int p, unsigned seq, uint4 (&v)[2]) {
+    if (v[0].y == seq && v[0].w == seq && v[1].y == seq && v[1].w == seq) return;
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        v[0] = ld_ll2(src); v[1] = ld_ll2(src + 2);
+        if (v[0].y == seq && v[0].w == seq && v[1].y == seq && v[1].w == seq) return;
+        if (globaltimer_ns() - t0 > 8000000000ull) tp_timeout(td.rank, p, seq);
+    }
+}
+
 template <bool REDUCE>
 __device__ __forceinline__ void tp_load_x_norm(float4 *xA, float4 *xB, float *red, const TpDev &td, int a_idx,
                                                const float *__restrict__ x_in, float *__restrict__ x_out,
                                                const float *__restrict__ nw, const float *__restrict__ ada) {
-    constexpr int NC = (DEC_DIM / 8 + TP_THREADS - 1) / TP_THREADS;   // 2
+    constexpr int NP = DEC_DIM / 4 / TP_THREADS;       // 3 pieces per thread
     const int t = threadIdx.x;
-    float4 a[NC], b[NC], wa[NC], wb[NC], da[NC], db[NC];
+    float4 x[NP], wn[NP], wd[NP];
     #pragma unroll
-    for (int i = 0; i < NC; i++) {
-        const int c = t + i * TP_THREADS;
-        if (c < DEC_DIM / 8) {
-            a[i] = *reinterpret_cast<const float4 *>(x_in + c * 8);
-            b[i] = *reinterpret_cast<const float4 *>(x_in + c * 8 + 4);
-            wa[i] = *reinterpret_cast<const float4 *>(nw + c * 8);
-            wb[i] = *reinterpret_cast<const float4 *>(nw + c * 8 + 4);
-            if (ada) {
-                da[i] = *reinterpret_cast<const float4 *>(ada + c * 8);
-                db[i] = *reinterpret_cast<const float4 *>(ada + c * 8 + 4);
-            }
+    for (int i = 0; i < NP; i++) {
+        const int hc = t + i * TP_THREADS;
+        x[i] = *reinterpret_cast<const float4 *>(x_in + hc * 4);
+        wn[i] = *reinterpret_cast<const float4 *>(nw + hc * 4);
+        if (ada) wd[i] = *reinterpret_cast<const float4 *>(ada + hc * 4);
+    }
+    if (REDUCE) {
+        const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
+        for (int p0 = 0; p0 < td.world; p0 += 4) {
+            uint4 v[NP][4][2];
+            #pragma unroll
+            for (int i = 0; i < NP; i++)
+                #pragma unroll
+                for (int pp = 0; pp < 4; pp++)
+                    if (p0 + pp < td.world) {
+                        const uint2 *src = td.self->part[a_idx & 1][p0 + pp] + (t + i * TP_THREADS) * 4;
+                        v[i][pp][0] = ld_ll2(src); v[i][pp][1] = ld_ll2(src + 2);
+                    }
+            #pragma unroll
+            for (int i = 0; i < NP; i++)
+                #pragma unroll
+                for (int pp = 0; pp < 4; pp++)
+                    if (p0 + pp < td.world) {
+                        tp_ll_settle4(td, td.self->part[a_idx & 1][p0 + pp] + (t + i * TP_THREADS) * 4, p0 + pp, seq, v[i][pp]);
+                        x[i].x += __uint_as_float(v[i][pp][0].x); x[i].y += __uint_as_float(v[i][pp][0].z);
+                        x[i].z += __uint_as_float(v[i][pp][1].x); x[i].w += __uint_as_float(v[i][pp][1].z);
+                    }
+        }
+        if (blockIdx.x == 0 && x_out) {
+            #pragma unroll
+            for (int i = 0; i < NP; i++) *reinterpret_cast<float4 *>(x_out + (t + i * TP_THREADS) * 4) = x[i];
         }
     }
     float ss = 0.f;
-    if (REDUCE) {
-        const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
-        #pragma unroll
-        for (int i = 0; i < NC; i++) {
-            const int c = t + i * TP_THREADS;
-            if (c < DEC_DIM / 8) {
-                for (int p0 = 0; p0 < td.world; p0 += 4) {
-                    uint4 v[4][4];
-                    #pragma unroll
-                    for (int pp = 0; pp < 4; pp++) {
-                        if (p0 + pp < td.world) {
-                            const uint2 *src = td.self->part[a_idx & 1][p0 + pp] + c * 8;
-                            #pragma unroll
-                            for (int k = 0; k < 4; k++) v[pp][k] = ld_ll2(src + 2 * k);
-                        }
-                    }
-                    #pragma unroll
-                    for (int pp = 0; pp < 4; pp++) {
-                        if (p0 + pp < td.world) {
-                            tp_ll_settle8(td, td.self->part[a_idx & 1][p0 + pp] + c * 8, p0 + pp, seq, v[pp]);
-                            a[i].x += __uint_as_float(v[pp][0].x); a[i].y += __uint_as_float(v[pp][0].z);
-                            a[i].z += __uint_as_float(v[pp][1].x); a[i].w += __uint_as_float(v[pp][1].z);
-                            b[i].x += __uint_as_float(v[pp][2].x); b[i].y += __uint_as_float(v[pp][2].z);
-                            b[i].z += __uint_as_float(v[pp][3].x); b[i].w += __uint_as_float(v[pp][3].z);
-                        }
-                    }
-                }
-                if (blockIdx.x == 0 && x_out) {
-                    *reinterpret_cast<float4 *>(x_out + c * 8) = a[i];
-                    *reinterpret_cast<float4 *>(x_out + c * 8 + 4) = b[i];
-                }
-            }
-        }
-    }
     #pragma unroll
-    for (int i = 0; i < NC; i++)
-        if (t + i * TP_THREADS < DEC_DIM / 8) ss += f4sq(a[i]) + f4sq(b[i]);
+    for (int i = 0; i < NP; i++) ss += f4sq(x[i]);
     ss = warp_sum(ss);
     if ((t & 31) == 0) red[t >> 5] = ss;
     __syncthreads();
@@ -106,18 +103,12 @@ __device__ __forceinline__ void tp_load_x_norm(float4 *xA, float4 *xB, float *re
     for (int w = 0; w < TP_WARPS; w++) tot += red[w];
     const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
     #pragma unroll
-    for (int i = 0; i < NC; i++) {
-        const int c = t + i * TP_THREADS;
-        if (c < DEC_DIM / 8) {
-            float4 u = a[i], v = b[i];
-            u.x = u.x * rinv * wa[i].x; u.y = u.y * rinv * wa[i].y; u.z = u.z * rinv * wa[i].z; u.w = u.w * rinv * wa[i].w;
-            v.x = v.x * rinv * wb[i].x; v.y = v.y * rinv * wb[i].y; v.z = v.z * rinv * wb[i].z; v.w = v.w * rinv * wb[i].w;
-            if (ada) {
-                u.x *= (1.0f + da[i].x); u.y *= (1.0f + da[i].y); u.z *= (1.0f + da[i].z); u.w *= (1.0f + da[i].w);
-                v.x *= (1.0f + db[i].x); v.y *= (1.0f + db[i].y); v.z *= (1.0f + db[i].z); v.w *= (1.0f + db[i].w);
-            }
-            xA[c] = u; xB[c] = v;
-        }
+    for (int i = 0; i < NP; i++) {
+        const int hc = t + i * TP_THREADS;
+        float4 u = x[i];
+        u.x = u.x * rinv * wn[i].x; u.y = u.y * rinv * wn[i].y; u.z = u.z * rinv * wn[i].z; u.w = u.w * rinv * wn[i].w;
+        if (ada) { u.x *= (1.0f + wd[i].x); u.y *= (1.0f + wd[i].y); u.z *= (1.0f + wd[i].z); u.w *= (1.0f + wd[i].w); }
+        if (hc & 1) xB[hc >> 1] = u; else xA[hc >> 1] = u;
     }
     __syncthreads();
 }
@@ -459,14 +450,12 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
     tp->n_local = 1;
     if (tp_rank_init(tp, tp->r[0], rank)) { vox_cuda_tp_free(tp); return nullptr; }
     tp->connected = (world == 1);
-    {   // Two step engines with the same arithmetic and exchange protocol: one persistent cooperative kernel per rank
-        // (dec_tp_mega.cu) or the kernel-per-op CUDA graph above.  Measured (profiles/r01_j_tp_decode.md): the persistent
-        // kernel wins at 2 GPUs (1.08 vs 1.12 ms per token), the PDL-chained graph at 4 (0.82 vs 0.87): with a quarter of
-        // the bytes per phase a grid barrier costs more than a kernel boundary whose successor already runs beside it.
-        // VOX_CUDA_TP_MEGA=1 / 0 forces one or the other.
+    {   // Two step engines with the same arithmetic and exchange protocol: the kernel-per-op CUDA graph above (default)
+        // and one persistent cooperative kernel per rank (dec_tp_mega.cu, VOX_CUDA_TP_MEGA=1).  Measured
+        // (profiles/r01_j_tp_decode.md): 1.067 vs 1.077 ms per token at 2 GPUs, 0.810 vs 0.868 at 4 - a grid barrier
+        // costs more than a PDL kernel boundary whose successor already runs beside its predecessor.
         const char *env = getenv("VOX_CUDA_TP_MEGA");
-        const bool want = env ? atoi(env) != 0 : world <= 2;
-        if (want) tp->mega = tp_mega_create(m, world);
+        if (env && atoi(env) != 0) tp->mega = tp_mega_create(m, world);
     }
     return tp;
 }
