@@ -54,3 +54,35 @@ def test_cli_batch_and_stream_match_ctypes(full_env, tmp_path):
     assert run_cli(["-d", e.mdir, "-i", wav, "-I", "0.5", "--stream", "0.3"]) == want
     pcm = (x * 32768.0).astype("<i2").tobytes()
     assert run_cli(["-d", e.mdir, "--stdin", "-I", "2.0"], stdin=pcm) == want
+
+
+def test_cli_ingests_stereo_44k_like_the_reference(full_env, tmp_path):
+    """A 44.1 kHz stereo WAV through the C CLI (RIFF parsing on the host, downmix + resampling on the device,
+    csrc/pcm.cu) gives the ids of the samples the reference's own vox_parse_wav_buffer produces from the file."""
+    import refharness as rh
+    import test_gpu_parity as tp
+    import vox_oracle_path  # noqa: F401
+    import vox_oracle as vo
+    e = full_env
+    x16 = tp.synth_audio(2 * 16000 + 500, seed=14)
+    n44 = int(len(x16) * 44100 / 16000)
+    mono44 = np.interp(np.arange(n44) * (len(x16) - 1) / (n44 - 1), np.arange(len(x16)), x16)
+    a = np.clip(np.stack([0.9 * mono44, 0.6 * mono44], axis=1) * 32767, -32768, 32767).astype(np.int16)
+    image = rh.make_wav(a, 2, 44100)
+    wav = str(tmp_path / "stereo44.wav")
+    with open(wav, "wb") as f:
+        f.write(image)
+    samples = rh.ref_parse_wav(image, strict=True)
+    buf, nf = vo.stream_buffer(samples)
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        toks = np.empty(nf // 8 + 8, np.int32)
+        n = e.L.vox_cuda_transcribe(st, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n > 0, e.vc.last_error()
+        want = toks[:n].tolist()
+        if 2 in want:
+            want = want[:want.index(2)]
+    finally:
+        e.L.vox_cuda_state_free(st)
+    assert run_cli(["-d", e.mdir, "-i", wav]) == want

@@ -493,7 +493,9 @@ void vox_b200_stream_free(vox_b200_stream *s) {
     free(s);
 }
 
-/* ---- WAV (16-bit PCM, mono, 16 kHz only; anything else is the front end's business) -------- */
+/* ---- WAV: RIFF parsing on the host (vox_parse_wav_buffer, voxtral_audio.c:49-92), the sample arithmetic on the
+ * device (vox_cuda_pcm_from_s16: channel mean, / 32768, linear-interpolation resampling to 16 kHz,
+ * voxtral_audio.c:94-137).  16-bit PCM, any channel count and rate, like the reference. -------- */
 float *vox_b200_load_wav(const char *path, int *n_samples) {
     FILE *f = fopen(path, "rb");
     if (!f) { fprintf(stderr, "vox_b200_load_wav: cannot open %s\n", path); return NULL; }
@@ -504,6 +506,7 @@ float *vox_b200_load_wav(const char *path, int *n_samples) {
     if (!d || fread(d, 1, (size_t)size, f) != (size_t)size) { fclose(f); free(d); return NULL; }
     fclose(f);
     float *out = NULL;
+    int16_t *frames = NULL;
     if (size < 44 || memcmp(d, "RIFF", 4) || memcmp(d + 8, "WAVE", 4)) goto bad;
     {
         int fmt = 0, ch = 0, bits = 0;
@@ -518,16 +521,21 @@ float *vox_b200_load_wav(const char *path, int *n_samples) {
                 memcpy(&rate, d + p + 12, 4);
                 bits = d[p + 22] | (d[p + 23] << 8);
             } else if (!memcmp(d + p, "data", 4)) {
-                if (fmt != 1 || ch != 1 || bits != 16 || rate != 16000) goto bad;
-                if ((long)len > size - p - 8) len = (uint32_t)(size - p - 8);
-                const int n = (int)(len / 2);
-                out = (float *)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1));
-                if (!out) goto bad;
-                for (int i = 0; i < n; i++) {
-                    const int16_t v = (int16_t)(d[p + 8 + 2 * i] | (d[p + 9 + 2 * i] << 8));
-                    out[i] = (float)v / 32768.0f;
+                if (fmt != 1 || ch < 1 || bits != 16 || rate == 0) goto bad;
+                if ((long)len > size - p - 8 || len == 0) len = (uint32_t)(size - p - 8);   /* piped ffmpeg writes -1 */
+                const int n_frames = (int)(len / (2u * (uint32_t)ch));
+                const int n_out = vox_cuda_pcm_resampled_len(n_frames, (int)rate);
+                if (n_frames <= 0 || n_out < 0) goto bad;
+                frames = (int16_t *)malloc((size_t)n_frames * (size_t)ch * 2);
+                out = (float *)malloc(sizeof(float) * (size_t)(n_out > 0 ? n_out : 1));
+                if (!frames || !out) goto bad;
+                memcpy(frames, d + p + 8, (size_t)n_frames * (size_t)ch * 2);                /* little-endian host */
+                if (vox_cuda_pcm_from_s16(frames, n_frames, ch, (int)rate, out, n_out) != n_out) {
+                    fprintf(stderr, "vox_b200_load_wav: %s\n", vox_cuda_last_error());
+                    goto bad;
                 }
-                *n_samples = n;
+                *n_samples = n_out;
+                free(frames);
                 free(d);
                 return out;
             }
@@ -535,8 +543,9 @@ float *vox_b200_load_wav(const char *path, int *n_samples) {
         }
     }
 bad:
-    fprintf(stderr, "vox_b200_load_wav: %s is not 16-bit mono 16 kHz PCM\n", path);
+    fprintf(stderr, "vox_b200_load_wav: %s is not a 16-bit PCM WAV file\n", path);
     free(d);
     free(out);
+    free(frames);
     return NULL;
 }
