@@ -127,6 +127,8 @@ __device__ __forceinline__ void tp_attn_task(const TpDev &td, int lk, int split,
     const int ng = (n_keys + 7) >> 3;
     int gps = (ng + ns - 1) / ns;
     gps = (gps + TP_WARPS - 1) / TP_WARPS * TP_WARPS;    // whole rounds of the 8 warps
+    const int n_active = (ng + gps - 1) / gps;           // splits that own keys: 1 at a short context, ns at a full window
+    if (split >= n_active) return;                       // whole CTA (uniform): idle splits neither write nor arrive
     const int g0 = split * gps, g1 = min(ng, g0 + gps);
     if (tid < 4 * DEC_HD / 4)
         reinterpret_cast<float4 *>(&qs[0][0])[tid] = __ldcg(reinterpret_cast<const float4 *>(q + (size_t)kvh * 4 * DEC_HD) + tid);
@@ -222,7 +224,7 @@ __device__ __forceinline__ void tp_attn_task(const TpDev &td, int lk, int split,
     __syncthreads();
     if (tid == 0) {
         const unsigned old = atomicAdd(&td.done[1 + lk], 1u);
-        *s_last = (old == (unsigned)ns - 1u);
+        *s_last = (old == (unsigned)n_active - 1u);
         if (*s_last) td.done[1 + lk] = 0;
     }
     __syncthreads();
@@ -230,9 +232,11 @@ __device__ __forceinline__ void tp_attn_task(const TpDev &td, int lk, int split,
         __threadfence();
         const float *base = part + ((size_t)kvh * TP_ATT_SPLITS * 4 + h) * TP_ATT_PART;
         float M = -INFINITY;
-        for (int s = 0; s < ns; s++) M = fmaxf(M, __ldcg(base + (size_t)s * 4 * TP_ATT_PART + DEC_HD));
+        #pragma unroll 4
+        for (int s = 0; s < n_active; s++) M = fmaxf(M, __ldcg(base + (size_t)s * 4 * TP_ATT_PART + DEC_HD));
         float n0 = 0.f, n1 = 0.f, den = 0.f;
-        for (int s = 0; s < ns; s++) {
+        #pragma unroll 4
+        for (int s = 0; s < n_active; s++) {
             const float *o = base + (size_t)s * 4 * TP_ATT_PART;
             const float ms = __ldcg(o + DEC_HD);
             if (ms == -INFINITY) continue;
