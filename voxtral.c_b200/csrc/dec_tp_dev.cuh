@@ -13,10 +13,11 @@ constexpr int TP_ATT_PART = DEC_HD + 4;                    // floats per (split,
 // One rank's exchange window.  Same layout on every rank; peers write into it, the owner only reads.
 // Every element is an 8-byte word {payload bits, sequence number of the exchange that wrote it}: 8-byte
 // aligned stores are single transactions, locally and over NVLink, so a reader that sees the sequence
-// number sees the payload.  Slots alternate with the sequence parity: a writer of exchange s can only run
-// ahead of a reader by one exchange (it needs every rank's s-1 to get there), so s-2's slot is free.
+// number sees the payload.  Two slots alternate (part: parity of the exchange's index in the step - 52 per step, so
+// consecutive exchanges always differ; amax: parity of the sequence number): a writer of exchange s can only run
+// ahead of a reader by one exchange (it needs every rank's s-1 to get there), so the slot s-2 used is free.
 struct TpComm {
-    uint2 part[2][TP_MAX][DEC_DIM];   // [sequence parity][source rank][row]  partial sums of wo / w2
+    uint2 part[2][TP_MAX][DEC_DIM];   // [exchange index & 1][source rank][row]  partial sums of wo / w2
     uint2 amax[2][TP_MAX][2];         // [sequence parity][source rank] {max logit bits, seq}, {index, seq}
 };
 
