@@ -110,6 +110,14 @@ void vox_cuda_state_reset_decoder(vox_cuda_state_t *s);
 /* enc_kv_cache_len = enc_kv_pos_offset = 0, conv tails / residuals cleared,
  * adapter buffer emptied (voxtral.c:797-824,1279-1280). */
 void vox_cuda_state_reset_encoder(vox_cuda_state_t *s);
+/* Encoder twin of the two calls below: logical position of the next encoder row
+ * (enc_kv_pos_offset + enc_kv_cache_len, voxtral.h:218-224).  A host that resets or
+ * compacts its own integers (voxtral.c:819-820, voxtral_encoder.c:431-449) passes the
+ * sum on before the next vox_cuda_encoder_step. */
+int  vox_cuda_encoder_position(const vox_cuda_state_t *s);
+int  vox_cuda_encoder_set_position(vox_cuda_state_t *s, int logical_pos);
+/* conv_stem_initialized = 0 (voxtral.c:807-817): tails and parity residual only. */
+void vox_cuda_state_reset_stem(vox_cuda_state_t *s);
 /* Logical decoder position = kv_pos_offset + kv_cache_len of the reference. */
 int  vox_cuda_decoder_position(const vox_cuda_state_t *s);
 /* Override the decoder position bookkeeping (test hook for the 8192-window

@@ -52,7 +52,11 @@ gcc $CFLAGS -c "$HERE/ref_shim.c" -o "$OUT/ref_shim.o"
 gcc $CFLAGS -c "$HERE/sgemm_fallback.c" -o "$OUT/sgemm_fallback.o"
 gcc $CFLAGS -c "$REF/main.c" -o "$OUT/main.o"
 
-gcc -shared -fopenmp -o "$OUT/libvoxref.so" $OBJS "$OUT/ref_shim.o" "$OUT/sgemm_fallback.o" \
+# --wrap: calls the reference's stream path makes into vox_decoder_forward /
+# vox_encoder_forward_incremental pass through the recorders of ref_shim.c (ids, margins,
+# rows per encoder call); the functions themselves are the reference's, unmodified.
+WRAP="-Wl,--wrap=vox_decoder_forward -Wl,--wrap=vox_encoder_forward_incremental"
+gcc -shared -fopenmp $WRAP -o "$OUT/libvoxref.so" $OBJS "$OUT/ref_shim.o" "$OUT/sgemm_fallback.o" \
     $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
 gcc -fopenmp -o "$OUT/voxtral_ref" "$OUT/main.o" $OBJS "$OUT/sgemm_fallback.o" \
     $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
@@ -70,7 +74,7 @@ for s in $SRCS; do
 done
 gcc $SCFLAGS -c "$HERE/ref_shim.c" -o "$OUT/strict_ref_shim.o"
 gcc $SCFLAGS -c "$HERE/sgemm_fallback.c" -o "$OUT/strict_sgemm_fallback.o"
-gcc -shared -fopenmp -o "$OUT/libvoxref_strict.so" $SOBJS "$OUT/strict_ref_shim.o" "$OUT/strict_sgemm_fallback.o" \
+gcc -shared -fopenmp $WRAP -o "$OUT/libvoxref_strict.so" $SOBJS "$OUT/strict_ref_shim.o" "$OUT/strict_sgemm_fallback.o" \
     $BLAS_LINK -lm -Wl,-rpath,'$ORIGIN'
 rm -f "$OUT"/*.o
 echo "build_ref: built $OUT/libvoxref.so and $OUT/voxtral_ref"

@@ -123,3 +123,50 @@ float *refshim_stream_mel(const float *samples, int n, int delay_tokens,
 }
 
 void refshim_free(void *p) { free(p); }
+
+/* ---- call log of the reference's OWN stream path ------------------------
+ * libvoxref.so is linked with -Wl,--wrap=vox_decoder_forward
+ * -Wl,--wrap=vox_encoder_forward_incremental (oracle/build_ref.sh), so the calls
+ * that stream_run_decoder / stream_run_encoder (voxtral.c:1012-1113, 826-951) make
+ * are routed through the two recorders below.  They call the real function and
+ * keep what it returned: the greedy token id with the top-2 logit margin, and the
+ * row count of every encoder call.  The arithmetic is untouched; the harness
+ * calling vox_decoder_forward directly still reaches the real symbol. */
+int __real_vox_decoder_forward(vox_ctx_t *ctx, const float *input_embeds, float *logits);
+float *__real_vox_encoder_forward_incremental(vox_ctx_t *ctx, const float *x_new, int new_len, int *out_len);
+
+#define REFSHIM_LOG_MAX (1 << 16)
+static int g_log_tok[REFSHIM_LOG_MAX];
+static float g_log_margin[REFSHIM_LOG_MAX];
+static int g_log_n;
+static int g_enc_rows[REFSHIM_LOG_MAX];
+static int g_enc_n;
+
+int __wrap_vox_decoder_forward(vox_ctx_t *ctx, const float *input_embeds, float *logits) {
+    int tok = __real_vox_decoder_forward(ctx, input_embeds, logits);
+    if (g_log_n < REFSHIM_LOG_MAX) {
+        float m = -1.0f;
+        if (logits && tok >= 0) {
+            float second = -3.0e38f;
+            for (int i = 0; i < VOX_VOCAB_SIZE; i++)
+                if (i != tok && logits[i] > second) second = logits[i];
+            m = logits[tok] - second;
+        }
+        g_log_tok[g_log_n] = tok;
+        g_log_margin[g_log_n] = m;
+        g_log_n++;
+    }
+    return tok;
+}
+
+float *__wrap_vox_encoder_forward_incremental(vox_ctx_t *ctx, const float *x_new, int new_len, int *out_len) {
+    if (g_enc_n < REFSHIM_LOG_MAX) g_enc_rows[g_enc_n++] = new_len;
+    return __real_vox_encoder_forward_incremental(ctx, x_new, new_len, out_len);
+}
+
+void refshim_log_reset(void) { g_log_n = 0; g_enc_n = 0; }
+int refshim_log_count(void) { return g_log_n; }
+const int *refshim_log_tokens(void) { return g_log_tok; }
+const float *refshim_log_margins(void) { return g_log_margin; }
+int refshim_enc_call_count(void) { return g_enc_n; }
+const int *refshim_enc_call_rows(void) { return g_enc_rows; }

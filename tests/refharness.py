@@ -32,10 +32,10 @@ def ensure_gen_model():
     return exe
 
 
-def model_dir(seed=1234, enc_layers=32, dec_layers=26, emb_sigma=0.05, extra=()):
+def model_dir(seed=1234, enc_layers=32, dec_layers=26, emb_sigma=0.02, extra=()):
     """Generate (once per box) the deterministic random-init checkpoint."""
     base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else "/tmp"
-    tag = f"voxm_s{seed}_e{enc_layers}_d{dec_layers}_g{emb_sigma}" + "".join(extra).replace("-", "").replace(" ", "")
+    tag = f"voxm2_s{seed}_e{enc_layers}_d{dec_layers}_g{emb_sigma}" + "".join(extra).replace("-", "").replace(" ", "")
     d = os.path.join(base, tag)
     if not os.path.exists(os.path.join(d, "tekken.json")):
         os.makedirs(d, exist_ok=True)

@@ -1,0 +1,266 @@
+"""Greedy token ids of BASELINE configs 1-4 against fixtures produced by the REFERENCE'S OWN stream API
+(tests/golden/ids_*.npz, written by tests/golden/make_golden_ids.py from oracle/_ref/libvoxref.so:
+vox_stream_init + vox_stream_feed + vox_stream_finish, every vox_decoder_forward call recorded).
+
+  config 1  samples/jfk.wav, 149 steps                      -> vox_cuda_transcribe, the C host, the drop-in
+  config 2  the 60 s bench clip (seed 1), 761 steps          -> vox_cuda_transcribe, stream group slot, TP lock step
+  config 3  the same clip fed in -I 0.5 / -I 2.0 pieces      -> the C host in --stream mode, the drop-in library
+  config 4  first 62 s of the 30-minute clip, fed w/o finish  -> head of the C host's streamed run
+
+Bit-exact ids are asserted.  The fixtures carry the reference's top-2 logit margin of every step; the
+smallest one is printed so a reader sees how far the comparison is from a coin flip."""
+import ctypes as C
+import os
+import re
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+PKG = os.path.join(ROOT, "voxtral.c_b200")
+sys.path.insert(0, ROOT)
+
+
+def gold(job):
+    path = os.path.join(GOLD, f"ids_{job}.npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated")
+    d = np.load(path)
+    print(f"{job}: {len(d['ids'])} reference steps, {len(set(d['ids'].tolist()))} distinct ids, "
+          f"min top-2 margin {float(d['margins'].min()):.2e}, encoder calls {d['enc_call_rows'].tolist()[:4]}...")
+    return d
+
+
+def job_audio(job, d):
+    import bench
+    if job == "jfk":
+        return d["pcm_s16"].astype(np.float32) / 32768.0
+    if job.startswith("clip60"):
+        return bench.synth_clip(60.0, 1)
+    if job == "long_head":
+        return bench.synth_clip(1800.0, 2)[:62 * 16000]
+    raise KeyError(job)
+
+
+def transcribe(e, x):
+    import bench
+    buf, nf = bench.frame_buffer(x)
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        toks = np.empty(nf // 8 + 8, np.int32)
+        n = e.L.vox_cuda_transcribe(st, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n > 0, e.vc.last_error()
+        return toks[:n].copy()
+    finally:
+        e.L.vox_cuda_state_free(st)
+
+
+def first_diff(a, b):
+    n = min(len(a), len(b))
+    nz = np.nonzero(np.asarray(a[:n]) != np.asarray(b[:n]))[0]
+    return int(nz[0]) if len(nz) else (n if len(a) != len(b) else -1)
+
+
+def assert_ids(got, d, what):
+    want = d["ids"]
+    k = first_diff(got, want)
+    assert k < 0, (f"{what}: first difference at step {k} of {len(want)} (reference margin there "
+                   f"{float(d['margins'][min(k, len(want) - 1)]):.3e}): got {got[k:k + 4].tolist() if k < len(got) else '[]'} "
+                   f"want {want[k:k + 4].tolist() if k < len(want) else '[]'}")
+
+
+def test_config1_jfk_ids(full_env):
+    d = gold("jfk")
+    assert_ids(transcribe(full_env, job_audio("jfk", d)), d, "vox_cuda_transcribe(jfk.wav)")
+
+
+def test_config2_clip60_ids(full_env):
+    d = gold("clip60")
+    assert len(d["ids"]) == 761
+    assert_ids(transcribe(full_env, job_audio("clip60", d)), d, "vox_cuda_transcribe(60 s bench clip)")
+
+
+def test_config2_clip60_ids_stream_group_and_tp(full_env):
+    """the same 761 ids from a stream-group slot (lock-step engine, slot 1 of 3) and from the tensor-parallel
+    engine run in lock step on one GPU (G = 2)"""
+    import bench
+    e = full_env
+    d = gold("clip60")
+    x = job_audio("clip60", d)
+    buf, nf = bench.frame_buffer(x)
+    T = nf // 8
+    g = e.L.vox_cuda_group_create(e.model, 3, T + 1)
+    assert g, e.vc.last_error()
+    try:
+        short, nfs = bench.frame_buffer(bench.synth_clip(3.0, 7))
+        assert e.L.vox_cuda_group_encode(g, 0, e.vc.fptr(short), len(short), nfs) > 0, e.vc.last_error()
+        assert e.L.vox_cuda_group_encode(g, 1, e.vc.fptr(buf), len(buf), nf) == T, e.vc.last_error()
+        toks = np.empty((3, T), np.int32)
+        counts = np.zeros(3, np.int32)
+        assert e.L.vox_cuda_group_decode(g, 39, e.vc.iptr(toks), T, e.vc.iptr(counts), None) > 0, e.vc.last_error()
+        assert_ids(toks[1, :counts[1]], d, "stream group slot 1")
+    finally:
+        e.L.vox_cuda_group_free(g)
+    tp = e.L.vox_cuda_tp_create_local(e.model, 2)
+    assert tp, e.vc.last_error()
+    try:
+        toks = np.empty(T + 8, np.int32)
+        n = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n > 0, e.vc.last_error()
+        assert_ids(toks[:n], d, "tensor-parallel engine, 2 ranks in lock step")
+    finally:
+        e.L.vox_cuda_tp_free(tp)
+
+
+# ---- the C host (voxtral_b200) in streaming mode: config 3 and config 4 (i) -------------------------------
+def write_wav(path, x):
+    pcm = np.round(np.asarray(x) * 32768.0).astype("<i2").tobytes()
+    with open(path, "wb") as f:
+        f.write(b"RIFF" + struct.pack("<I", 36 + len(pcm)) + b"WAVEfmt " +
+                struct.pack("<IHHIIHH", 16, 1, 1, 16000, 32000, 2, 16) + b"data" + struct.pack("<I", len(pcm)) + pcm)
+
+
+def run_host(args, stdin=None):
+    exe = os.path.join(PKG, "voxtral_b200")
+    assert os.path.exists(exe), "run make -C voxtral.c_b200 cuda"
+    p = subprocess.run([exe] + args, input=stdin, capture_output=True, timeout=900)
+    assert p.returncode == 0, p.stderr.decode()[-2000:]
+    return [int(t) for t in p.stdout.decode().split()], p.stderr.decode()
+
+
+@pytest.mark.parametrize("job,interval,piece", [("clip60_i05", "0.5", "0.5"), ("clip60_i20", "2.0", "1.0")])
+def test_config3_streamed_ids_c_host(full_env, tmp_path, job, interval, piece):
+    """voxtral_b200 --stream: the clip fed in pieces with the processing interval of the fixture; ids and the
+    row count of every encoder call (first chunk >= 312 mel, then the interval rule, voxtral.c:826-951) must
+    match what the reference's vox_stream_feed did"""
+    d = gold(job)
+    x = job_audio(job, d)
+    wav = str(tmp_path / "clip.wav")
+    write_wav(wav, x)
+    ids, err = run_host(["-d", full_env.mdir, "-i", wav, "-I", interval, "--stream", piece, "-v"])
+    want = d["ids"].tolist()
+    if 2 in want:
+        want = want[:want.index(2)]
+    k = first_diff(np.array(ids), np.array(want))
+    assert k < 0, (job, k, ids[k:k + 4], want[k:k + 4], float(d["margins"][k]))
+    m = re.search(r"encoder calls: (\d+) rows:([ 0-9]*)", err)
+    assert m, err[-600:]
+    rows = [int(v) for v in m.group(2).split()]
+    assert int(m.group(1)) == len(d["enc_call_rows"]) and rows == d["enc_call_rows"].tolist()[:64], (rows, d["enc_call_rows"].tolist())
+
+
+def test_config4_long_head_ids_c_host(full_env, tmp_path):
+    """config 4 (i): the first 62 s of the 30-minute clip streamed without finish on the reference; the C host
+    streams the same samples (and finishes - later audio cannot change earlier ids, the path is causal), so its
+    first len(fixture) ids must equal the fixture"""
+    d = gold("long_head")
+    x = job_audio("long_head", d)
+    wav = str(tmp_path / "head.wav")
+    write_wav(wav, x)
+    ids, _ = run_host(["-d", full_env.mdir, "-i", wav])
+    want = d["ids"].tolist()
+    assert len(ids) >= len(want)
+    k = first_diff(np.array(ids[:len(want)]), np.array(want))
+    assert k < 0, (k, ids[k:k + 4], want[k:k + 4], float(d["margins"][k]))
+
+
+# ---- the drop-in: the reference's own host sources built with -DUSE_CUDA ----------------------------------
+DECODER_RE = re.compile(r"Decoder:\s+\d+\s+text tokens\s+\((\d+)\s+steps\)\s+in\s+(\d+)\s+ms\s+"
+                        r"\(prefill\s+(\d+)\s+ms\s+\+\s+([0-9.]+)\s+ms/step\)")            # /root/reference/benchmark.py:26-29
+ENCODER_RE = re.compile(r"Encoder:\s+\d+\s+mel\s+->\s+\d+\s+tokens\s+\((\d+)\s+ms\)")      # benchmark.py:30
+
+
+def text_of(ids):
+    ids = list(ids)
+    if 2 in ids:
+        ids = ids[:ids.index(2)]
+    return "".join(f" t{t}" for t in ids if t >= 1000)
+
+
+def test_dropin_cli_jfk_text_and_timing_lines(full_env, tmp_path):
+    """voxtral_cuda = /root/reference/main.c + voxtral*.c compiled with -DUSE_CUDA (integration/use_cuda.patch)
+    and linked to libvoxcuda.so.  Its stdout must be the text of the reference's CPU run, and its stderr must
+    carry the reference's own Encoder:/Decoder: lines in the format benchmark.py parses."""
+    exe = os.path.join(PKG, "voxtral_cuda")
+    if not os.path.exists(exe):
+        pytest.skip("voxtral_cuda not built (make -C voxtral.c_b200 dropin needs /root/reference)")
+    d = gold("jfk")
+    wav = str(tmp_path / "jfk.wav")
+    write_wav(wav, job_audio("jfk", d))
+    p = subprocess.run([exe, "-d", full_env.mdir, "-i", wav], capture_output=True, timeout=900)
+    assert p.returncode == 0, p.stderr.decode()[-2000:]
+    err = p.stderr.decode()
+    print(err[-800:])
+    assert p.stdout.decode().strip() == text_of(d["ids"]).strip()
+    md, me = DECODER_RE.search(err), ENCODER_RE.search(err)
+    assert md and me, err[-800:]
+    assert int(md.group(1)) == len(d["ids"])
+    # --alt through the reference's own stream_fill_alts on logits copied back from the device
+    p = subprocess.run([exe, "-d", full_env.mdir, "-i", wav, "--alt", "0.2", "--silent"], capture_output=True, timeout=900)
+    assert p.returncode == 0, p.stderr.decode()[-2000:]
+    assert " t%d" % int(d["ids"][0]) in p.stdout.decode()
+
+
+@pytest.mark.parametrize("job,interval,piece", [("clip60_i05", 0.5, 8000), ("jfk", 0.0, 0)])
+def test_dropin_library_stream_api(full_env, job, interval, piece):
+    """libvoxtral_cuda.so: vox_load / vox_stream_init / vox_set_processing_interval / vox_stream_feed /
+    vox_stream_finish / vox_stream_get_alt of the reference's voxtral.h with the B200 backend behind them, fed exactly
+    as the fixture's reference run was fed; text ids (and alternatives for jfk) must match"""
+    so = os.path.join(PKG, "libvoxtral_cuda.so")
+    if not os.path.exists(so):
+        pytest.skip("libvoxtral_cuda.so not built")
+    d = gold(job)
+    x = np.ascontiguousarray(job_audio(job, d), np.float32)
+    code = f"""
+import ctypes as C, numpy as np, re, sys, json
+L = C.CDLL({so!r})
+f32p = C.POINTER(C.c_float)
+L.vox_load.restype = C.c_void_p; L.vox_load.argtypes = [C.c_char_p]
+L.vox_stream_init.restype = C.c_void_p; L.vox_stream_init.argtypes = [C.c_void_p]
+L.vox_stream_feed.argtypes = [C.c_void_p, f32p, C.c_int]
+L.vox_stream_finish.argtypes = [C.c_void_p]; L.vox_stream_free.argtypes = [C.c_void_p]; L.vox_free.argtypes = [C.c_void_p]
+L.vox_stream_set_alt.argtypes = [C.c_void_p, C.c_int, C.c_float]
+L.vox_set_processing_interval.argtypes = [C.c_void_p, C.c_float]
+L.vox_stream_get_alt.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int, C.c_int]
+x = np.load(sys.argv[1])
+ctx = L.vox_load({full_env.mdir!r}.encode()); assert ctx
+s = L.vox_stream_init(ctx); assert s
+n_alt = {int(d['alt_n'])}
+if {float(d['alt_cutoff'])} > 0: L.vox_stream_set_alt(s, n_alt, C.c_float({float(d['alt_cutoff'])}))
+piece = {piece} or len(x)
+if {interval} > 0: L.vox_set_processing_interval(s, C.c_float({interval}))
+buf = (C.c_char_p * (64 * n_alt))()
+rows = []
+def drain():
+    while True:
+        n = L.vox_stream_get_alt(s, buf, 64, n_alt)
+        if n <= 0: break
+        for i in range(n):
+            rows.append([int(re.fullmatch(rb" t(\\d+)", buf[i*n_alt+a]).group(1)) if buf[i*n_alt+a] else -1 for a in range(n_alt)])
+for off in range(0, len(x), piece):
+    c = np.ascontiguousarray(x[off:off+piece]); assert L.vox_stream_feed(s, c.ctypes.data_as(f32p), len(c)) == 0; drain()
+assert L.vox_stream_finish(s) == 0; drain()
+L.vox_stream_free(s); L.vox_free(ctx)
+print("ROWS" + json.dumps(rows))
+"""
+    import json
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        np.save(os.path.join(td, "x.npy"), x)
+        p = subprocess.run([sys.executable, "-c", code, os.path.join(td, "x.npy")], capture_output=True, timeout=900)
+    assert p.returncode == 0, p.stderr.decode()[-3000:]
+    rows = np.array(json.loads(p.stdout.decode().split("ROWS")[-1]), np.int32).reshape(-1, int(d["alt_n"]))
+    want = d["alts"]
+    k = first_diff(rows[:, 0], want[:, 0])
+    assert k < 0, (job, "text ids differ at", k, rows[k:k + 3].tolist(), want[k:k + 3].tolist())
+    if float(d["alt_cutoff"]) > 0:
+        bad = np.nonzero((rows != want).any(axis=1))[0]
+        assert len(bad) == 0, (job, "alternatives differ at text positions", bad[:8].tolist(),
+                               rows[bad[:3]].tolist(), want[bad[:3]].tolist())

@@ -386,6 +386,13 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
 }
 
 static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
+    // a block writes all its K/V rows into the ring before its attention runs: once a row reaches logical
+    // position 8191 the ring slot of the oldest key it needs has been overwritten by a later row of the block
+    if (s->h_params.pos + seq_len > DEC_WINDOW) {
+        vox_set_error("decoder_prefill: rows [%d,%d) reach the %d-position window; prefill only below it (step beyond)",
+                      s->h_params.pos, s->h_params.pos + seq_len, DEC_WINDOW);
+        return -1;
+    }
     if (dec_prefill_into(s, x_dev, seq_len, s->kv_k, s->kv_v, (size_t)DEC_WINDOW * DEC_KVDIM, DEC_WINDOW - 1,
                          &s->h_params.pos, &s->h_params.n_valid)) return -1;
     if (push_params(s)) return -1;

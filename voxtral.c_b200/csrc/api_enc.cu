@@ -69,7 +69,7 @@ void enc_state_free(vox_cuda_state *s) {
 extern "C" void vox_cuda_state_reset_encoder(vox_cuda_state_t *s) {
     if (!s) return;
     EncState *e = (EncState *)s->enc_priv;
-    e->pos = 0;
+    e->pos = 0; e->pos_min = 0;
     e->stem_init = 0; e->c0_resid = 0; e->enc_resid = 0;
     // zero histories: rows 0..1 of mel_in, rows 0..1 of c0 (voxtral.c:807-817)
     cudaMemsetAsync(e->mel_in, 0, 2 * VOX_CUDA_MEL_BINS * 4, s->stream);
@@ -174,7 +174,7 @@ int enc_layers_precise(vox_cuda_state *s, float *x, int M, float *out) {
         if (sgemm_bf16w(st, M, 3 * ENC_QKV, ENC_DIM, e->xn, ENC_DIM, L.wqkv, e->qkv, 3 * ENC_QKV, L.bqkv, EPI_BIAS)) return -1;
         if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
         if (rows_attention(st, ENC_HD, e->qkv, 3 * ENC_QKV, kc, vc, ENC_QKV, ENC_RING - 1, ENC_HEADS, 1, M,
-                           pos0, 0, ENC_WINDOW, e->att, ENC_QKV)) return -1;
+                           pos0, e->pos_min, ENC_WINDOW, e->att, ENC_QKV)) return -1;
         if (sgemm_bf16w(st, M, ENC_DIM, ENC_QKV, e->att, ENC_QKV, L.wo, x, ENC_DIM, L.bo, EPI_BIAS | EPI_RESIDUAL)) return -1;
         if (rows_rmsnorm(st, x, ENC_DIM, L.ffn_norm, nullptr, e->xn, ENC_DIM, M, ENC_DIM)) return -1;
         if (sgemm_bf16w(st, M, 2 * ENC_HIDDEN, ENC_DIM, e->xn, ENC_DIM, L.w13, e->gu, 2 * ENC_HIDDEN, nullptr, EPI_NONE)) return -1;
@@ -213,7 +213,7 @@ static int adapter_device(vox_cuda_state *s, const float *enc_rows, int k_tokens
 }
 
 __global__ void move_rows_kernel(float *dst, const float *src, size_t n) {
-    // forward copy; dst < src and the grid is launched with one CTA so order is safe
+    // forward copy of NON-overlapping ranges (the <= 3 leftover rows of encode_piece)
     for (size_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
 }
 
@@ -295,13 +295,51 @@ extern "C" int vox_cuda_adapter_discard_before(vox_cuda_state_t *s, int keep_fro
     const int consumed = keep_from - s->adapter_offset;
     if (consumed <= 0) return 0;
     const int remaining = s->adapter_count - keep_from;
+    // Slide the kept rows to the front.  Pieces of at most `consumed` rows never overlap their own
+    // destination, and stream order keeps piece i+1 (which reads what piece i did not write) behind
+    // piece i; when that would be many tiny copies the rows go through a scratch buffer instead.
     if (remaining > 0) {
-        move_rows_kernel<<<1, 1024, 0, s->stream>>>(s->adapter_buf, s->adapter_buf + (size_t)consumed * DEC_DIM,
-                                                    (size_t)remaining * DEC_DIM);
-        LAUNCHED();
+        const size_t row = (size_t)DEC_DIM * 4;
+        if ((remaining + consumed - 1) / consumed <= 8) {
+            for (int r = 0; r < remaining; r += consumed) {
+                const int n = remaining - r < consumed ? remaining - r : consumed;
+                CUDA_TRY(cudaMemcpyAsync(s->adapter_buf + (size_t)r * DEC_DIM, s->adapter_buf + (size_t)(r + consumed) * DEC_DIM,
+                                         n * row, cudaMemcpyDeviceToDevice, s->stream));
+            }
+        } else {
+            float *tmp = nullptr;
+            CUDA_TRY(cudaMalloc((void **)&tmp, remaining * row));
+            cudaError_t e1 = cudaMemcpyAsync(tmp, s->adapter_buf + (size_t)consumed * DEC_DIM, remaining * row,
+                                             cudaMemcpyDeviceToDevice, s->stream);
+            cudaError_t e2 = cudaMemcpyAsync(s->adapter_buf, tmp, remaining * row, cudaMemcpyDeviceToDevice, s->stream);
+            cudaStreamSynchronize(s->stream);
+            cudaFree(tmp);
+            if (e1 != cudaSuccess || e2 != cudaSuccess) { vox_set_error("adapter_discard_before: copy failed"); return -1; }
+        }
     }
     s->adapter_offset += consumed;
     return 0;
+}
+
+// Host-owned encoder position (voxtral.h:218-224: enc_kv_pos_offset + enc_kv_cache_len).  The ring is
+// addressed by logical position, so honouring a host reset or compaction is this one integer.
+extern "C" int vox_cuda_encoder_position(const vox_cuda_state_t *s) {
+    return s ? ((EncState *)s->enc_priv)->pos : -1;
+}
+extern "C" int vox_cuda_encoder_set_position(vox_cuda_state_t *s, int logical_pos) {
+    if (!s || logical_pos < 0) return -1;
+    EncState *e = (EncState *)s->enc_priv;
+    if (logical_pos != e->pos) { e->pos = logical_pos; e->pos_min = logical_pos; }   // a jump = an empty cache at that position
+    return 0;
+}
+// conv-stem tails only (conv_stem_initialized = 0, voxtral.c:807-817); the K/V ring position and the
+// adapter buffer are left alone
+extern "C" void vox_cuda_state_reset_stem(vox_cuda_state_t *s) {
+    if (!s) return;
+    EncState *e = (EncState *)s->enc_priv;
+    e->stem_init = 0; e->c0_resid = 0;
+    cudaMemsetAsync(e->mel_in, 0, 2 * VOX_CUDA_MEL_BINS * 4, s->stream);
+    cudaMemsetAsync(e->c0, 0, 2 * ENC_DIM * 4, s->stream);
 }
 
 // ---- host-pointer variants of the individual stages (reference call sites) -------

@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
     extern __shared__ __align__(16) uint16_t sm[];
     tcx::pdl_launch_dependents();
     tcx::pdl_wait();
-    if (pos_dev) pos0 = *pos_dev;                 // replayed CUDA graphs keep the position in device memory
+    if (pos_dev) { pos0 = pos_dev[0]; first_valid = pos_dev[1]; }   // replayed CUDA graphs keep {position, oldest valid key} in device memory
     uint16_t *Qh = sm, *Ql = sm + TILE, *Kh = sm + 2 * TILE, *Kl = sm + 3 * TILE, *Vh = sm + 4 * TILE, *Vl = sm + 5 * TILE;
     const int head = blockIdx.y, q0 = blockIdx.x * BQ;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -248,16 +248,16 @@ int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, cons
     }
     if (mode == 1) {
         if (pos_dev) { vox_set_error("enc_attention: device position needs the tensor-core path"); return -1; }
-        if (rows_attention(st, ENC_HD, qkv, 3 * ENC_QKV, kc, vc, ENC_QKV, ENC_RING - 1, ENC_HEADS, 1, M, pos0, 0,
+        if (rows_attention(st, ENC_HD, qkv, 3 * ENC_QKV, kc, vc, ENC_QKV, ENC_RING - 1, ENC_HEADS, 1, M, pos0, e->pos_min,
                            ENC_WINDOW, e->att, ENC_QKV)) return -1;
         return f32_to_bf16_rows(st, e->att, ENC_QKV, out_b, ldo, M, ENC_QKV, split);
     }
     dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
     if (split)
-        CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
                             ENC_RING - 1, out_b, ldo, 1, pos_dev));
     else
-        CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, 0, ENC_WINDOW,
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
                             ENC_RING - 1, out_b, ldo, 0, pos_dev));
     LAUNCHED();
     return 0;

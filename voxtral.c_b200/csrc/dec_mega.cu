@@ -31,14 +31,17 @@
 namespace mk {
 
 #ifndef MK_PROF
-#define MK_PROF 1                           // per-tile wait timing of the consumers (VOX_CUDA_MEGA_PROF readout)
+#define MK_PROF 0                           // 1: per-tile wait timing of the consumers (VOX_CUDA_MEGA_PROF readout); `make prof`
+#endif
+#ifndef MK_NSTAGE
+#define MK_NSTAGE 8
 #endif
 
 constexpr int CW = 8;                       // consumer warps
 constexpr int CT = CW * 32;                 // consumer threads
 constexpr int NT = CT + 64;                 // + producer warp + L2 prefetch warp
 constexpr int STAGE_BYTES = 24576;
-constexpr int NSTAGE = 8;
+constexpr int NSTAGE = MK_NSTAGE;
 constexpr int MAXTR = 4;                    // rows per tile at K = 3072
 constexpr int PART_LD = DEC_HD + 4;         // acc[128], m, l, pad (16-byte rows)
 constexpr int MAX_SPLITS = 32;

@@ -211,7 +211,7 @@ struct EncSmall {
     WtOp *ops[3];                       // per NB in {32, 64, 128}: [n_enc][4] prepared products (lazily)
     // The call is launch bound on the host (~290 launches); a chunk shape seen twice is captured into a CUDA
     // graph (position in device memory) and replayed.  Key = (M, x, out).
-    int *d_pos, *h_pos;                 // device position + pinned staging ring
+    int *d_pos, *h_pos;                 // device {position, oldest valid key} + pinned staging ring
     unsigned h_pos_i;
     struct { int M, seen; const float *x, *out; cudaGraphExec_t exec; } graphs[SM_GRAPHS];
 };
@@ -246,7 +246,7 @@ static EncSmall *small_get(vox_cuda_state *s, int NB) {
                 return nullptr;
             }
         }
-        if (cudaMalloc((void **)&q->d_pos, 4) != cudaSuccess || cudaMallocHost((void **)&q->h_pos, 64 * 4) != cudaSuccess) {
+        if (cudaMalloc((void **)&q->d_pos, 8) != cudaSuccess || cudaMallocHost((void **)&q->h_pos, 64 * 8) != cudaSuccess) {
             vox_set_error("enc_small: position buffers alloc failed");
             enc_small_free(q);
             return nullptr;
@@ -337,9 +337,9 @@ int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
         // first sighting of a shape runs eagerly (slot stays -1); the second one is captured
     }
     if (slot >= 0) {
-        int *hp = q->h_pos + (q->h_pos_i++ & 63);
-        *hp = pos0;
-        CUDA_TRY(cudaMemcpyAsync(q->d_pos, hp, 4, cudaMemcpyHostToDevice, st));
+        int *hp = q->h_pos + 2 * (q->h_pos_i++ & 63);
+        hp[0] = pos0; hp[1] = e->pos_min;
+        CUDA_TRY(cudaMemcpyAsync(q->d_pos, hp, 8, cudaMemcpyHostToDevice, st));
         if (!q->graphs[slot].exec) {
             cudaGraph_t graph = nullptr;
             CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));

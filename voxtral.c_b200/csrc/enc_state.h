@@ -13,6 +13,7 @@ struct EncState {
     float *kv_k, *kv_v;        // precise mode: [n_enc][ENC_RING][2048] fp32
     size_t kv_bytes;
     int pos;                   // logical position of the next row (enc_kv_pos_offset + enc_kv_cache_len)
+    int pos_min;               // logical position of the oldest valid key (a host-side position jump empties the cache)
     // incremental conv stem (voxtral.c:469-473)
     float *mel_in;             // [2 + ENC_MAXMEL][128]; rows 0-1 = last two mel frames
     float *c0;                 // [2 + ENC_MAXMEL][1280]; row 0 = last conv0 row fed to conv1,

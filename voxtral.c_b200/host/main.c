@@ -25,19 +25,20 @@ static double now_ms(void) {
 }
 
 static void usage(const char *p) {
-    fprintf(stderr, "usage: %s -d <model_dir> (-i <file.wav> | --stdin) [-I <seconds>] [--stream <chunk_seconds>]\n", p);
+    fprintf(stderr, "usage: %s -d <model_dir> (-i <file.wav> | --stdin) [-I <seconds>] [--stream <chunk_seconds>] [-v]\n", p);
 }
 
 int main(int argc, char **argv) {
     const char *model_dir = NULL, *input = NULL;
     float interval = 2.0f, feed_chunk = 0.0f;
-    int from_stdin = 0;
+    int from_stdin = 0, verbose = 0;
     for (int i = 1; i < argc; i++) {
         if (!strcmp(argv[i], "-d") && i + 1 < argc) model_dir = argv[++i];
         else if (!strcmp(argv[i], "-i") && i + 1 < argc) input = argv[++i];
         else if (!strcmp(argv[i], "-I") && i + 1 < argc) interval = (float)atof(argv[++i]);
         else if (!strcmp(argv[i], "--stream") && i + 1 < argc) feed_chunk = (float)atof(argv[++i]);
         else if (!strcmp(argv[i], "--stdin")) from_stdin = 1;
+        else if (!strcmp(argv[i], "-v")) verbose = 1;
         else { usage(argv[0]); return 2; }
     }
     if (!model_dir || (!input && !from_stdin)) { usage(argv[0]); return 2; }
@@ -105,10 +106,11 @@ int main(int argc, char **argv) {
         double mel_ms, enc_ms, dec_ms;
         int calls, steps;
         vox_b200_stream_stats(s, &mel_ms, &enc_ms, &dec_ms, &calls, &steps);
-        fprintf(stderr, "Mel: %.1f ms\nEncoder: %d calls, %.1f ms (%.2f ms/call)\nDecoder: %d steps, %.1f ms (%.3f ms/step incl. prefill)\n"
+        fprintf(stderr, "Audio: %ld samples (%.1f seconds)\n", fed, fed / 16000.0);     /* voxtral_audio.c summary line */
+        vox_b200_stream_report(s, stderr, verbose);
+        fprintf(stderr, "Mel: %.1f ms; encoder %.2f ms/call over %d calls; %d decoder steps\n"
                         "Stream: %.2f s of audio in %.1f ms, %.1fx real time\n",
-                mel_ms, calls, enc_ms, calls ? enc_ms / calls : 0.0, steps, dec_ms, steps ? dec_ms / steps : 0.0,
-                fed / 16000.0, wall, (fed / 16.0) / wall);
+                mel_ms, calls ? enc_ms / calls : 0.0, calls, steps, fed / 16000.0, wall, (fed / 16.0) / wall);
         vox_b200_stream_free(s);
     }
     free(samples);

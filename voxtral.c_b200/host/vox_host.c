@@ -32,6 +32,7 @@ struct vox_b200_ctx {
     int fd;
     uint8_t *map;
     size_t map_bytes;
+    size_t map_total;       /* length passed to mmap (map_bytes is later reduced to the data section) */
     const char *json;                  /* safetensors header (not NUL terminated) */
     size_t json_len;
     const uint8_t *data;               /* first byte after the header */
@@ -180,7 +181,7 @@ vox_b200_ctx *vox_b200_load(const char *model_dir) {
     c->fd = open(path, O_RDONLY);
     struct stat st;
     if (c->fd < 0 || fstat(c->fd, &st)) { fprintf(stderr, "vox_b200_load: cannot open %s\n", path); goto fail; }
-    c->map_bytes = (size_t)st.st_size;
+    c->map_bytes = c->map_total = (size_t)st.st_size;
     c->map = (uint8_t *)mmap(NULL, c->map_bytes, PROT_READ, MAP_PRIVATE, c->fd, 0);
     if (c->map == MAP_FAILED) { c->map = NULL; fprintf(stderr, "vox_b200_load: mmap failed\n"); goto fail; }
     uint64_t hlen;
@@ -246,7 +247,7 @@ void vox_b200_free(vox_b200_ctx *c) {
     if (c->model) vox_cuda_model_free(c->model);
     for (int i = 0; i < c->n_small; i++) free(c->small[i]);
     free(c->ada_scale);
-    if (c->map) munmap(c->map, c->map_bytes + 8 + c->json_len);
+    if (c->map) munmap(c->map, c->map_total);
     if (c->fd >= 0) close(c->fd);
     free(c);
 }
@@ -322,8 +323,10 @@ struct vox_b200_stream {
     int decoder_started, eos_seen, gen_pos, prev_token;
     int *ids;                   /* pending output queue */
     int n_ids, ids_cap, ids_read;
-    double mel_ms, enc_ms, dec_ms;
-    int enc_calls, dec_steps;
+    double mel_ms, enc_ms, dec_ms, prefill_ms;
+    int enc_calls, dec_steps, n_text;
+    int stem_resid;             /* parity residual of the conv stem (voxtral.c:656-733), to count rows per call */
+    int enc_rows[64];           /* encoder rows of the first 64 calls (diagnostics, -v) */
 };
 
 vox_b200_stream *vox_b200_stream_init(vox_b200_ctx *c) {
@@ -344,8 +347,8 @@ vox_b200_stream *vox_b200_stream_init(vox_b200_ctx *c) {
 
 void vox_b200_set_processing_interval(vox_b200_stream *s, float seconds) {
     if (!s) return;
-    int f = (int)(seconds * 100.0f + 0.5f);
-    s->interval_frames = f < 2 ? 2 : f;
+    int f = (int)((seconds > 0 ? seconds : 0) * 100.0f);       /* voxtral.c:1669-1675 */
+    s->interval_frames = f < 1 ? 1 : f;
 }
 
 static int append(vox_b200_stream *s, const float *x, size_t n, size_t zeros) {
@@ -390,6 +393,7 @@ static int run_decoder(vox_b200_stream *s) {
         int prompt[1 + LEFT_PAD_TOKENS + 64];
         for (int i = 0; i < prompt_len; i++) prompt[i] = i == 0 ? VOX_TOKEN_BOS : VOX_TOKEN_STREAMING_PAD;
         if (vox_cuda_decoder_prefill_fused(st, prompt, 0, prompt_len - 1)) return -1;
+        s->prefill_ms += now_ms() - t0;
         s->decoder_started = 1;
         s->gen_pos = prompt_len - 1;
         s->prev_token = prompt[prompt_len - 1];
@@ -401,6 +405,7 @@ static int run_decoder(vox_b200_stream *s) {
         if (vox_cuda_decoder_run(st, s->prev_token, s->gen_pos, k, out) != k) { free(out); return -1; }
         const int keep = truncate_at_eos(out, k);
         if (keep < k) s->eos_seen = 1;
+        for (int i = 0; i < keep; i++) s->n_text += out[i] >= 1000;
         const int rc = push_ids(s, out, keep);
         s->prev_token = out[k - 1];
         s->gen_pos = total;
@@ -410,6 +415,10 @@ static int run_decoder(vox_b200_stream *s) {
         /* stream_adapter_compact (voxtral.c:762-775): consumed tokens are no longer needed */
         vox_cuda_adapter_discard_before(st, s->gen_pos);
     }
+    /* after EOS nothing consumes adapter tokens any more: drop them as they arrive so that the device
+     * buffer (1024 rows) cannot fill while audio keeps coming (the reference reallocs its host buffer
+     * instead, voxtral.c:905-921) */
+    if (s->eos_seen) vox_cuda_adapter_discard_before(st, total);
     s->dec_ms += now_ms() - t0;
     return 0;
 }
@@ -432,6 +441,8 @@ static int process_frames(vox_b200_stream *s, int upto_frames) {
         t0 = now_ms();
         if (vox_cuda_encode_chunk(st, s->mel, n) < 0) return -1;
         s->enc_ms += now_ms() - t0;
+        if (s->enc_calls < 64) s->enc_rows[s->enc_calls] = (s->stem_resid + n) / 2;
+        s->stem_resid = (s->stem_resid + n) & 1;
         s->enc_calls++;
         s->frames_done += n;
         s->first_chunk_done = 1;
@@ -446,9 +457,10 @@ int vox_b200_stream_feed(vox_b200_stream *s, const float *samples, int n_samples
     s->real_samples += n_samples;
     const int avail = s->n >= WIN ? (int)((s->n - WIN) / HOP) + 1 : 0;
     int fresh = avail - s->frames_done;
-    const int need = s->first_chunk_done ? s->interval_frames : (s->interval_frames > 312 ? s->interval_frames : 312);
-    if (fresh < need) return 0;                         /* wait for a full processing interval (voxtral.c:1669-1675) */
-    fresh &= ~1;
+    /* first chunk: 312 mel frames (the decoder prompt), later ones: the processing interval; every complete
+     * frame goes in, an odd count leaves a conv0 row on the device (voxtral.c:837-840,405,1669-1675) */
+    const int need = s->first_chunk_done ? s->interval_frames : 312;
+    if (fresh < need) return 0;
     if (process_frames(s, s->frames_done + fresh)) { fprintf(stderr, "vox_b200_stream_feed: %s\n", vox_cuda_last_error()); return -1; }
     return 0;
 }
@@ -458,6 +470,13 @@ int vox_b200_stream_finish(vox_b200_stream *s) {
     if (s->finished) return 0;
     const int pad = right_pad_samples((int)(s->real_samples % TOKEN_SAMPLES), s->ctx->delay_tokens);
     if (append(s, NULL, 0, (size_t)pad)) return -1;
+    /* vox_stream_flush: every frame the padding completed goes through the encoder first ... */
+    const int before = s->n >= WIN ? (int)((s->n - WIN) / HOP) + 1 : 0;
+    if (before > s->frames_done && process_frames(s, before)) {
+        fprintf(stderr, "vox_b200_stream_finish: %s\n", vox_cuda_last_error());
+        return -1;
+    }
+    /* ... then vox_mel_finish adds the reflected tail and the last frames follow (voxtral.c:1299-1317) */
     reflect_tail(s->buf, s->n);
     s->n += 200;
     const int total = (int)((s->n - WIN) / HOP) + 1;
@@ -483,6 +502,24 @@ void vox_b200_stream_stats(const vox_b200_stream *s, double *mel_ms, double *enc
     if (decoder_ms) *decoder_ms = s->dec_ms;
     if (encoder_calls) *encoder_calls = s->enc_calls;
     if (decoder_steps) *decoder_steps = s->dec_steps;
+}
+
+/* The reference's own summary lines, byte-compatible with what vox_stream_free prints at verbosity 1
+ * (voxtral.c:1359-1370) and /root/reference/benchmark.py:25-30 parses. */
+void vox_b200_stream_report(const vox_b200_stream *s, FILE *f, int verbose) {
+    if (!s || !f) return;
+    fprintf(f, "Encoder: %d mel -> %d tokens (%.0f ms)\n", s->frames_done, s->gen_pos, s->enc_ms + s->mel_ms);
+    if (s->n_text > 0) {
+        const double gen_ms = s->dec_ms - s->prefill_ms;
+        const int n_generated = s->dec_steps;
+        fprintf(f, "Decoder: %d text tokens (%d steps) in %.0f ms (prefill %.0f ms + %.1f ms/step)\n",
+                s->n_text, n_generated, s->dec_ms, s->prefill_ms, n_generated > 1 ? gen_ms / (n_generated - 1) : 0);
+    }
+    if (verbose) {
+        fprintf(f, "encoder calls: %d rows:", s->enc_calls);
+        for (int i = 0; i < s->enc_calls && i < 64; i++) fprintf(f, " %d", s->enc_rows[i]);
+        fprintf(f, "\n");
+    }
 }
 
 void vox_b200_stream_free(vox_b200_stream *s) {
@@ -515,7 +552,7 @@ float *vox_b200_load_wav(const char *path, int *n_samples) {
         while (p + 8 <= size) {
             uint32_t len;
             memcpy(&len, d + p + 4, 4);
-            if (!memcmp(d + p, "fmt ", 4) && len >= 16) {
+            if (!memcmp(d + p, "fmt ", 4) && len >= 16 && p + 8 + (long)len <= size) {   /* voxtral_audio.c:66 */
                 fmt = d[p + 8] | (d[p + 9] << 8);
                 ch = d[p + 10] | (d[p + 11] << 8);
                 memcpy(&rate, d + p + 12, 4);

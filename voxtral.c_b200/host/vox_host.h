@@ -19,6 +19,7 @@
 #define VOX_HOST_H
 #include <stddef.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #ifdef __cplusplus
 extern "C" {
@@ -49,6 +50,10 @@ int vox_b200_stream_get_ids(vox_b200_stream *s, int *ids_out, int max);
 /* Wall-clock split like the reference's summary lines (voxtral.c:1359-1370). */
 void vox_b200_stream_stats(const vox_b200_stream *s, double *mel_ms, double *encoder_ms, double *decoder_ms,
                            int *encoder_calls, int *decoder_steps);
+/* "Encoder: %d mel -> %d tokens (%.0f ms)" and "Decoder: %d text tokens (%d steps) in ..." exactly as the
+ * reference prints them (voxtral.c:1359-1370; parsed by its benchmark.py:25-30); verbose adds the row count
+ * of every encoder call. */
+void vox_b200_stream_report(const vox_b200_stream *s, FILE *f, int verbose);
 void vox_b200_stream_free(vox_b200_stream *s);
 
 /* 16-bit PCM mono 16 kHz WAV -> f32 samples (malloc'd, caller frees); NULL on anything else. */

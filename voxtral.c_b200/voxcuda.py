@@ -57,6 +57,9 @@ SIGNATURES = {
     "vox_cuda_state_free": (None, [C.c_void_p]),
     "vox_cuda_state_reset_decoder": (None, [C.c_void_p]),
     "vox_cuda_state_reset_encoder": (None, [C.c_void_p]),
+    "vox_cuda_encoder_position": (C.c_int, [C.c_void_p]),
+    "vox_cuda_encoder_set_position": (C.c_int, [C.c_void_p, C.c_int]),
+    "vox_cuda_state_reset_stem": (None, [C.c_void_p]),
     "vox_cuda_decoder_position": (C.c_int, [C.c_void_p]),
     "vox_cuda_decoder_set_position": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_decoder_kv_write": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, f32p, f32p]),
