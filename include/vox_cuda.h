@@ -165,6 +165,15 @@ int vox_cuda_decoder_prefill_fused(vox_cuda_state_t *s, const int *tokens,
 int vox_cuda_decoder_alternatives(vox_cuda_state_t *s, int max_alt, float cutoff,
                                   int *ids);
 
+/* The same rule fused into the decoder kernel (vox_stream_set_alt, voxtral.c:1330-1339): with n_alt > 1 every
+ * following step - single, vox_cuda_decoder_run, vox_cuda_transcribe - also records the best three other
+ * text logits while the logits row is produced (no second pass over the 131072 logits, no logits copy).
+ * vox_cuda_decoder_get_alts returns, for the LAST n steps, n rows of VOX_CUDA_MAX_ALT ids: [0] = the greedy
+ * id, then the alternatives that pass the cutoff, -1 = none (what vox_stream_get_alt hands out per text
+ * token, voxtral.c:1341-1357; non-text ids get no alternatives).  n_alt = 1 switches recording off. */
+int vox_cuda_decoder_set_alt(vox_cuda_state_t *s, int n_alt, float cutoff);
+int vox_cuda_decoder_get_alts(vox_cuda_state_t *s, int n, int *alts_out);
+
 /* ---- encoder (hot path #2) -------------------------------------------- */
 /* vox_encoder_forward_incremental / vox_metal_encoder_full_step
  * (voxtral_encoder.c:495-693, voxtral_metal.h:245): x host [new_len,1280]

@@ -81,6 +81,40 @@ def test_config1_jfk_ids(full_env):
     assert_ids(transcribe(full_env, job_audio("jfk", d)), d, "vox_cuda_transcribe(jfk.wav)")
 
 
+def test_config1_jfk_alternatives_fused_in_the_decoder_kernel(full_env):
+    """--alt for EVERY step of a whole-clip run: the decoder kernel keeps the best text logits beside the argmax
+    (vox_cuda_decoder_set_alt), the host applies the cutoff.  Pinned to what vox_stream_set_alt(4, 0.2) +
+    vox_stream_get_alt of the reference returned for each text token of jfk.wav."""
+    import bench
+    e = full_env
+    d = gold("jfk")
+    want = d["alts"]
+    buf, nf = bench.frame_buffer(job_audio("jfk", d))
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        assert e.L.vox_cuda_decoder_set_alt(st, int(d["alt_n"]), C.c_float(float(d["alt_cutoff"]))) == 0, e.vc.last_error()
+        toks = np.empty(nf // 8 + 8, np.int32)
+        n = e.L.vox_cuda_transcribe(st, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n == len(d["ids"]), (n, e.vc.last_error())
+        rows = np.empty((n, 4), np.int32)
+        assert e.L.vox_cuda_decoder_get_alts(st, n, e.vc.iptr(rows)) == n, e.vc.last_error()
+        assert np.array_equal(rows[:, 0], toks[:n])
+        got = rows[rows[:, 0] >= 1000]
+        assert got.shape == want.shape, (got.shape, want.shape)
+        bad = np.nonzero((got != want).any(axis=1))[0]
+        print("text tokens", len(want), "with >= 1 alternative", int((want[:, 1] >= 0).sum()), "mismatching rows", len(bad))
+        assert len(bad) == 0, (bad[:8].tolist(), got[bad[:3]].tolist(), want[bad[:3]].tolist())
+        # the last-step call (rescan of the logits row) agrees with the fused record of the last step
+        ids = np.empty(8, np.int32)
+        k = e.L.vox_cuda_decoder_alternatives(st, int(d["alt_n"]), C.c_float(float(d["alt_cutoff"])), e.vc.iptr(ids))
+        last = rows[-1]
+        if last[0] >= 1000:
+            assert ids[:k].tolist() == [int(v) for v in last[1:] if v >= 0]
+    finally:
+        e.L.vox_cuda_state_free(st)
+
+
 def test_config2_clip60_ids(full_env):
     d = gold("clip60")
     assert len(d["ids"]) == 761

@@ -59,6 +59,7 @@ extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) {
         const char *env = getenv("VOX_CUDA_DEC_GRAPH");
         s->use_graph_steps = (env && atoi(env)) ? 1 : 0;
     }
+    s->alt_n = 1;
     if (dec_mega_init(s)) goto fail;
     vox_cuda_state_reset_decoder(s);
     vox_cuda_state_reset_encoder(s);
@@ -79,7 +80,7 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     dec_mega_free(s);
     void *ptrs[] = {s->kv_k, s->kv_v, s->d_params, s->d_x, s->d_q, s->d_attn, s->d_h, s->d_logits,
                     s->d_embed_in, s->d_rope, s->d_attn_part, s->d_blockmax, s->d_tokens,
-                    s->adapter_buf, s->pf_buf};
+                    s->adapter_buf, s->pf_buf, s->d_alt, s->d_alt_cand};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (s->m) {
         const size_t kv = (size_t)s->m->n_dec * DEC_WINDOW * DEC_KVDIM * 4;
@@ -87,6 +88,7 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     }
     if (s->h_tokens) cudaFreeHost(s->h_tokens);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    if (s->h_alt) cudaFreeHost(s->h_alt);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -243,6 +245,57 @@ extern "C" int vox_cuda_decoder_run(vox_cuda_state_t *s, int prev_token, int ada
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     for (int i = 0; i < n; i++) tokens_out[i] = s->h_tokens[(c0 + i) & (TOKENS_RING - 1)];
     advance_host(s, n, tokens_out[n - 1]);
+    return n;
+}
+
+// ---- alternatives fused into the step (stream_fill_alts, voxtral.c:955-1010) --------------------
+// The vocabulary phase of the decoder kernel tracks the four best text logits next to the argmax
+// (dec_mega.cu); here the cutoff rule is applied to the per-step records: candidate i is kept while
+// 1 - p_i / p_best <= cutoff, p_i / p_best = exp(l_i - l_best) (the softmax normaliser cancels).
+extern "C" int vox_cuda_decoder_set_alt(vox_cuda_state_t *s, int n_alt, float cutoff) {
+    if (!s) return -1;
+    if (n_alt < 1) n_alt = 1;
+    if (n_alt > VOX_CUDA_MAX_ALT) n_alt = VOX_CUDA_MAX_ALT;
+    if (cutoff < 0.f) cutoff = 0.f;
+    if (cutoff > 1.f) cutoff = 1.f;                  // vox_stream_set_alt, voxtral.c:1330-1339
+    if (n_alt > 1 && s->use_graph_steps) { vox_set_error("decoder_set_alt: needs the default (persistent kernel) engine"); return -1; }
+    if (n_alt > 1 && !s->d_alt) {
+        CUDA_TRY(cudaMalloc((void **)&s->d_alt, sizeof(AltRecord) * TOKENS_RING));
+        CUDA_TRY(cudaMalloc((void **)&s->d_alt_cand, sizeof(float2) * 4 * 1024));
+        CUDA_TRY(cudaMallocHost((void **)&s->h_alt, sizeof(AltRecord) * TOKENS_RING));
+    }
+    s->alt_n = n_alt; s->alt_cutoff = cutoff;
+    return 0;
+}
+
+// alts_out [n][VOX_CUDA_MAX_ALT] for the LAST n decoded steps: [0] = the greedy id, then alternatives, -1 = none.
+// Only text tokens (id >= 1000) get alternatives, as in stream_run_decoder (voxtral.c:1064-1069,1122-1131).
+extern "C" int vox_cuda_decoder_get_alts(vox_cuda_state_t *s, int n, int *alts_out) {
+    if (!s || !alts_out || n < 0 || n > TOKENS_RING || n > s->h_params.step_count) return -1;
+    if (s->alt_n <= 1 || !s->d_alt) { vox_set_error("decoder_get_alts: call vox_cuda_decoder_set_alt(n_alt > 1) before decoding"); return -1; }
+    const int c0 = s->h_params.step_count - n;
+    for (int i = 0; i < n;) {
+        const int slot = (c0 + i) & (TOKENS_RING - 1);
+        const int len = (n - i < TOKENS_RING - slot) ? n - i : TOKENS_RING - slot;
+        CUDA_TRY(cudaMemcpyAsync(s->h_alt + slot, s->d_alt + slot, sizeof(AltRecord) * len, cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->h_tokens + slot, s->d_tokens + slot, (size_t)len * 4, cudaMemcpyDeviceToHost, s->stream));
+        i += len;
+    }
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    for (int i = 0; i < n; i++) {
+        const int slot = (c0 + i) & (TOKENS_RING - 1);
+        const AltRecord &r = s->h_alt[slot];
+        int *o = alts_out + (size_t)i * VOX_CUDA_MAX_ALT;
+        o[0] = s->h_tokens[slot];
+        for (int k = 1; k < VOX_CUDA_MAX_ALT; k++) o[k] = -1;
+        if (o[0] < 1000) continue;
+        for (int k = 0; k + 1 < s->alt_n && k < 3; k++) {
+            if (r.id[k] < 0) break;
+            const float ratio = expf(r.v[k] - r.best);
+            if (1.0f - ratio > s->alt_cutoff) break;
+            o[k + 1] = r.id[k];
+        }
+    }
     return n;
 }
 

@@ -70,6 +70,38 @@ struct Smem {
     int token;
     volatile unsigned issued;               // tiles the producer has requested so far (read by the L2 prefetcher)
     float resid[64];                        // residual values of the rows this CTA owns in wo / w2
+    float altv[CW][4];                      // per-warp top-4 text logits of the vocabulary phase (--alt)
+    int alti[CW][4];
+};
+
+struct Top4 {
+    float v[4]; int i[4];
+    __device__ __forceinline__ void clear() {
+        #pragma unroll
+        for (int k = 0; k < 4; k++) { v[k] = -INFINITY; i[k] = 0x7fffffff; }
+    }
+    // order: larger logit first, lower id on ties; NaN never enters (same rule as the argmax)
+    __device__ __forceinline__ void insert(float nv, int ni) {
+        if (!(nv > v[3] || (nv == v[3] && ni < i[3]))) return;
+        v[3] = nv; i[3] = ni;
+        #pragma unroll
+        for (int k = 3; k > 0; k--) {
+            const bool up = v[k] > v[k - 1] || (v[k] == v[k - 1] && i[k] < i[k - 1]);
+            const float tv = up ? v[k - 1] : v[k]; const int ti = up ? i[k - 1] : i[k];
+            v[k - 1] = up ? v[k] : v[k - 1]; i[k - 1] = up ? i[k] : i[k - 1];
+            v[k] = tv; i[k] = ti;
+        }
+    }
+    __device__ __forceinline__ void merge_warp() {
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov[4]; int oi[4];
+            #pragma unroll
+            for (int k = 0; k < 4; k++) { ov[k] = __shfl_xor_sync(0xffffffffu, v[k], o); oi[k] = __shfl_xor_sync(0xffffffffu, i[k], o); }
+            #pragma unroll
+            for (int k = 0; k < 4; k++) insert(ov[k], oi[k]);
+        }
+    }
 };
 
 struct Params {
@@ -90,6 +122,11 @@ struct Params {
     int spin_ns;                            // back-off of the grid-barrier poll loop (0 = tight loop)
     unsigned *err;
     unsigned long long *prof;               // optional [G][8] cycle counters of consumer thread 0 (debug)
+    // --alt (stream_fill_alts, voxtral.c:955-1010): the vocabulary phase keeps, beside the running argmax, the
+    // four best logits among ids >= 1000; alt_cand [G][4] (value, id) per CTA, alt_out [TOKENS_RING] records
+    float2 *alt_cand;
+    AltRecord *alt_out;
+    int alt_on;
 };
 
 // ---- PTX helpers ---------------------------------------------------------------
@@ -759,8 +796,24 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             t_pro += clock64() - tp;
             float bv = -INFINITY;
             int bi = 0x7fffffff;
-            consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
-                [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); });
+            Top4 top;
+            top.clear();
+            if (P.alt_on)
+                consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
+                    [&](int row, float v0, float) {
+                        P.logits[row] = v0; argmax_merge(bv, bi, v0, row);
+                        if (row >= 1000) top.insert(v0, row);            // TOKEN_TEXT_MIN, voxtral.c:399,986
+                    });
+            else
+                consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
+                    [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); });
+            if (P.alt_on) {
+                top.merge_warp();
+                if (lane == 0) {
+                    #pragma unroll
+                    for (int k = 0; k < 4; k++) { sm.altv[w][k] = top.v[k]; sm.alti[w][k] = top.i[k]; }
+                }
+            }
             // epilogue lanes of every warp hold candidates: block-wide merge
             #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
@@ -775,6 +828,12 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 for (int k = 1; k < CW; k++) argmax_merge(bv, bi, sm.bv[k], sm.bi[k]);
                 P.blockmax[2 * c] = bv;
                 P.blockmax[2 * c + 1] = __int_as_float(bi);
+                if (P.alt_on) {
+                    for (int k = 1; k < CW; k++)
+                        for (int j = 0; j < 4; j++) top.insert(sm.altv[k][j], sm.alti[k][j]);
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++) P.alt_cand[4 * c + j] = make_float2(top.v[j], __int_as_float(top.i[j]));
+                }
             }
         }
         MK_GRID_SYNC();
@@ -800,6 +859,24 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             consumer_sync();
             prev_token = sm.token;
             if (c == 0 && tid == 0) P.tokens[step_count & (TOKENS_RING - 1)] = prev_token;
+            if (P.alt_on && c == 0 && w == 1) {
+                // merge the per-CTA candidates; the greedy token itself is skipped (voxtral.c:987)
+                Top4 top;
+                top.clear();
+                for (int k = lane; k < 4 * G; k += 32) {
+                    const float2 cd = __ldcg(P.alt_cand + k);
+                    if (__float_as_int(cd.y) != prev_token) top.insert(cd.x, __float_as_int(cd.y));
+                }
+                top.merge_warp();
+                if (lane == 0) {
+                    AltRecord r;
+                    r.best = __ldcg(P.logits + prev_token);
+                    #pragma unroll
+                    for (int k = 0; k < 3; k++) { r.v[k] = top.v[k]; r.id[k] = top.i[k] == 0x7fffffff ? -1 : top.i[k]; }
+                    r.pad = 0;
+                    P.alt_out[step_count & (TOKENS_RING - 1)] = r;
+                }
+            }
         }
         step_count += 1;
         pos += 1;
@@ -903,6 +980,7 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.blockmax = s->d_blockmax;
     P.embed_in = s->d_embed_in; P.adapter = s->adapter_buf;
     P.params = s->d_params; P.tokens = s->d_tokens;
+    P.alt_cand = s->d_alt_cand; P.alt_out = s->d_alt; P.alt_on = (s->alt_n > 1 && s->d_alt) ? 1 : 0;
     P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.spin_ns = h->spin_ns; P.err = h->d_err; P.prof = h->d_prof;
     void *args[] = {&P};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void *)mk::dec_mega_kernel, dim3(h->grid), dim3(mk::NT), args,

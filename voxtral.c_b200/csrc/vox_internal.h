@@ -16,6 +16,9 @@ struct DecStepParams {
     int pad;
 };
 
+// --alt: best logit and the three best OTHER text tokens (ids >= 1000, by logit, lowest id on ties) of one step
+struct AltRecord { float best; float v[3]; int id[3]; int pad; };
+
 struct DecLayerDev {
     const uint16_t *wqkv;   // [6144,3072] rows: wq(4096) | wk(1024) | wv(1024)
     const uint16_t *wo;     // [3072,4096]
@@ -74,6 +77,11 @@ struct vox_cuda_state {
     int *d_tokens;               // ring of produced tokens (device), [TOKENS_RING]
     int *h_tokens;               // pinned host copy
     float *h_pinned;             // pinned staging (embed / logits)
+    // --alt (vox_cuda_decoder_set_alt): per-step records written by the decoder kernel, ring indexed like d_tokens
+    AltRecord *d_alt, *h_alt;    // device ring [TOKENS_RING] + pinned host mirror (allocated on first use)
+    float2 *d_alt_cand;          // [grid][4] per-CTA candidates
+    int alt_n;                   // 1 = off
+    float alt_cutoff;
     cudaGraphExec_t step_graph;
     int graph_ready;
     void *mega;                  // MegaHost*, dec_mega.cu (persistent cooperative step kernel)
