@@ -139,6 +139,7 @@ float *__real_vox_encoder_forward_incremental(vox_ctx_t *ctx, const float *x_new
 static int g_log_tok[REFSHIM_LOG_MAX];
 static float g_log_margin[REFSHIM_LOG_MAX];
 static int g_log_n;
+static float g_log_top[REFSHIM_LOG_MAX][5];   /* logit of the returned id, then the 4 best logits among ids >= 1000 other than it */
 static int g_enc_rows[REFSHIM_LOG_MAX];
 static int g_enc_n;
 
@@ -151,6 +152,18 @@ int __wrap_vox_decoder_forward(vox_ctx_t *ctx, const float *input_embeds, float 
             for (int i = 0; i < VOX_VOCAB_SIZE; i++)
                 if (i != tok && logits[i] > second) second = logits[i];
             m = logits[tok] - second;
+        }
+        float *top = g_log_top[g_log_n];
+        top[0] = top[1] = top[2] = top[3] = top[4] = -3.0e38f;
+        if (logits && tok >= 0) {
+            top[0] = logits[tok];
+            for (int i = 1000; i < VOX_VOCAB_SIZE; i++) {
+                const float v = logits[i];
+                if (i == tok || !(v > top[4])) continue;
+                int k = 4;
+                while (k > 1 && v > top[k - 1]) { top[k] = top[k - 1]; k--; }
+                top[k] = v;
+            }
         }
         g_log_tok[g_log_n] = tok;
         g_log_margin[g_log_n] = m;
@@ -168,5 +181,6 @@ void refshim_log_reset(void) { g_log_n = 0; g_enc_n = 0; }
 int refshim_log_count(void) { return g_log_n; }
 const int *refshim_log_tokens(void) { return g_log_tok; }
 const float *refshim_log_margins(void) { return g_log_margin; }
+const float *refshim_log_top(void) { return &g_log_top[0][0]; }
 int refshim_enc_call_count(void) { return g_enc_n; }
 const int *refshim_enc_call_rows(void) { return g_enc_rows; }

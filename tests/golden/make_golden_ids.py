@@ -73,6 +73,7 @@ def run_job(job):
     L.refshim_log_tokens.restype = C.POINTER(C.c_int)
     L.refshim_log_margins.restype = C.POINTER(C.c_float)
     L.refshim_enc_call_rows.restype = C.POINTER(C.c_int)
+    L.refshim_log_top.restype = C.POINTER(C.c_float)
     L.refshim_log_reset()
     s = L.vox_stream_init(ref.ctx)
     assert s
@@ -109,6 +110,7 @@ def run_job(job):
     n = L.refshim_log_count()
     ids = np.ctypeslib.as_array(L.refshim_log_tokens(), shape=(n,)).copy()
     margins = np.ctypeslib.as_array(L.refshim_log_margins(), shape=(n,)).copy()
+    top = np.ctypeslib.as_array(L.refshim_log_top(), shape=(n, 5)).copy()
     ne = L.refshim_enc_call_count()
     enc_rows = np.ctypeslib.as_array(L.refshim_enc_call_rows(), shape=(ne,)).copy()
     alts = np.array(alts, np.int32).reshape(-1, ALT_N)
@@ -119,6 +121,7 @@ def run_job(job):
         text_ids = text_ids[text_ids >= 1000]
     assert np.array_equal(alts[:, 0], text_ids), (alts[:8, 0], text_ids[:8])
     out = {"ids": ids.astype(np.int32), "margins": margins.astype(np.float32), "enc_call_rows": enc_rows.astype(np.int32),
+           "top_logits": top.astype(np.float32),     # [steps][5]: logit of the id, then the 4 best other text logits
            "alts": alts, "alt_n": np.int32(ALT_N), "alt_cutoff": np.float32(ALT_CUTOFF if job == "jfk" else 0.0),
            "n_samples": np.int64(len(x)), "cpu_seconds": np.float32(time.time() - t0)}
     if s16 is not None:

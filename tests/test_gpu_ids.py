@@ -102,8 +102,20 @@ def test_config1_jfk_alternatives_fused_in_the_decoder_kernel(full_env):
         assert np.array_equal(rows[:, 0], toks[:n])
         got = rows[rows[:, 0] >= 1000]
         assert got.shape == want.shape, (got.shape, want.shape)
-        bad = np.nonzero((got != want).any(axis=1))[0]
-        print("text tokens", len(want), "with >= 1 alternative", int((want[:, 1] >= 0).sum()), "mismatching rows", len(bad))
+        # A candidate is kept while 1 - p_i/p_best <= cutoff.  Where the REFERENCE's own ratio sits within 1e-3 of the
+        # cutoff, the ~1e-4 logit difference between two fp32 summation orders decides, so those rows (the fixture
+        # carries the reference logits: 1 of 147 for jfk, |r - cutoff| = 1.9e-4) are compared up to that candidate only.
+        top = d["top_logits"][d["ids"] >= 1000]
+        r = 1.0 - np.exp(top[:, 1:4] - top[:, :1])
+        near = np.abs(r - float(d["alt_cutoff"])) < 1e-3
+        ambiguous = near.any(axis=1)
+        assert int(ambiguous.sum()) <= 2, int(ambiguous.sum())
+        bad = np.nonzero((got != want).any(axis=1) & ~ambiguous)[0]
+        for i in np.nonzero(ambiguous)[0]:
+            k = 1 + int(np.argmax(near[i]))                      # ids before the boundary candidate must still agree
+            assert np.array_equal(got[i, :k], want[i, :k]), (i, got[i].tolist(), want[i].tolist())
+        print("text tokens", len(want), "with >= 1 alternative", int((want[:, 1] >= 0).sum()), "cutoff-boundary rows",
+              int(ambiguous.sum()), "mismatching rows", len(bad))
         assert len(bad) == 0, (bad[:8].tolist(), got[bad[:3]].tolist(), want[bad[:3]].tolist())
         # the last-step call (rescan of the logits row) agrees with the fused record of the last step
         ids = np.empty(8, np.int32)
@@ -239,7 +251,9 @@ def test_dropin_cli_jfk_text_and_timing_lines(full_env, tmp_path):
     # --alt through the reference's own stream_fill_alts on logits copied back from the device
     p = subprocess.run([exe, "-d", full_env.mdir, "-i", wav, "--alt", "0.2", "--silent"], capture_output=True, timeout=900)
     assert p.returncode == 0, p.stderr.decode()[-2000:]
-    assert " t%d" % int(d["ids"][0]) in p.stdout.decode()
+    a0 = [int(v) for v in d["alts"][0] if v >= 0]          # first text token with its alternatives: "[t1| t2]"
+    first = "[" + "|".join(" t%d" % v for v in a0) + "]" if len(a0) > 1 else " t%d" % a0[0]
+    assert p.stdout.decode().lstrip().startswith(first.lstrip("[ ")) or p.stdout.decode().lstrip("[ ").startswith(first.lstrip("[ ")), (first, p.stdout.decode()[:80])
 
 
 @pytest.mark.parametrize("job,interval,piece", [("clip60_i05", 0.5, 8000), ("jfk", 0.0, 0)])
