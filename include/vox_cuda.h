@@ -346,6 +346,9 @@ void vox_cuda_tp_free(vox_cuda_tp_t *tp);
  * the average device time per step in milliseconds (<0 on error). */
 float vox_cuda_bench_decoder_steps(vox_cuda_state_t *s, int prev_token,
                                    int adapter_index, int n, int *tokens_out);
+/* CUDA-event time (ms) of the encoder side of a whole clip on the resident PCM (vox_cuda_pcm_upload):
+ * log-mel + conv stem + 32 layers + adapter (stream_run_encoder, voxtral.c:826-951); <0 on error. */
+float vox_cuda_bench_encoder(vox_cuda_state_t *s, int n_samples, int n_frames);
 /* Number of kernel launches issued by this library since init. */
 unsigned long long vox_cuda_launch_count(void);
 

@@ -309,6 +309,8 @@ print("ROWS" + json.dumps(rows))
     k = first_diff(rows[:, 0], want[:, 0])
     assert k < 0, (job, "text ids differ at", k, rows[k:k + 3].tolist(), want[k:k + 3].tolist())
     if float(d["alt_cutoff"]) > 0:
-        bad = np.nonzero((rows != want).any(axis=1))[0]
+        top = d["top_logits"][d["ids"] >= 1000]                  # rows on the cutoff boundary: see the fused-alternatives test
+        ambiguous = (np.abs(1.0 - np.exp(top[:, 1:4] - top[:, :1]) - float(d["alt_cutoff"])) < 1e-3).any(axis=1)
+        bad = np.nonzero((rows != want).any(axis=1) & ~ambiguous)[0]
         assert len(bad) == 0, (job, "alternatives differ at text positions", bad[:8].tolist(),
                                rows[bad[:3]].tolist(), want[bad[:3]].tolist())

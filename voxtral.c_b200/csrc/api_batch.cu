@@ -87,6 +87,19 @@ int batch_encode_clip(vox_cuda_state *s, const float *pcm, int n_samples, int n_
     return 0;
 }
 
+// CUDA-event time (ms) of the encoder side alone on the resident PCM (vox_cuda_pcm_upload): log-mel -> conv stem ->
+// 32 layers -> adapter, i.e. what stream_run_encoder does for a whole clip (voxtral.c:826-951).  bench.py's tensor roofline.
+extern "C" float vox_cuda_bench_encoder(vox_cuda_state_t *s, int n_samples, int n_frames) {
+    if (!s || n_frames <= 0) return -1.f;
+    cudaStream_t st = s->stream;
+    if (cudaEventRecord(s->ev0, st) != cudaSuccess) return -1.f;
+    if (batch_encode_clip(s, nullptr, n_samples, n_frames)) return -1.f;
+    if (cudaEventRecord(s->ev1, st) != cudaSuccess || cudaEventSynchronize(s->ev1) != cudaSuccess) return -1.f;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+    return ms;
+}
+
 extern "C" int vox_cuda_transcribe(vox_cuda_state_t *s, const float *pcm, int n_samples, int n_frames,
                                    int prompt_len, int *tokens_out, int max_tokens, float *device_ms) {
     if (!s || !tokens_out || n_frames <= 0 || prompt_len < 2 || prompt_len > 128) return -1;

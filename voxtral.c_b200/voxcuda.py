@@ -50,6 +50,7 @@ SIGNATURES = {
     "vox_cuda_last_error": (C.c_char_p, []),
     "vox_cuda_memory_used": (C.c_size_t, []),
     "vox_cuda_launch_count": (C.c_ulonglong, []),
+    "vox_cuda_bench_encoder": (C.c_float, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_model_create": (C.c_void_p, [C.POINTER(Weights)]),
     "vox_cuda_model_set_ada_scale": (C.c_int, [C.c_void_p, f32p]),
     "vox_cuda_model_free": (None, [C.c_void_p]),
