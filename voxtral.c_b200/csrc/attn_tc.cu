@@ -227,6 +227,21 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
 
 }  // namespace at
 
+static int enc_attention_launch(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                                uint16_t *out_b, long ldo, int split, int terms, const int *pos_dev) {
+    EncState *e = (EncState *)s->enc_priv;
+    cudaStream_t st = s->stream;
+    dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
+    if (terms == 3)
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
+                            ENC_RING - 1, out_b, ldo, split, pos_dev));
+    else
+        CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
+                            ENC_RING - 1, out_b, ldo, split, pos_dev));
+    LAUNCHED();
+    return 0;
+}
+
 // qkv: fp32 [M][3*2048] (q rotated in place by rows_rope_kv); kc / vc: this layer's fp32 ring.
 int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                       uint16_t *out_b, long ldo, int split, const int *pos_dev);
@@ -252,13 +267,16 @@ int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, cons
                            ENC_WINDOW, e->att, ENC_QKV)) return -1;
         return f32_to_bf16_rows(st, e->att, ENC_QKV, out_b, ldo, M, ENC_QKV, split);
     }
-    dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
-    if (split)
-        CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
-                            ENC_RING - 1, out_b, ldo, 1, pos_dev));
-    else
-        CUDA_TRY(launch_pdl(at::enc_attn_kernel<1>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
-                            ENC_RING - 1, out_b, ldo, 0, pos_dev));
-    LAUNCHED();
-    return 0;
+    return enc_attention_launch(s, qkv, kc, vc, M, pos0, out_b, ldo, split, split ? 3 : 1, pos_dev);
+}
+
+int enc_attention_terms(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                        uint16_t *out_b, long ldo, int split, int terms) {
+    static int init = 0;
+    if (!init) {
+        cudaFuncSetAttribute(at::enc_attn_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM_BYTES);
+        cudaFuncSetAttribute(at::enc_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM_BYTES);
+        init = 1;
+    }
+    return enc_attention_launch(s, qkv, kc, vc, M, pos0, out_b, ldo, split, terms, nullptr);
 }

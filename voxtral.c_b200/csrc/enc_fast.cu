@@ -23,9 +23,15 @@ int enc_attention(vox_cuda_state *s, const float *qkv, const float *kc, const fl
                   uint16_t *out_b, long ldo, int split);
 int enc_attention_dev(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                       uint16_t *out_b, long ldo, int split, const int *pos_dev);
+// terms = 3: fp32-class products (hi*hi + hi*lo + lo*hi), 1: plain bf16; split = output rows as [hi | lo]
+int enc_attention_terms(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
+                        uint16_t *out_b, long ldo, int split, int terms);
 
 void vox_mem_account(long delta);
 
+#ifndef VOX_ENC_X1_DEFAULT
+#define VOX_ENC_X1_DEFAULT 0
+#endif
 // Activations feeding the tensor cores are stored as TWO bf16 terms, [hi | lo] per
 // row ("bf16x2", a = hi + lo to ~16 mantissa bits); the GEMM walks both halves against
 // the same weights.  That keeps the encoder at fp32-class accuracy (max |d| ~1e-4
@@ -38,6 +44,20 @@ static int split_mode(void) {
         sp = (env && atoi(env)) ? 0 : 1;
     }
     return sp;
+}
+// Which products take SINGLE-bf16 activations (bit set) instead of the hi/lo pair: 1 = wq|wk|wv, 2 = wo,
+// 4 = w1|w3, 8 = w2, 16 = adapter, 32 = attention (QK^T and PV with one term instead of three).
+// VOX_CUDA_ENC_BF16X1=1 is the same as mask 63.  The default is set from the per-product accuracy study in
+// profiles/ (each cleared bit doubles that product's tensor work).
+enum { X1_QKV = 1, X1_WO = 2, X1_W13 = 4, X1_W2 = 8, X1_ADAPTER = 16, X1_ATTN = 32 };
+static int x1_mask(void) {
+    static int m = -1;
+    if (m < 0) {
+        const char *env = getenv("VOX_CUDA_ENC_X1_MASK");
+        m = env ? atoi(env) & 63 : VOX_ENC_X1_DEFAULT;
+        if (!split_mode()) m = 63;
+    }
+    return m;
 }
 
 struct EncFast {
@@ -90,22 +110,24 @@ int enc_layers_fast(vox_cuda_state *s, float *x, int M, float *out) {
     cudaStream_t st = s->stream;
     const size_t kv_layer = (size_t)ENC_RING * ENC_QKV;
     const int pos0 = e->pos;
-    const int sp = split_mode(), mul = sp ? 2 : 1;
-    const int osp = sp ? TC_OUT_SPLIT : 0;
+    const int mask = x1_mask();
+    // per product: split = 1 -> A operand is [hi | lo] (row length 2K), 0 -> one bf16 term
+    const int s_qkv = !(mask & X1_QKV), s_wo = !(mask & X1_WO), s_w13 = !(mask & X1_W13), s_w2 = !(mask & X1_W2);
+    const int s_att = !(mask & X1_ATTN);
     for (int l = 0; l < m->n_enc; l++) {
         const EncLayerDev &L = m->enc[l];
         float *kc = e->kv_k + l * kv_layer, *vc = e->kv_v + l * kv_layer;
-        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.attn_norm, nullptr, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
-        if (gemm_tc(st, M, 3 * ENC_QKV, ENC_DIM, mul * ENC_DIM, f->xn_b, mul * ENC_DIM, L.wqkv,
+        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.attn_norm, nullptr, f->xn_b, (1 + s_qkv) * ENC_DIM, M, ENC_DIM, s_qkv)) return -1;
+        if (gemm_tc(st, M, 3 * ENC_QKV, ENC_DIM, (1 + s_qkv) * ENC_DIM, f->xn_b, (1 + s_qkv) * ENC_DIM, L.wqkv,
                     epi(e->qkv, 3 * ENC_QKV, nullptr, 0, L.bqkv, TC_BIAS | TC_OUT_F32))) return -1;
         if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
-        if (enc_attention(s, e->qkv, kc, vc, M, pos0, f->att_b, mul * ENC_QKV, sp)) return -1;
-        if (gemm_tc(st, M, ENC_DIM, ENC_QKV, mul * ENC_QKV, f->att_b, mul * ENC_QKV, L.wo,
+        if (enc_attention_terms(s, e->qkv, kc, vc, M, pos0, f->att_b, (1 + s_wo) * ENC_QKV, s_wo, s_att ? 3 : 1)) return -1;
+        if (gemm_tc(st, M, ENC_DIM, ENC_QKV, (1 + s_wo) * ENC_QKV, f->att_b, (1 + s_wo) * ENC_QKV, L.wo,
                     epi(x, ENC_DIM, nullptr, 0, L.bo, TC_BIAS | TC_RESIDUAL))) return -1;
-        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.ffn_norm, nullptr, f->xn_b, mul * ENC_DIM, M, ENC_DIM, sp)) return -1;
-        if (gemm_tc(st, M, 2 * ENC_HIDDEN, ENC_DIM, mul * ENC_DIM, f->xn_b, mul * ENC_DIM, L.w13,
-                    epi(nullptr, 0, f->hh_b, mul * ENC_HIDDEN, nullptr, TC_SWIGLU | TC_OUT_BF16 | osp, ENC_HIDDEN))) return -1;
-        if (gemm_tc(st, M, ENC_DIM, ENC_HIDDEN, mul * ENC_HIDDEN, f->hh_b, mul * ENC_HIDDEN, L.w2,
+        if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.ffn_norm, nullptr, f->xn_b, (1 + s_w13) * ENC_DIM, M, ENC_DIM, s_w13)) return -1;
+        if (gemm_tc(st, M, 2 * ENC_HIDDEN, ENC_DIM, (1 + s_w13) * ENC_DIM, f->xn_b, (1 + s_w13) * ENC_DIM, L.w13,
+                    epi(nullptr, 0, f->hh_b, (1 + s_w2) * ENC_HIDDEN, nullptr, TC_SWIGLU | TC_OUT_BF16 | (s_w2 ? TC_OUT_SPLIT : 0), ENC_HIDDEN))) return -1;
+        if (gemm_tc(st, M, ENC_DIM, ENC_HIDDEN, (1 + s_w2) * ENC_HIDDEN, f->hh_b, (1 + s_w2) * ENC_HIDDEN, L.w2,
                     epi(x, ENC_DIM, nullptr, 0, L.b2, TC_BIAS | TC_RESIDUAL))) return -1;
     }
     if (rows_rmsnorm(st, x, ENC_DIM, m->enc_norm, nullptr, out, ENC_DIM, M, ENC_DIM)) return -1;
@@ -120,7 +142,7 @@ int adapter_fast(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *
     if (!f) return -1;
     vox_cuda_model *m = s->m;
     cudaStream_t st = s->stream;
-    const int sp = split_mode(), mul = sp ? 2 : 1;
+    const int sp = !(x1_mask() & X1_ADAPTER), mul = sp ? 2 : 1;
     const int K0 = 4 * ENC_DIM;
     if (f32_to_bf16_rows(st, enc_rows, K0, f->enc_b, mul * K0, k_tokens, K0, sp)) return -1;
     if (gemm_tc(st, k_tokens, DEC_DIM, K0, mul * K0, f->enc_b, mul * K0, m->adapter_w0,
@@ -319,7 +341,7 @@ static int small_graph_mode(void) {
 // M <= 128 new positions: same layer arithmetic as enc_layers_fast (split-bf16 operands, fp32 accumulation)
 int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
     EncState *e = (EncState *)s->enc_priv;
-    if (!split_mode()) return enc_layers_fast(s, x, M, out);    // single-bf16 A/B mode lives on the large-tile path
+    if (x1_mask()) return enc_layers_fast(s, x, M, out);       // single-bf16 products live on the large-tile path only
     if (!fast_get(s)) return -1;
     const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
     EncSmall *q = small_get(s, NB);
