@@ -39,17 +39,17 @@ for rep in range(3):
                  f"compute+other {100 * (t - prof[1] - prof[2] - prof[3] - prof[4]) / t:.1f}%")
     print(line, flush=True)
 
-# barrier skew: for barriers 0..11 from layer 10 of the last step (phases qkv, attn, wo, w13, w2, qkv, ...)
+# barrier skew: for barriers 0..11 from layer 10 of the last step (after wo, w13, w2, wo, ...)
 L.vox_cuda_debug_mega_barriers.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_int)]
 buf = (C.c_ulonglong * (1024 * 24))()
 g = C.c_int()
 if L.vox_cuda_debug_mega_barriers(st, buf, C.byref(g)) == 0:
     a = np.array(buf[:g.value * 24], dtype=np.int64).reshape(g.value, 12, 2)
-    names = ["qkv", "attn", "wo", "w13", "w2"]
+    names = ["wo", "w13", "w2"]     # grid barriers of a layer (qkv -> attention -> wo hand over through counters)
     t0 = a[:, 0, 0].min()
     if os.environ.get("DEC_PROBE_DUMP"):
         np.save(os.environ["DEC_PROBE_DUMP"], a)          # [cta, barrier, (arrive, exit)] ns, for offline analysis
     for k in range(12):
         arr, ex = a[:, k, 0], a[:, k, 1]
-        print(f"barrier {k:2d} after {names[k % 5]:4s}: first arrive {arr.min() - t0:7d} ns, last arrive {arr.max() - t0:7d} "
+        print(f"barrier {k:2d} after {names[k % 3]:4s}: first arrive {arr.min() - t0:7d} ns, last arrive {arr.max() - t0:7d} "
               f"(skew {arr.max() - arr.min():6d}), first exit +{ex.min() - arr.max():5d}, last exit +{ex.max() - arr.max():5d}")

@@ -68,6 +68,8 @@ struct Smem {
     float bv[CW];
     int bi[CW];
     int token;
+    int last_split;                         // this CTA was the last split of its kv head to finish (it merges)
+    int owners;                             // CTAs that own qkv rows of this CTA's kv head
     volatile unsigned issued;               // tiles the producer has requested so far (read by the L2 prefetcher)
     float resid[64];                        // residual values of the rows this CTA owns in wo / w2
     float altv[CW][4];                      // per-warp top-4 text logits of the vocabulary phase (--alt)
@@ -111,6 +113,8 @@ struct Params {
     const float *dec_norm, *ada_scale, *inv_freq;
     float *kv_k, *kv_v;
     float *x, *q, *attn_part, *h, *logits, *blockmax;
+    float *attn;                            // [4096] merged, normalised attention output of the current layer
+    unsigned *attn_cnt;                     // hand-over counters, SYNC_* layout (zeroed by the host before each launch)
     const float *embed_in, *adapter;
     DecStepParams *params;
     int *tokens;
@@ -221,6 +225,30 @@ __device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsign
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     consumer_sync();
+}
+
+// Targeted waits that replace two of the five grid barriers of a layer (all counters are zeroed by the host before
+// every launch and only grow): the attention CTAs of kv head g wait for the CTAs that own rows of q / k / v of g
+// (SYNC_QKV + g), every CTA waits for the 8 merged kv heads before wo (SYNC_ATTN_DONE).
+constexpr int SYNC_ATTN_ARRIVE = 0;          // [8] splits finished per kv head
+constexpr int SYNC_QKV = 8;                  // [8] qkv row owners finished per kv head
+constexpr int SYNC_ATTN_DONE = 16;           // kv heads merged
+constexpr int SYNC_WORDS = 32;
+__device__ __forceinline__ void wait_count(const unsigned *p, unsigned target, unsigned *err, unsigned code) {
+    // thread 0 polls, everyone else parks in the CTA barrier behind it
+    if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        while ((int)(ld_relaxed(p) - target) < 0) {
+            if (clock64() - t0 > 3000000000LL) die(err, code, target);
+        }
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    }
+    consumer_sync();
+}
+// does CTA row range [a, b) of the 6144 qkv rows hold rows of kv head g (its 4 query heads, its k, its v)?
+__device__ __forceinline__ bool qkv_rows_touch(int a, int b, int g) {
+    const int q0 = g * 4 * DEC_HD, k0 = DEC_QDIM + g * DEC_HD, v0 = DEC_QDIM + DEC_KVDIM + g * DEC_HD;
+    return (a < q0 + 4 * DEC_HD && b > q0) || (a < k0 + DEC_HD && b > k0) || (a < v0 + DEC_HD && b > v0);
 }
 
 // rows [r0, r1) of an R-row matrix owned by CTA c; boundaries are multiples of `unit`
@@ -437,7 +465,7 @@ __device__ __forceinline__ int attn_splits(int n_keys, int G) {
 }
 
 __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const float *kc, const float *vc,
-                                                int pos, int n_keys, int c, int G) {
+                                                int pos, int n_keys, int c, int G, unsigned arrivals_expected) {
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const int kvh = c & 7, split = c >> 3;
     const int s_eff = attn_splits(n_keys, G);
@@ -534,6 +562,50 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
         *reinterpret_cast<float2 *>(o + d) = make_float2(n0, n1);
         if (d == 0) { o[DEC_HD] = M; o[DEC_HD + 1] = den; }
     }
+    // The split that finishes LAST for this kv head merges all of them and publishes the normalised rows
+    // (4 heads x 128) once, instead of every CTA of the grid redoing the merge in its wo prologue (148 x the
+    // loads and exps, all hitting the same L2 lines at the same moment).
+    __threadfence();                                     // partial rows visible before the arrival is counted
+    consumer_sync();
+    if (tid == 0) {
+        const unsigned old = atomicAdd(P.attn_cnt + kvh, 1u);
+        sm.last_split = (old + 1u == arrivals_expected) ? 1 : 0;
+    }
+    consumer_sync();
+    if (!sm.last_split) return;
+    __threadfence();                                     // acquire side: the other splits' rows
+    {
+        const int h = tid >> 6, d = (tid & 63) * 2;
+        const float *base = P.attn_part + ((size_t)(kvh * 4 + h)) * PART_LD;
+        const size_t sstride = (size_t)DEC_HEADS * PART_LD;
+        float M = -INFINITY, n0 = 0.f, n1 = 0.f, den = 0.f;
+        for (int sp = 0; sp < s_eff; sp += 8) {              // 16 loads in flight per round trip; one round for <= 8 splits
+            float2 nv[8], ml[8];
+            #pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const int si = min(sp + k, s_eff - 1);
+                nv[k] = __ldcg(reinterpret_cast<const float2 *>(base + si * sstride + d));
+                ml[k] = __ldcg(reinterpret_cast<const float2 *>(base + si * sstride + DEC_HD));
+            }
+            float Mn = M;
+            #pragma unroll
+            for (int k = 0; k < 8; k++) if (sp + k < s_eff) Mn = fmaxf(Mn, ml[k].x);
+            const float c0 = (M == -INFINITY) ? 0.f : expf(M - Mn);
+            n0 *= c0; n1 *= c0; den *= c0;
+            #pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (sp + k < s_eff) {
+                    const float e = (ml[k].x == -INFINITY) ? 0.f : expf(ml[k].x - Mn);
+                    n0 = fmaf(e, nv[k].x, n0); n1 = fmaf(e, nv[k].y, n1); den = fmaf(e, ml[k].y, den);
+                }
+            }
+            M = Mn;
+        }
+        const float inv = den > 0.f ? 1.0f / den : 0.f;
+        *reinterpret_cast<float2 *>(P.attn + (kvh * 4 + h) * DEC_HD + d) = make_float2(n0 * inv, n1 * inv);
+    }
+    consumer_sync();
+    if (tid == 0) red_release_add(P.attn_cnt + SYNC_ATTN_DONE, 1u);     // one of the 8 kv heads is ready for wo
 }
 
 // ---- the kernel ----------------------------------------------------------------------------
@@ -647,6 +719,25 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     // rows of the [3072]-row matrices (wo, w2) this CTA owns: residual values are staged in smem
     int rr0, rr1;
     cta_rows(DEC_DIM, 1, c, G, rr0, rr1);
+    // arrivals per kv head since kernel start (every CTA tracks the same number); the counters are zeroed here,
+    // a whole qkv phase and a grid barrier before their first use
+    unsigned attn_arrivals = 0, layer_phases = 0;
+    // who feeds whom in the qkv -> attention hand-over
+    int my_heads = 0;                           // bit g: this CTA owns rows of kv head g
+    {
+        int a, b;
+        cta_rows(DEC_QKV, 2, c, G, a, b);
+        #pragma unroll
+        for (int g = 0; g < 8; g++) my_heads |= qkv_rows_touch(a, b, g) ? (1 << g) : 0;
+        if (tid == 0) sm.owners = 0;
+        consumer_sync();
+        if (tid < G) {
+            cta_rows(DEC_QKV, 2, tid, G, a, b);
+            if (qkv_rows_touch(a, b, c & 7)) atomicAdd(&sm.owners, 1);
+        }
+        consumer_sync();
+    }
+    const unsigned owners = (unsigned)sm.owners;
 
     for (int step = 0; step < P.n_steps; step++) {
         const int n_keys = min(n_valid, DEC_WINDOW - 1) + 1;
@@ -704,61 +795,32 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                         *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
                     });
             }
-            MK_GRID_SYNC();
-            // ---------------- phase 2: attention partials ----------------
+            // q / k / v rows of this CTA are written: tell the attention CTAs of the kv heads they belong to
+            layer_phases += 1u;
+            consumer_sync();
+            if (tid < 8 && ((my_heads >> tid) & 1)) red_release_add(P.attn_cnt + SYNC_QKV + tid, 1u);
+            // ---------------- phase 2: attention partials (the CTAs that own a key range of a kv head) ----------------
             {
                 const long long ta = clock64();
-                attention_phase(sm, P, kc, vc, pos, n_keys, c, G);
+                attn_arrivals += (unsigned)s_eff;
+                if ((c >> 3) < s_eff) {
+                    wait_count(P.attn_cnt + SYNC_QKV + (c & 7), owners * layer_phases, P.err, 3u);
+                    attention_phase(sm, P, kc, vc, pos, n_keys, c, G, attn_arrivals);
+                }
                 t_attn += clock64() - ta;
             }
-            MK_GRID_SYNC();
+            // every CTA: all 8 kv heads merged?
+            {
+                const long long tg_ = clock64();
+                wait_count(P.attn_cnt + SYNC_ATTN_DONE, 8u * layer_phases, P.err, 4u);
+                t_grid += clock64() - tg_;
+            }
             // ---------------- phase 3: merge partials -> wo -> residual ----------------
             {
                 const long long tp = clock64();
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_QDIM / 256];
-                // online merge of the split partials, 4 splits x 4 heads of loads in flight per round trip
-                float Mj[4], dj[4];
-                float4 nj[4];
-                #pragma unroll
-                for (int j = 0; j < 4; j++) { Mj[j] = -INFINITY; dj[j] = 0.f; nj[j] = make_float4(0.f, 0.f, 0.f, 0.f); }
-                for (int sb = 0; sb < s_eff; sb += 4) {
-                    float2 ml[4][4];
-                    float4 av[4][4];
-                    #pragma unroll
-                    for (int j = 0; j < 4; j++)
-                        #pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            const int sidx = min(sb + k, s_eff - 1);     // clamped duplicates are masked below
-                            const float *o = P.attn_part + ((size_t)sidx * DEC_HEADS + (j * 8 + w)) * PART_LD;
-                            ml[j][k] = __ldcg(reinterpret_cast<const float2 *>(o + DEC_HD));
-                            av[j][k] = __ldcg(reinterpret_cast<const float4 *>(o) + lane);
-                        }
-                    #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        float M = Mj[j];
-                        #pragma unroll
-                        for (int k = 0; k < 4; k++) if (sb + k < s_eff) M = fmaxf(M, ml[j][k].x);
-                        const float c0 = (Mj[j] == -INFINITY) ? 0.f : expf(Mj[j] - M);
-                        nj[j].x *= c0; nj[j].y *= c0; nj[j].z *= c0; nj[j].w *= c0; dj[j] *= c0;
-                        #pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            if (sb + k < s_eff) {
-                                const float e = (ml[j][k].x == -INFINITY) ? 0.f : expf(ml[j][k].x - M);
-                                nj[j].x = fmaf(e, av[j][k].x, nj[j].x); nj[j].y = fmaf(e, av[j][k].y, nj[j].y);
-                                nj[j].z = fmaf(e, av[j][k].z, nj[j].z); nj[j].w = fmaf(e, av[j][k].w, nj[j].w);
-                                dj[j] = fmaf(e, ml[j][k].y, dj[j]);
-                            }
-                        }
-                        Mj[j] = M;
-                    }
-                }
-                #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float inv = dj[j] > 0.f ? 1.0f / dj[j] : 0.f;
-                    xr[4 * j] = nj[j].x * inv; xr[4 * j + 1] = nj[j].y * inv;
-                    xr[4 * j + 2] = nj[j].z * inv; xr[4 * j + 3] = nj[j].w * inv;
-                }
+                (void)load_slice<DEC_QDIM>(P.attn, col0, xr);     // rows merged by the last split of each kv head
                 t_pro += clock64() - tp;
                 consume<DEC_QDIM, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait,
                     [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
@@ -921,11 +983,11 @@ int dec_mega_init(vox_cuda_state *s) {
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel, mk::NT, sizeof(mk::Smem)));
     if (occ < 1 || sms < 8) { vox_set_error("dec_mega: kernel does not fit (occupancy %d, %d SMs)", occ, sms); return -1; }
     h->grid = sms;
-    h->barriers_per_step = 5 * s->m->n_dec + 1;
+    h->barriers_per_step = 3 * s->m->n_dec + 1;       // after wo, w1|w3, w2 of every layer + after the logits
     CUDA_TRY(cudaMalloc((void **)&h->d_layers, sizeof(DecLayerDev) * VOX_CUDA_DEC_LAYERS));
     CUDA_TRY(cudaMemcpy(h->d_layers, s->m->dec, sizeof(DecLayerDev) * VOX_CUDA_DEC_LAYERS, cudaMemcpyHostToDevice));
-    CUDA_TRY(cudaMalloc((void **)&h->d_bar, 8));
-    CUDA_TRY(cudaMemset(h->d_bar, 0, 8));
+    CUDA_TRY(cudaMalloc((void **)&h->d_bar, 256));                  // [0] grid barrier, [8 ...] hand-over counters (SYNC_*)
+    CUDA_TRY(cudaMemset(h->d_bar, 0, 256));
     // watchdog record in mapped host memory: still readable after a device-side trap
     CUDA_TRY(cudaHostAlloc((void **)&h->d_err, 16, cudaHostAllocMapped));
     memset(h->d_err, 0, 16);
@@ -976,12 +1038,14 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.layers = h->d_layers; P.n_dec = m->n_dec;
     P.tok_emb = m->tok_emb; P.dec_norm = m->dec_norm; P.ada_scale = m->ada_scale; P.inv_freq = m->inv_freq_dec;
     P.kv_k = s->kv_k; P.kv_v = s->kv_v;
+    P.attn = s->d_attn; P.attn_cnt = h->d_bar + 8;
     P.x = s->d_x; P.q = s->d_q; P.attn_part = s->d_attn_part; P.h = s->d_h; P.logits = s->d_logits;
     P.blockmax = s->d_blockmax;
     P.embed_in = s->d_embed_in; P.adapter = s->adapter_buf;
     P.params = s->d_params; P.tokens = s->d_tokens;
     P.alt_cand = s->d_alt_cand; P.alt_out = s->d_alt; P.alt_on = (s->alt_n > 1 && s->d_alt) ? 1 : 0;
     P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.spin_ns = h->spin_ns; P.err = h->d_err; P.prof = h->d_prof;
+    CUDA_TRY(cudaMemsetAsync(h->d_bar + 8, 0, mk::SYNC_WORDS * sizeof(unsigned), s->stream));   // hand-over counters start at 0
     void *args[] = {&P};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void *)mk::dec_mega_kernel, dim3(h->grid), dim3(mk::NT), args,
                                          sizeof(mk::Smem), s->stream));
