@@ -9,10 +9,10 @@
 //   * warp 8 (one elected lane) is the PRODUCER: it walks the static list of
 //     weight tiles this CTA owns - contiguous row ranges of every matrix, in
 //     consumption order, across phase, layer and token boundaries - and streams
-//     them into an 8 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
+//     them into a 6 x 24 KB shared-memory ring with cp.async.bulk (TMA 1-D
 //     bulk copies, mbarrier complete_tx, L2 evict_first).  It never waits for
 //     activations, only for ring space, so the HBM pipe stays busy while the
-//     consumers sit in a grid barrier (192 KB/SM = 4.4 us of HBM time).
+//     consumers sit in a grid barrier (144 KB/SM = 3.3 us of HBM time; deeper rings measured slower).
 //   * warps 0-7 are CONSUMERS: each warp owns a fixed K-slice of every row (its
 //     slice of the activation vector lives in registers), all warps multiply each
 //     tile as it lands (packed FFMA2), row sums are combined once per group of
@@ -34,12 +34,12 @@ namespace mk {
 #define MK_PROF 0                           // 1: per-tile wait timing of the consumers (VOX_CUDA_MEGA_PROF readout); `make prof`
 #endif
 #ifndef MK_NSTAGE
-#define MK_NSTAGE 8
+#define MK_NSTAGE 6                         // ring depth: 4 / 6 / 8 stages measured 1.434 / 1.427 / 1.470 ms per token
 #endif
 
 constexpr int CW = 8;                       // consumer warps
 constexpr int CT = CW * 32;                 // consumer threads
-constexpr int NT = CT + 64;                 // + producer warp + L2 prefetch warp
+constexpr int NT = CT + 128;                // + one warpgroup: producer warp, L2 prefetch warp, two idle warps (setmaxnreg needs whole warpgroups)
 constexpr int STAGE_BYTES = 24576;
 constexpr int NSTAGE = MK_NSTAGE;
 constexpr int MAXTR = 4;                    // rows per tile at K = 3072
@@ -465,7 +465,8 @@ __device__ __forceinline__ int attn_splits(int n_keys, int G) {
 }
 
 __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const float *kc, const float *vc,
-                                                int pos, int n_keys, int c, int G, unsigned arrivals_expected) {
+                                                int pos, int n_keys, int c, int G, unsigned arrivals_expected,
+                                                const unsigned *qkv_ready, unsigned qkv_target) {
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
     const int kvh = c & 7, split = c >> 3;
     const int s_eff = attn_splits(n_keys, G);
@@ -475,6 +476,20 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
     const int U = s_eff * CW, u = split * CW + w;
     const int g0 = (int)(((long long)u * ng) / U), g1 = (int)(((long long)(u + 1) * ng) / U);
     const float scale = 0.08838834764831845f;  // 1/sqrt(128)
+    const size_t hoff = (size_t)kvh * DEC_HD + 4 * lane;
+    // Keys of earlier tokens do not depend on this step: the first group's K / V rows are requested BEFORE waiting
+    // for the owners of this kv head's q / k / v rows (the newest key, written in this step, sits in the last group).
+    float4 kf[8], vf[8];
+    const bool pre = g0 < g1 && g0 * 8 + 8 <= n_keys - 1;
+    if (pre) {
+        #pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int slot = (first + g0 * 8 + i) & (DEC_WINDOW - 1);
+            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
+            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+        }
+    }
+    wait_count(qkv_ready, qkv_target, P.err, 3u);
     float4 q[4];
     #pragma unroll
     for (int h = 0; h < 4; h++) q[h] = __ldcg(reinterpret_cast<const float4 *>(P.q + (kvh * 4 + h) * DEC_HD) + lane);
@@ -482,16 +497,16 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
     float4 acc[4];
     #pragma unroll
     for (int h = 0; h < 4; h++) acc[h] = make_float4(0.f, 0.f, 0.f, 0.f);
-    const size_t hoff = (size_t)kvh * DEC_HD + 4 * lane;
     for (int g = g0; g < g1; g++) {
         const int j0 = g * 8;
         const int nv = min(8, n_keys - j0);
-        float4 kf[8], vf[8];
-        #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamp: always a valid row
-            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
-            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+        if (!(pre && g == g0)) {
+            #pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamp: always a valid row
+                kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
+                vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+            }
         }
         float v[32];
         #pragma unroll
@@ -660,7 +675,10 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
 
     const int n_dec = P.n_dec;
 
+    // Register reallocation between warpgroups: ptxas caps a 384-thread CTA at 168 registers per thread, which
+    // spills in the consumers; the producer warpgroup keeps 40 and hands the rest to the two consumer warpgroups.
     if (tid >= CT) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         // =========================== PRODUCER ===========================
         if (tid == CT + 32 && P.l2_ahead > 0) {
             unsigned fg = 0;
@@ -693,6 +711,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     }
 
     // =============================== CONSUMERS ===============================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int w = tid >> 5, lane = tid & 31;
     unsigned gt = 0;                              // global index of the next phase's first tile
     int pbuf = 0;
@@ -803,10 +822,9 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             {
                 const long long ta = clock64();
                 attn_arrivals += (unsigned)s_eff;
-                if ((c >> 3) < s_eff) {
-                    wait_count(P.attn_cnt + SYNC_QKV + (c & 7), owners * layer_phases, P.err, 3u);
-                    attention_phase(sm, P, kc, vc, pos, n_keys, c, G, attn_arrivals);
-                }
+                if ((c >> 3) < s_eff)
+                    attention_phase(sm, P, kc, vc, pos, n_keys, c, G, attn_arrivals,
+                                    P.attn_cnt + SYNC_QKV + (c & 7), owners * layer_phases);
                 t_attn += clock64() - ta;
             }
             // every CTA: all 8 kv heads merged?
