@@ -341,6 +341,24 @@ int  vox_cuda_tp_transcribe(vox_cuda_tp_t *tp, const float *pcm, int n_samples, 
                             int prompt_len, int *tokens_out, int max_tokens, float *ms_per_step);
 void vox_cuda_tp_free(vox_cuda_tp_t *tp);
 
+/* ---- an entry point that allocates nothing (csrc/noalloc.cu) ---------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The rule of vox_cuda_decoder_alternatives on a logits row the caller passes: the best (max_alt - 1) ids >= 1000
+ * other than best_token, by logit (lowest id on ties), kept while 1 - p_i / p_best <= cutoff; ids_out gets up to
+ * VOX_CUDA_MAX_ALT - 1 ids, *count_out their number.  logits, ids_out and count_out must be DEVICE-ACCESSIBLE
+ * (device memory, or pinned host memory such as vox_cuda_host_alloc returns).  The kernel's scratch (per-slice
+ * candidates + an arrival counter, 8448 bytes) is a file-scope static __device__ array that every GPU loading the
+ * library holds until exit; it bounds the input: n_logits <= VOX_CUDA_NOALLOC_MAX_LOGITS, larger rows are rejected
+ * (-1 + vox_cuda_last_error()).  The call performs no cudaMalloc / cudaFree / allocating library call: it enqueues
+ * one 4-byte memset and one kernel on `stream` (a cudaStream_t, NULL = the default stream) and, if sync != 0, waits
+ * for them; with sync == 0 the outputs are valid once the caller has synchronised the stream.  The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress) - make it outside a capture.  All calls share the
+ * array: calls that overlap on the GPU (different streams without a dependency) race; ordered calls are fine. */
+#define VOX_CUDA_NOALLOC_MAX_LOGITS 262144
+int vox_cuda_alternatives_noalloc(const float *logits, int n_logits, int best_token, int max_alt, float cutoff,
+                                  int *ids_out, int *count_out, void *stream, int sync);
+
 /* ---- measurement helpers (bench.py / profiles) ------------------------ */
 /* vox_cuda_decoder_run timed with CUDA events on the launch stream: returns
  * the average device time per step in milliseconds (<0 on error). */

@@ -72,6 +72,8 @@ SIGNATURES = {
     "vox_cuda_decoder_read_logits": (C.c_int, [C.c_void_p, f32p]),
     "vox_cuda_decoder_prefill_fused": (C.c_int, [C.c_void_p, i32p, C.c_int, C.c_int]),
     "vox_cuda_decoder_alternatives": (C.c_int, [C.c_void_p, C.c_int, C.c_float, i32p]),
+    "vox_cuda_alternatives_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_int]),
     "vox_cuda_decoder_set_alt": (C.c_int, [C.c_void_p, C.c_int, C.c_float]),
     "vox_cuda_decoder_get_alts": (C.c_int, [C.c_void_p, C.c_int, i32p]),
     "vox_cuda_gemm_bf16_streams": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, u16p, C.c_int, C.c_int, f32p]),
