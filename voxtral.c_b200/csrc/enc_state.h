@@ -2,9 +2,11 @@
 #pragma once
 #include "vox_internal.h"
 
-constexpr int ENC_CHUNK = 2048;    // max encoder positions per internal pass
-constexpr int ENC_MAXMEL = 4096;   // max mel frames per internal pass (= 2 * ENC_CHUNK)
-constexpr int ENC_RING = 4096;     // KV ring slots (>= ENC_CHUNK + 1 + ENC_WINDOW - 1), power of two
+constexpr int ENC_CHUNK = 3328;    // max encoder positions per internal pass (26 row tiles: a 60 s clip = 3196 positions is ONE pass,
+                                   // so its N = 1280 products are 125 tiles in one wave instead of 80 + 45 in two)
+constexpr int ENC_MAXMEL = 6656;   // max mel frames per internal pass (= 2 * ENC_CHUNK)
+constexpr int ENC_RING = 4096;     // KV ring slots (>= ENC_CHUNK + ENC_WINDOW - 1 = 4077), power of two
+static_assert(ENC_RING >= ENC_CHUNK + 750 - 1 && ENC_MAXMEL == 2 * ENC_CHUNK, "encoder pass limits");
 
 struct EncState {
     // KV ring, slot = logical position & (ENC_RING-1).  Replaces the memmove

@@ -423,12 +423,12 @@ static int run_decoder(vox_b200_stream *s) {
     return 0;
 }
 
-/* mel + encoder on every frame that is complete, in chunks of at most 4096 frames */
+/* mel + encoder on every frame that is complete, in chunks of at most 6656 frames (one internal pass of the backend) */
 static int process_frames(vox_b200_stream *s, int upto_frames) {
     vox_cuda_state_t *st = s->ctx->state;
     while (s->frames_done < upto_frames) {
         int n = upto_frames - s->frames_done;
-        if (n > 4096) n = 4096;
+        if (n > 6656) n = 6656;
         if (n > s->mel_cap) {
             float *p = (float *)realloc(s->mel, sizeof(float) * 128 * (size_t)n);
             if (!p) return -1;
