@@ -192,6 +192,11 @@ __device__ __forceinline__ unsigned ld_relaxed(const unsigned *p) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -217,12 +222,12 @@ __device__ __forceinline__ void grid_sync(unsigned *bar, unsigned target, unsign
             red_release_add(bar, 1u);
         }
         const long long t0 = clock64();
-        while ((int)(ld_relaxed(bar) - target) < 0) {
+        // acquire loads: the one that sees the last arrival's release orders everything after it, no separate fence
+        while ((int)(ld_acquire(bar) - target) < 0) {
             if (spin_ns) __nanosleep(spin_ns);
             if (clock64() - t0 > 3000000000LL) die(err, 2u, target);
         }
         if (t_own) *t_own += clock64() - t0;    // spin time
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     consumer_sync();
 }
@@ -238,10 +243,9 @@ __device__ __forceinline__ void wait_count(const unsigned *p, unsigned target, u
     // thread 0 polls, everyone else parks in the CTA barrier behind it
     if (threadIdx.x == 0) {
         const long long t0 = clock64();
-        while ((int)(ld_relaxed(p) - target) < 0) {
+        while ((int)(ld_acquire(p) - target) < 0) {
             if (clock64() - t0 > 3000000000LL) die(err, code, target);
         }
-        asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     consumer_sync();
 }
