@@ -229,6 +229,16 @@ def run_cuda(args, rank, world):
         vc.check(L.vox_cuda_decoder_set_position(st, 20000, 8192), "set_position")
         full_window = {"ms_per_token": float(L.vox_cuda_bench_decoder_steps(st, 32, 38, 200, None)),
                        "kv_bytes_per_token": 26 * 8192 * 1024 * 4 * 2}
+        # the same step with fp16 K/V rings (the reference's GPU default): reported beside, not as, the fp32 number
+        st16 = vc.check(L.vox_cuda_state_create_ex(model, 16), "state_create_ex")
+        n16 = vc.check(L.vox_cuda_transcribe(st16, vc.fptr(pinned), len(buf), nf, PROMPT_LEN, vc.iptr(toks), max_tok, None), "transcribe")
+        ids16 = toks[:n16].copy()
+        vc.check(L.vox_cuda_decoder_set_position(st16, 20000, 8192), "set_position")
+        full_window["fp16_kv"] = {"ms_per_token": float(L.vox_cuda_bench_decoder_steps(st16, 32, 38, 200, None)),
+                                  "kv_bytes_per_token": 26 * 8192 * 1024 * 2 * 2,
+                                  "clip_ids_equal_fp32_kv": int((ids16 == toks_e2e[:n16]).sum()) if n16 == n_tok else None,
+                                  "clip_steps": int(n16)}
+        L.vox_cuda_state_free(st16)
     # ---- config 5 leg: S independent clips per GPU through a stream group (lock-step decode, one pass
     # over the weights per step); host PCM in, token ids out, inside the timed region ----
     multi = None

@@ -104,6 +104,15 @@ void vox_cuda_model_free(vox_cuda_model_t *m);
  *      voxtral_encoder.c:371-391, and the stream's conv tails
  *      voxtral.c:469-483) ------------------------------------------------- */
 vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m);
+/* kv_bits 32 = the call above (fp32 rings: the reference's CPU / BLAS layout, ids equal the reference);
+ * 16 = fp16 decoder K/V rings, the reference's GPU default ("fp16 KV", voxtral.c:189-190, SPEED.md:24-43):
+ * rows are rounded once when appended, scores / softmax / output stay fp32; half the K/V bytes per token
+ * (0.87 instead of 1.74 GB at the full 8192-key window).  Not bit-comparable with the fp32 BLAS oracle: the
+ * tests state the logit tolerance (tests/test_gpu_kv16.py).  Prompt prefill: at most 128 rows at position 0.
+ * vox_cuda_decoder_kv_read / _write keep fp32 host rows and convert.  Default engine only (not the legacy
+ * graph decoder, not the tensor-parallel decoder). */
+vox_cuda_state_t *vox_cuda_state_create_ex(vox_cuda_model_t *m, int kv_bits);
+int  vox_cuda_state_kv_bits(const vox_cuda_state_t *s);
 void vox_cuda_state_free(vox_cuda_state_t *s);
 /* kv_cache_len = kv_pos_offset = 0 (voxtral.c:781-782,1050-1051). */
 void vox_cuda_state_reset_decoder(vox_cuda_state_t *s);

@@ -2,6 +2,7 @@
 #include "vox_internal.h"
 #include "rows.h"
 #include "gemm_tc.h"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
@@ -29,13 +30,27 @@ static int push_params(vox_cuda_state *s) {
     return 0;
 }
 
-extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) {
+extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) { return vox_cuda_state_create_ex(m, 32); }
+
+extern "C" int vox_cuda_state_kv_bits(const vox_cuda_state_t *s) { return s ? (s->kv16 ? 16 : 32) : -1; }
+
+// kv_bits 32: fp32 K/V rings (the reference's CPU / BLAS layout: ids equal the reference); 16: fp16 rings, the
+// reference's GPU default (voxtral.c:189-190) - half the K/V bytes per token (0.87 of 1.74 GB at the full window).
+extern "C" vox_cuda_state_t *vox_cuda_state_create_ex(vox_cuda_model_t *m, int kv_bits) {
     if (!m) return nullptr;
+    if (kv_bits != 32 && kv_bits != 16) { vox_set_error("state_create: kv_bits must be 32 or 16"); return nullptr; }
     vox_cuda_state *s = (vox_cuda_state *)calloc(1, sizeof(vox_cuda_state));
     s->m = m;
-    const size_t kv = (size_t)m->n_dec * DEC_WINDOW * DEC_KVDIM * 4;
+    s->kv16 = kv_bits == 16;
+    const size_t kv = s->kv16 ? (size_t)m->n_dec * PF_KV_ROWS * DEC_KVDIM * 4 : (size_t)m->n_dec * DEC_WINDOW * DEC_KVDIM * 4;
+    const size_t kvh = (size_t)m->n_dec * DEC_WINDOW * DEC_KVDIM * 2;
     if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) goto fail;
     DM(s->kv_k, kv); DM(s->kv_v, kv);
+    if (s->kv16) {
+        DM(s->kv_k16, kvh); DM(s->kv_v16, kvh);
+        if (cudaMemsetAsync(s->kv_k16, 0, kvh, s->stream) != cudaSuccess) goto fail;
+        if (cudaMemsetAsync(s->kv_v16, 0, kvh, s->stream) != cudaSuccess) goto fail;
+    }
     DM(s->d_params, sizeof(DecStepParams));
     DM(s->d_x, DEC_DIM * 4); DM(s->d_q, DEC_QDIM * 4); DM(s->d_attn, DEC_QDIM * 4);
     DM(s->d_h, DEC_HIDDEN * 4); DM(s->d_logits, (size_t)VOCAB * 4); DM(s->d_embed_in, DEC_DIM * 4);
@@ -58,6 +73,7 @@ extern "C" vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m) {
     {
         const char *env = getenv("VOX_CUDA_DEC_GRAPH");
         s->use_graph_steps = (env && atoi(env)) ? 1 : 0;
+        if (s->use_graph_steps && s->kv16) { vox_set_error("state_create: fp16 K/V needs the default (persistent kernel) engine"); goto fail; }
     }
     s->alt_n = 1;
     if (dec_mega_init(s)) goto fail;
@@ -80,10 +96,11 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     dec_mega_free(s);
     void *ptrs[] = {s->kv_k, s->kv_v, s->d_params, s->d_x, s->d_q, s->d_attn, s->d_h, s->d_logits,
                     s->d_embed_in, s->d_rope, s->d_attn_part, s->d_blockmax, s->d_tokens,
-                    s->adapter_buf, s->pf_buf, s->d_alt, s->d_alt_cand};
+                    s->adapter_buf, s->pf_buf, s->d_alt, s->d_alt_cand, s->kv_k16, s->kv_v16};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (s->m) {
-        const size_t kv = (size_t)s->m->n_dec * DEC_WINDOW * DEC_KVDIM * 4;
+        const size_t kv = s->kv16 ? (size_t)s->m->n_dec * (PF_KV_ROWS * 4 + DEC_WINDOW * 2) * DEC_KVDIM
+                                  : (size_t)s->m->n_dec * DEC_WINDOW * DEC_KVDIM * 4;
         vox_mem_account(-(long)(2 * kv));
     }
     if (s->h_tokens) cudaFreeHost(s->h_tokens);
@@ -122,6 +139,28 @@ static int kv_copy(vox_cuda_state *s, int layer, int logical_pos, int n, float *
         const int run = (n - done < DEC_WINDOW - slot) ? n - done : DEC_WINDOW - slot;   // up to the ring end
         const size_t bytes = (size_t)run * DEC_KVDIM * sizeof(float);
         const size_t doff = layer_off + (size_t)slot * DEC_KVDIM, hoff = (size_t)done * DEC_KVDIM;
+        if (s->kv16) {                                   // host rows stay fp32 (the reference's layout): convert on the host
+            const size_t cnt = (size_t)run * DEC_KVDIM;
+            __half *tmp = (__half *)malloc(cnt * sizeof(__half));
+            if (!tmp) return -1;
+            for (int which = 0; which < 2; which++) {
+                float *h = which ? v : k;
+                __half *d = (__half *)(which ? s->kv_v16 : s->kv_k16) + doff;
+                if (!h) continue;
+                cudaError_t e;
+                if (to_device) {
+                    for (size_t i = 0; i < cnt; i++) tmp[i] = __float2half_rn(h[hoff + i]);
+                    e = cudaMemcpy(d, tmp, cnt * sizeof(__half), cudaMemcpyHostToDevice);
+                } else {
+                    e = cudaMemcpy(tmp, d, cnt * sizeof(__half), cudaMemcpyDeviceToHost);
+                    for (size_t i = 0; i < cnt; i++) h[hoff + i] = __half2float(tmp[i]);
+                }
+                if (e != cudaSuccess) { free(tmp); vox_set_error("decoder_kv copy: %s", cudaGetErrorString(e)); return -1; }
+            }
+            free(tmp);
+            done += run;
+            continue;
+        }
         if (k) CUDA_TRY(to_device ? cudaMemcpy(s->kv_k + doff, k + hoff, bytes, cudaMemcpyHostToDevice)
                                   : cudaMemcpy(k + hoff, s->kv_k + doff, bytes, cudaMemcpyDeviceToHost));
         if (v) CUDA_TRY(to_device ? cudaMemcpy(s->kv_v + doff, v + hoff, bytes, cudaMemcpyHostToDevice)
@@ -438,6 +477,17 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
     return 0;
 }
 
+// prompt rows [n_dec][PF_KV_ROWS][1024] fp32 (rows 0 .. gridDim.x-1) -> slots 0 .. of the fp16 rings
+__global__ void __launch_bounds__(256) kv_rows_to_half_kernel(const float *__restrict__ src_k, const float *__restrict__ src_v,
+                                                              __half *__restrict__ dst_k, __half *__restrict__ dst_v) {
+    const int row = blockIdx.x, l = blockIdx.y;
+    const size_t so = ((size_t)l * PF_KV_ROWS + row) * DEC_KVDIM, d = ((size_t)l * DEC_WINDOW + row) * DEC_KVDIM;
+    for (int i = threadIdx.x; i < DEC_KVDIM; i += 256) {
+        dst_k[d + i] = __float2half_rn(src_k[so + i]);
+        dst_v[d + i] = __float2half_rn(src_v[so + i]);
+    }
+}
+
 static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
     // a block writes all its K/V rows into the ring before its attention runs: once a row reaches logical
     // position 8191 the ring slot of the oldest key it needs has been overwritten by a later row of the block
@@ -446,7 +496,17 @@ static int prefill_device(vox_cuda_state *s, float *x_dev, int seq_len) {
                       s->h_params.pos, s->h_params.pos + seq_len, DEC_WINDOW);
         return -1;
     }
-    if (dec_prefill_into(s, x_dev, seq_len, s->kv_k, s->kv_v, (size_t)DEC_WINDOW * DEC_KVDIM, DEC_WINDOW - 1,
+    if (s->kv16) {
+        // fp32 prefill into the PF_KV_ROWS-row buffer, then the rows are rounded into the fp16 ring (api_group.cu does the same)
+        if (s->h_params.pos != 0 || seq_len > PF_KV_ROWS) {
+            vox_set_error("decoder_prefill: an fp16-K/V state prefills at most %d rows, at position 0", PF_KV_ROWS);
+            return -1;
+        }
+        if (dec_prefill_into(s, x_dev, seq_len, s->kv_k, s->kv_v, (size_t)PF_KV_ROWS * DEC_KVDIM, PF_KV_ROWS - 1,
+                             &s->h_params.pos, &s->h_params.n_valid)) return -1;
+        kv_rows_to_half_kernel<<<dim3(seq_len, s->m->n_dec), 256, 0, s->stream>>>(s->kv_k, s->kv_v, (__half *)s->kv_k16, (__half *)s->kv_v16);
+        LAUNCHED();
+    } else if (dec_prefill_into(s, x_dev, seq_len, s->kv_k, s->kv_v, (size_t)DEC_WINDOW * DEC_KVDIM, DEC_WINDOW - 1,
                          &s->h_params.pos, &s->h_params.n_valid)) return -1;
     if (push_params(s)) return -1;
     CUDA_TRY(cudaStreamSynchronize(s->stream));

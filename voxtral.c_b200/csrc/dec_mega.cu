@@ -25,6 +25,7 @@
 // Arithmetic is fp32 on exactly-widened bf16 weights, like the reference; only
 // the summation order differs.
 #include "vox_internal.h"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -111,7 +112,7 @@ struct Params {
     int n_dec;
     const uint16_t *tok_emb;
     const float *dec_norm, *ada_scale, *inv_freq;
-    float *kv_k, *kv_v;
+    void *kv_k, *kv_v;                      // rings of float or __half rows (kernel template parameter KV)
     float *x, *q, *attn_part, *h, *logits, *blockmax;
     float *attn;                            // [4096] merged, normalised attention output of the current layer
     unsigned *attn_cnt;                     // hand-over counters, SYNC_* layout (zeroed by the host before each launch)
@@ -468,7 +469,21 @@ __device__ __forceinline__ int attn_splits(int n_keys, int G) {
     return min(min(G >> 3, MAX_SPLITS), (ng + CW - 1) / CW);
 }
 
-__device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const float *kc, const float *vc,
+// K/V ring element type: float (the reference's CPU / BLAS layout, voxtral_decoder.c:703-705) or __half (the
+// reference's GPU default "fp16 KV", voxtral.c:189-190): rows are rounded once when appended and widened when read;
+// scores, softmax and the output stay fp32.
+__device__ __forceinline__ float4 ld_kv4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ float4 ld_kv4(const __half *p) {
+    const uint2 u = __ldcg(reinterpret_cast<const uint2 *>(p));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st_kv2(float *p, float a, float b) { *reinterpret_cast<float2 *>(p) = make_float2(a, b); }
+__device__ __forceinline__ void st_kv2(__half *p, float a, float b) { *reinterpret_cast<__half2 *>(p) = __floats2half2_rn(a, b); }
+
+template <typename KV>
+__device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const KV *kc, const KV *vc,
                                                 int pos, int n_keys, int c, int G, unsigned arrivals_expected,
                                                 const unsigned *qkv_ready, unsigned qkv_target) {
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
@@ -489,8 +504,8 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
         #pragma unroll
         for (int i = 0; i < 8; i++) {
             const int slot = (first + g0 * 8 + i) & (DEC_WINDOW - 1);
-            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
-            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+            kf[i] = ld_kv4(kc + (size_t)slot * DEC_KVDIM + hoff);
+            vf[i] = ld_kv4(vc + (size_t)slot * DEC_KVDIM + hoff);
         }
     }
     wait_count(qkv_ready, qkv_target, P.err, 3u);
@@ -508,8 +523,8 @@ __device__ __forceinline__ void attention_phase(Smem &sm, const Params &P, const
             #pragma unroll
             for (int i = 0; i < 8; i++) {
                 const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamp: always a valid row
-                kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
-                vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+                kf[i] = ld_kv4(kc + (size_t)slot * DEC_KVDIM + hoff);
+                vf[i] = ld_kv4(vc + (size_t)slot * DEC_KVDIM + hoff);
             }
         }
         float v[32];
@@ -664,6 +679,7 @@ __device__ __forceinline__ void norm_slice(Smem &sm, float (&xr)[DEC_DIM / 256],
     }
 }
 
+template <typename KV>
 __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
@@ -776,7 +792,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         for (int l = 0; l < n_dec; l++) {
             if (l == 10) bar_k = 0; else if (l < 10) bar_k = 100;
             const DecLayerDev L = P.layers[l];
-            float *kc = P.kv_k + l * kv_layer, *vc = P.kv_v + l * kv_layer;
+            KV *kc = reinterpret_cast<KV *>(P.kv_k) + l * kv_layer, *vc = reinterpret_cast<KV *>(P.kv_v) + l * kv_layer;
             // ---------------- phase 1: rmsnorm -> qkv -> rope -> q / KV ring ----------------
             {
                 const long long tp = clock64();
@@ -811,11 +827,9 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                             const float r0 = v0 * cs - v1 * sn, r1 = v0 * sn + v1 * cs;
                             v0 = r0; v1 = r1;
                         }
-                        float *dst;
-                        if (row < DEC_QDIM) dst = P.q + row;
-                        else if (row < DEC_QDIM + DEC_KVDIM) dst = kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM);
-                        else dst = vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM);
-                        *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
+                        if (row < DEC_QDIM) *reinterpret_cast<float2 *>(P.q + row) = make_float2(v0, v1);
+                        else if (row < DEC_QDIM + DEC_KVDIM) st_kv2(kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM), v0, v1);
+                        else st_kv2(vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM), v0, v1);
                     });
             }
             // q / k / v rows of this CTA are written: tell the attention CTAs of the kv heads they belong to
@@ -1000,9 +1014,11 @@ int dec_mega_init(vox_cuda_state *s) {
     int dev = 0, sms = 0, occ = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)sizeof(mk::Smem)));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel, mk::NT, sizeof(mk::Smem)));
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(mk::Smem)));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float>, mk::NT, sizeof(mk::Smem)));
     if (occ < 1 || sms < 8) { vox_set_error("dec_mega: kernel does not fit (occupancy %d, %d SMs)", occ, sms); return -1; }
     h->grid = sms;
     h->barriers_per_step = 3 * s->m->n_dec + 1;       // after wo, w1|w3, w2 of every layer + after the logits
@@ -1059,7 +1075,7 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     mk::Params P;
     P.layers = h->d_layers; P.n_dec = m->n_dec;
     P.tok_emb = m->tok_emb; P.dec_norm = m->dec_norm; P.ada_scale = m->ada_scale; P.inv_freq = m->inv_freq_dec;
-    P.kv_k = s->kv_k; P.kv_v = s->kv_v;
+    P.kv_k = s->kv16 ? (void *)s->kv_k16 : (void *)s->kv_k; P.kv_v = s->kv16 ? (void *)s->kv_v16 : (void *)s->kv_v;
     P.attn = s->d_attn; P.attn_cnt = h->d_bar + 8;
     P.x = s->d_x; P.q = s->d_q; P.attn_part = s->d_attn_part; P.h = s->d_h; P.logits = s->d_logits;
     P.blockmax = s->d_blockmax;
@@ -1069,7 +1085,8 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.spin_ns = h->spin_ns; P.err = h->d_err; P.prof = h->d_prof;
     CUDA_TRY(cudaMemsetAsync(h->d_bar + 8, 0, mk::SYNC_WORDS * sizeof(unsigned), s->stream));   // hand-over counters start at 0
     void *args[] = {&P};
-    CUDA_TRY(cudaLaunchCooperativeKernel((const void *)mk::dec_mega_kernel, dim3(h->grid), dim3(mk::NT), args,
+    const void *fn = s->kv16 ? (const void *)mk::dec_mega_kernel<__half> : (const void *)mk::dec_mega_kernel<float>;
+    CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(h->grid), dim3(mk::NT), args,
                                          sizeof(mk::Smem), s->stream));
     h->bar_count += (unsigned)h->grid * (unsigned)h->barriers_per_step * (unsigned)n_steps;
     LAUNCHED();

@@ -68,7 +68,12 @@ struct vox_cuda_state {
     vox_cuda_model *m;
     cudaStream_t stream;
     // ---- decoder ----
-    float *kv_k, *kv_v;          // [n_dec][DEC_WINDOW][1024] fp32 ring, slot = logical & 8191
+    float *kv_k, *kv_v;          // [n_dec][DEC_WINDOW][1024] fp32 ring, slot = logical & 8191 (kv16 == 0)
+    // kv16 == 1 (vox_cuda_state_create_ex(m, 16)): the rings are fp16 (void pointers: this header stays free of
+    // cuda_fp16.h), kv_k / kv_v shrink to [n_dec][PF_KV_ROWS][1024] fp32 rows that the prompt prefill writes before
+    // they are rounded into the ring (the arrangement of the stream groups, api_group.cu)
+    void *kv_k16, *kv_v16;
+    int kv16;
     DecStepParams *d_params;     // device
     DecStepParams h_params;      // host mirror (authoritative between calls)
     float *d_x, *d_q, *d_attn, *d_h, *d_logits, *d_embed_in, *d_rope;
@@ -98,6 +103,7 @@ struct vox_cuda_state {
     cudaEvent_t ev0, ev1;
 };
 
+constexpr int PF_KV_ROWS = 128;   // prompt rows an fp16-ring state can prefill (the prompt has 38)
 constexpr int ATTN_NSPLIT = 16;
 constexpr int TOKENS_RING = 65536;
 constexpr int LOGITS_ROWS_PER_CTA = 128;

@@ -55,6 +55,8 @@ SIGNATURES = {
     "vox_cuda_model_set_ada_scale": (C.c_int, [C.c_void_p, f32p]),
     "vox_cuda_model_free": (None, [C.c_void_p]),
     "vox_cuda_state_create": (C.c_void_p, [C.c_void_p]),
+    "vox_cuda_state_create_ex": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "vox_cuda_state_kv_bits": (C.c_int, [C.c_void_p]),
     "vox_cuda_state_free": (None, [C.c_void_p]),
     "vox_cuda_state_reset_decoder": (None, [C.c_void_p]),
     "vox_cuda_state_reset_encoder": (None, [C.c_void_p]),
