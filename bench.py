@@ -115,6 +115,7 @@ def run_cuda(args, rank, world):
     import refharness as rh
     import voxcuda as vc
     import hostmodel
+    import streams          # shard table + the SUM / MAX timing protocol (tests/test_cpu_streams.py runs it under gloo)
 
     L = vc.lib()
     if L.vox_cuda_init() != 1:
@@ -173,7 +174,7 @@ def run_cuda(args, rank, world):
     for _ in range(args.steps):
         n_tok, _ = one(True)
     barrier()
-    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    audio_e2e, t_e2e = streams.aggregate(dist, "cuda", args.clip_seconds * args.steps, time.perf_counter() - t0)
     launches = L.vox_cuda_launch_count() - launches0
 
     # ---- resident leg: PCM already in HBM, CUDA events on the launching stream ----
@@ -185,7 +186,7 @@ def run_cuda(args, rank, world):
         n_tok, ms = one(False)
         ms_sum += ms
     barrier()
-    t_res = max_over_ranks(ms_sum * 1e-3)
+    audio_res, t_res = streams.aggregate(dist, "cuda", args.clip_seconds * args.steps, ms_sum * 1e-3)
     consistent = bool(np.array_equal(toks[:n_tok], toks_e2e))
 
     # ---- the roofline kernel in isolation: the persistent decoder-step kernel ----
@@ -244,7 +245,8 @@ def run_cuda(args, rank, world):
     multi = None
     if args.streams > 0:
         S = args.streams
-        clips = [frame_buffer(synth_clip(args.clip_seconds, 100 + S * rank + i)) for i in range(S)]     # seeds 100..163 on rank 0
+        s0, s1 = streams.shard_streams(S * world, rank, world)                                  # this rank's streams of the job
+        clips = [frame_buffer(synth_clip(args.clip_seconds, 100 + i)) for i in range(s0, s1)]    # seeds 100..163 on rank 0
         T = clips[0][1] // 8
         g = vc.check(L.vox_cuda_group_create(model, S, T + 1), "group_create")
         gtoks = np.empty((S, T), np.int32)
@@ -353,12 +355,11 @@ def run_cuda(args, rank, world):
             traffic, traffic_src = tj["dram_bytes_per_token"], tj.get("commit")
         except Exception:
             pass
-        audio = args.clip_seconds * args.steps * world
         n_pos = nf // 2
         enc_tflops = ENC_FLOP_PER_POSITION * n_pos / (enc_ms * 1e-3) / 1e12
         tpeak = float(peaks.get("bf16_tflops_sustained", 1378.0))
         line = {
-            "metric": METRIC, "value": audio / t_res, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": METRIC, "value": audio_res / t_res, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (bf16 weights; encoder GEMM operands bf16x2)",
             "data": "synthetic",
@@ -369,7 +370,7 @@ def run_cuda(args, rank, world):
         if tp_res is not None:
             line["tp_decode"] = tp_res
         line.update({
-            "e2e": {"value": audio / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
+            "e2e": {"value": audio_e2e / t_e2e, "unit": UNIT, "ms_per_step": 1e3 * t_e2e / args.steps,
                     "h2d_bytes_per_step": int(buf.nbytes), "d2h_bytes_per_step": int(4 * n_tok),
                     "api": "vox_cuda_transcribe(host PCM in pinned memory) -> token ids on the host"},
             "gpu_launches": int(launches),

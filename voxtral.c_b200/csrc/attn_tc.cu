@@ -227,10 +227,345 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
 
 }  // namespace at
 
+// ======================================================================================================
+// tcgen05 version (round 2): S = Q K^T and O_tile = P V on the 5th-generation tensor cores, accumulators in TMEM.
+//
+//   CTA = 128 queries of one head, 128 threads; thread t owns query row t = TMEM lane t, so the online softmax needs
+//   no cross-lane reductions.  Key tiles of 64 keys.  Shared memory holds K-major SWIZZLE_128B operand tiles of 64 bf16
+//   columns (128-byte rows, 8-row groups 1024 B apart - the layout TMA would produce; here the tiles are written by the
+//   threads, because K / V live in the fp32 ring and are split into hi + lo bf16 terms on the way in):
+//       Q  [128 q   x 64 d]   hi, lo   (A operand of S)        K  [64 keys x 64 d]    hi, lo  (B operand of S)
+//       P  [128 q   x 64 key] hi, lo   (A operand of P V)      Vt [64 d    x 64 keys] hi, lo  (B operand of P V: V transposed)
+//   TMEM: columns 0..63 / 64..127 = two S tiles, 128..191 = O tile (fp32).  Software pipeline per key tile t: tcgen05.ld S(t);
+//   K(t+1) -> smem and S(t+1) = Q K^T (hi*hi + lo*hi + hi*lo) issued into the other S buffer; mask + online softmax of tile t in
+//   registers while it runs; wait for P V of tile t-1 (it had the whole softmax to finish), o = o * corr + O tile; P(t), Vt(t) ->
+//   smem, P V(t) issued (fresh accumulator).  K / V rows of the next tiles travel in registers.  96 KB of smem, 256 TMEM
+//   columns: two CTAs per SM.  Same arithmetic contract as enc_attn_kernel<3> (fp32-class products, fp32 softmax).
+namespace at5 {
+
+using namespace tcx;
+
+constexpr int BQ = 128, BK = 64, HD = ENC_HD, NT = 128;
+constexpr int Q_BYTES = BQ * 128, K_BYTES = BK * 128;              // one bf16 plane of a tile
+constexpr int OFF_QH = 0, OFF_QL = Q_BYTES, OFF_KH = 2 * Q_BYTES, OFF_KL = OFF_KH + K_BYTES, OFF_VH = OFF_KL + K_BYTES,
+              OFF_VL = OFF_VH + K_BYTES, OFF_PH = OFF_VL + K_BYTES, OFF_PL = OFF_PH + Q_BYTES, OFF_END = OFF_PL + Q_BYTES;
+constexpr int SMEM_BYTES = OFF_END + 1024 + 64;                    // + alignment slack + barrier / TMEM slot
+constexpr uint32_t IDESC = umma_idesc(128, 64);
+constexpr uint32_t TMEM_COLS = 256;                                // two S buffers (64 + 64) + O tile (64), power of two
+
+// byte offset of the 16-byte chunk c (8 bf16 columns) of row r inside a SWIZZLE_128B K-major plane
+__device__ __forceinline__ uint32_t sw_off(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+__device__ __forceinline__ uint32_t pk(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+__device__ __forceinline__ void split_pk(float a, float b, uint32_t &hi, uint32_t &lo) {
+    hi = pk(a, b);
+    lo = pk(a - bf16_lo(hi), b - bf16_hi(hi));
+}
+// 8 consecutive floats -> one 16-byte chunk of the hi plane and one of the lo plane
+__device__ __forceinline__ void store_chunk(unsigned char *ph, unsigned char *pl, int r, int c, const float4 &a, const float4 &b, float scale) {
+    uint4 h, l;
+    split_pk(a.x * scale, a.y * scale, h.x, l.x); split_pk(a.z * scale, a.w * scale, h.y, l.y);
+    split_pk(b.x * scale, b.y * scale, h.z, l.z); split_pk(b.z * scale, b.w * scale, h.w, l.w);
+    *reinterpret_cast<uint4 *>(ph + sw_off(r, c)) = h;
+    *reinterpret_cast<uint4 *>(pl + sw_off(r, c)) = l;
+}
+
+// K tile: thread t stages dims (t & 1) * 32 .. +31 of key (t >> 1): two threads read one 256-byte row (coalesced).
+// Load and store are separate so that the loads of tile t+1 are in flight while tile t is worked on.
+__device__ __forceinline__ void load_k(float4 (&v)[8], const float *__restrict__ kc, int head, int kt, int gmax, int ring_mask) {
+    const int key = threadIdx.x >> 1, half = threadIdx.x & 1, j = kt + key;
+    if (j <= gmax) {
+        const float4 *src = reinterpret_cast<const float4 *>(kc + (size_t)(j & ring_mask) * ENC_QKV + head * HD + half * 32);
+        #pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
+    } else {
+        #pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+__device__ __forceinline__ void store_k(unsigned char *kh, unsigned char *kl, const float4 (&v)[8]) {
+    const int key = threadIdx.x >> 1, half = threadIdx.x & 1;
+    #pragma unroll
+    for (int c = 0; c < 4; c++) store_chunk(kh, kl, key, half * 4 + c, v[2 * c], v[2 * c + 1], 1.0f);
+}
+
+// V tile, transposed: thread t owns keys 2 * (t >> 2), +1 and dims i * 16 + (t & 3) * 4 .. +3 (i < 4); it writes, for each of its
+// 16 dims, one 4-byte word = that dim of its two keys into row (dim) of Vt
+__device__ __forceinline__ void load_v(float4 (&a)[4], float4 (&b)[4], const float *__restrict__ vc, int head, int kt, int gmax, int ring_mask) {
+    const int kp = threadIdx.x >> 2, q4 = threadIdx.x & 3;
+    const int j0 = kt + 2 * kp, j1 = j0 + 1;
+    #pragma unroll
+    for (int i = 0; i < 4; i++) {
+        a[i] = (j0 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j0 & ring_mask) * ENC_QKV + head * HD + i * 16 + q4 * 4))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+        b[i] = (j1 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j1 & ring_mask) * ENC_QKV + head * HD + i * 16 + q4 * 4))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+__device__ __forceinline__ void store_vt(unsigned char *vh, unsigned char *vl, const float4 (&a)[4], const float4 (&b)[4]) {
+    const int kp = threadIdx.x >> 2, q4 = threadIdx.x & 3;
+    const int col = 2 * kp;                                        // key column of the pair inside the 64-key row
+    #pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w}, bv[4] = {b[i].x, b[i].y, b[i].z, b[i].w};
+        #pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int d = i * 16 + q4 * 4 + e;
+            uint32_t h, l;
+            split_pk(av[e], bv[e], h, l);
+            const uint32_t off = sw_off(d, col >> 3) + (uint32_t)((col & 7) * 2);
+            *reinterpret_cast<uint32_t *>(vh + off) = h;
+            *reinterpret_cast<uint32_t *>(vl + off) = l;
+        }
+    }
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int TERMS>
+__global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
+    const float *__restrict__ qkv, long ldq, const float *__restrict__ kc, const float *__restrict__ vc,
+    int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split,
+    const int *__restrict__ pos_dev) {
+    extern __shared__ unsigned char smraw[];
+    unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)smraw + 1023) & ~(uintptr_t)1023);   // swizzle atoms are 1024-byte aligned
+    uint64_t *bar_s = reinterpret_cast<uint64_t *>(sm + OFF_END), *bar_o = bar_s + 1;      // S products done / P V products done
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sm + OFF_END + 16);
+    pdl_launch_dependents();
+    pdl_wait();
+    if (pos_dev) { pos0 = pos_dev[0]; first_valid = pos_dev[1]; }
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int head = blockIdx.y, q0 = blockIdx.x * BQ;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "n"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        mb_init(bar_s, 1);
+        mb_init(bar_o, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // Q tile: thread t = query row t, pre-scaled by 1/sqrt(64) (an exact power of two)
+    {
+        const int row = q0 + tid;
+        float4 v[16];
+        if (row < M) {
+            const float4 *src = reinterpret_cast<const float4 *>(qkv + (size_t)row * ldq + head * HD);
+            #pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = __ldg(src + i);
+        } else {
+            #pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        #pragma unroll
+        for (int c = 0; c < 8; c++) store_chunk(sm + OFF_QH, sm + OFF_QL, tid, c, v[2 * c], v[2 * c + 1], 0.125f);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16), t_o = t_s + 128;     // this warp's 32 lanes: S buffers at columns 0 / 64, O at 128
+
+    const int gq = pos0 + q0 + tid;                                                  // logical position of this thread's query
+    const int gmin = pos0 + q0, gmax = pos0 + min(q0 + BQ - 1, M - 1);
+    int k_lo = gmin - (window - 1);
+    if (k_lo < first_valid) k_lo = first_valid;
+
+    float o[HD];
+    #pragma unroll
+    for (int i = 0; i < HD; i++) o[i] = 0.f;
+    float m = -INFINITY, l = 0.f;
+    const uint32_t a_q[2] = {s32(sm + OFF_QH), s32(sm + OFF_QL)}, a_k[2] = {s32(sm + OFF_KH), s32(sm + OFF_KL)};
+    const uint32_t a_p[2] = {s32(sm + OFF_PH), s32(sm + OFF_PL)}, a_v[2] = {s32(sm + OFF_VH), s32(sm + OFF_VL)};
+    constexpr float LOG2E = 1.4426950408889634f;
+
+    // S = Q K^T of one key tile into S buffer `buf` (TMEM columns buf * 64 ..): hi*hi, lo*hi, hi*lo
+    auto issue_s = [&](int buf) {
+        tc_fence_after();
+        #pragma unroll
+        for (int term = 0; term < (TERMS > 1 ? 3 : 1); term++) {
+            const uint64_t da = umma_desc(a_q[term == 1 ? 1 : 0]), db = umma_desc(a_k[term == 2 ? 1 : 0]);
+            #pragma unroll
+            for (int k = 0; k < HD / 16; k++)
+                umma_f16(tmem + (uint32_t)(buf * 64), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (term | k) ? 1u : 0u);
+        }
+        umma_commit(bar_s);
+    };
+
+    // Software pipeline over the key tiles: while the threads do the softmax of tile t, the tensor core computes S of tile
+    // t+1 (second S buffer) and finishes P V of tile t-1; the K / V rows of the next tile travel in registers.
+    float4 kreg[8], va[4], vb[4];
+    load_k(kreg, kc, head, k_lo, gmax, ring_mask);
+    load_v(va, vb, vc, head, k_lo, gmax, ring_mask);
+    store_k(sm + OFF_KH, sm + OFF_KL, kreg);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy stores -> visible to the tensor core's reads
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) issue_s(0);
+    if (k_lo + BK <= gmax) load_k(kreg, kc, head, k_lo + BK, gmax, ring_mask);
+
+    unsigned ph_s = 0, ph_o = 0;
+    float corr_prev = 0.f;
+    int buf = 0;
+    for (int kt = k_lo; kt <= gmax; kt += BK, buf ^= 1) {
+        const bool has_next = kt + BK <= gmax, first = kt == k_lo;
+        // ---- S row of this tile -> registers ----
+        mb_wait(bar_s, ph_s); ph_s ^= 1u;
+        tc_fence_after();
+        uint32_t sr[2][32];
+        tmem_ld32(t_s + (uint32_t)(buf * 64), sr[0]);
+        tmem_ld32(t_s + (uint32_t)(buf * 64) + 32, sr[1]);
+        // ---- next K tile -> smem (S of this tile has retired, so the K planes are free), S(t+1) starts now ----
+        if (has_next) {
+            store_k(sm + OFF_KH, sm + OFF_KL, kreg);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        tc_fence_before();
+        __syncthreads();
+        if (has_next && tid == 0) issue_s(buf ^ 1);
+        // ---- mask (boundary tiles only) + online softmax in registers ----
+        const bool interior = kt + BK - 1 <= gmin && kt > gmax - window && kt >= first_valid;    // uniform over the CTA
+        float mx = -INFINITY;
+        if (interior) {
+            #pragma unroll
+            for (int i = 0; i < BK; i++) mx = fmaxf(mx, __uint_as_float(sr[i >> 5][i & 31]));
+        } else {
+            #pragma unroll
+            for (int i = 0; i < BK; i++) {
+                const int jk = kt + i;
+                const bool ok = jk <= gq && jk > gq - window && jk >= first_valid;
+                const float v = ok ? __uint_as_float(sr[i >> 5][i & 31]) : -INFINITY;
+                sr[i >> 5][i & 31] = __float_as_uint(v);
+                mx = fmaxf(mx, v);
+            }
+        }
+        const float mn = fmaxf(m, mx);
+        const float mu = (mn == -INFINITY) ? 0.f : mn;
+        const float corr = (m == -INFINITY) ? 0.f : ex2((m - mu) * LOG2E);
+        const float mu2 = mu * LOG2E;
+        m = mn;
+        float ps = 0.f;
+        #pragma unroll
+        for (int i = 0; i < BK; i++) {
+            const float pv = ex2(fmaf(__uint_as_float(sr[i >> 5][i & 31]), LOG2E, -mu2));    // 2^-inf = 0 for masked keys
+            sr[i >> 5][i & 31] = __float_as_uint(pv);
+            ps += pv;
+        }
+        l = l * corr + ps;
+        // ---- P V of the previous tile has had the whole softmax to finish: o = o * corr + O tile ----
+        if (!first) {
+            mb_wait(bar_o, ph_o); ph_o ^= 1u;
+            tc_fence_after();
+            #pragma unroll
+            for (int hlf = 0; hlf < 2; hlf++) {
+                uint32_t r[32];
+                tmem_ld32(t_o + hlf * 32, r);
+                #pragma unroll
+                for (int i = 0; i < 32; i++) o[hlf * 32 + i] = fmaf(o[hlf * 32 + i], corr_prev, __uint_as_float(r[i]));
+            }
+        }
+        corr_prev = corr;
+        // ---- P and the transposed V tile -> smem (their planes are free: P V of the previous tile has retired) ----
+        #pragma unroll
+        for (int c = 0; c < BK / 8; c++) {
+            uint4 h, lo4;
+            #define PV_(e) __uint_as_float(sr[(c * 8 + (e)) >> 5][(c * 8 + (e)) & 31])
+            split_pk(PV_(0), PV_(1), h.x, lo4.x); split_pk(PV_(2), PV_(3), h.y, lo4.y);
+            split_pk(PV_(4), PV_(5), h.z, lo4.z); split_pk(PV_(6), PV_(7), h.w, lo4.w);
+            #undef PV_
+            *reinterpret_cast<uint4 *>(sm + OFF_PH + sw_off(tid, c)) = h;
+            if (TERMS > 1) *reinterpret_cast<uint4 *>(sm + OFF_PL + sw_off(tid, c)) = lo4;
+        }
+        store_vt(sm + OFF_VH, sm + OFF_VL, va, vb);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            #pragma unroll
+            for (int term = 0; term < (TERMS > 1 ? 3 : 1); term++) {
+                const uint64_t da = umma_desc(a_p[term == 1 ? 1 : 0]), db = umma_desc(a_v[term == 2 ? 1 : 0]);
+                #pragma unroll
+                for (int k = 0; k < BK / 16; k++) umma_f16(tmem + 128, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (term | k) ? 1u : 0u);
+            }
+            umma_commit(bar_o);
+        }
+        // ---- rows of the tiles after next: in flight during the next iteration ----
+        if (has_next) {
+            load_v(va, vb, vc, head, kt + BK, gmax, ring_mask);
+            if (kt + 2 * BK <= gmax) load_k(kreg, kc, head, kt + 2 * BK, gmax, ring_mask);
+        }
+    }
+    {   // last tile's P V
+        mb_wait(bar_o, ph_o);
+        tc_fence_after();
+        #pragma unroll
+        for (int hlf = 0; hlf < 2; hlf++) {
+            uint32_t r[32];
+            tmem_ld32(t_o + hlf * 32, r);
+            #pragma unroll
+            for (int i = 0; i < 32; i++) o[hlf * 32 + i] = fmaf(o[hlf * 32 + i], corr_prev, __uint_as_float(r[i]));
+        }
+    }
+    // ---- normalise, split, store this thread's row ----
+    const int row = q0 + tid;
+    if (row < M) {
+        const float inv = l > 0.f ? 1.0f / l : 0.f;
+        uint16_t *oh = out + (size_t)row * ldo + head * HD;
+        #pragma unroll
+        for (int c = 0; c < HD / 8; c++) {
+            uint4 h, lo4;
+            split_pk(o[8 * c] * inv, o[8 * c + 1] * inv, h.x, lo4.x); split_pk(o[8 * c + 2] * inv, o[8 * c + 3] * inv, h.y, lo4.y);
+            split_pk(o[8 * c + 4] * inv, o[8 * c + 5] * inv, h.z, lo4.z); split_pk(o[8 * c + 6] * inv, o[8 * c + 7] * inv, h.w, lo4.w);
+            *reinterpret_cast<uint4 *>(oh + 8 * c) = h;
+            if (split) *reinterpret_cast<uint4 *>(oh + ENC_QKV + 8 * c) = lo4;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS));
+    }
+}
+
+}  // namespace at5
+// 0: tcgen05 kernel (default), 1: the mma.sync kernel (VOX_CUDA_ENC_ATTN_MMA=1, kept as the cross-check)
+static int attn_mma_mode(void) {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("VOX_CUDA_ENC_ATTN_MMA");
+        v = (e && atoi(e)) ? 1 : 0;
+        cudaFuncSetAttribute(at5::enc_attn_tc5_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, at5::SMEM_BYTES);
+        cudaFuncSetAttribute(at5::enc_attn_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, at5::SMEM_BYTES);
+        cudaFuncSetAttribute(at::enc_attn_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM_BYTES);
+        cudaFuncSetAttribute(at::enc_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM_BYTES);
+    }
+    return v;
+}
+
 static int enc_attention_launch(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                                 uint16_t *out_b, long ldo, int split, int terms, const int *pos_dev) {
     EncState *e = (EncState *)s->enc_priv;
     cudaStream_t st = s->stream;
+    if (!attn_mma_mode()) {
+        dim3 grid((M + at5::BQ - 1) / at5::BQ, ENC_HEADS);
+        if (terms == 3)
+            CUDA_TRY(launch_pdl(at5::enc_attn_tc5_kernel<3>, grid, at5::NT, at5::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min,
+                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev));
+        else
+            CUDA_TRY(launch_pdl(at5::enc_attn_tc5_kernel<1>, grid, at5::NT, at5::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min,
+                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev));
+        LAUNCHED();
+        return 0;
+    }
     dim3 grid((M + at::BQ - 1) / at::BQ, ENC_HEADS);
     if (terms == 3)
         CUDA_TRY(launch_pdl(at::enc_attn_kernel<3>, grid, at::NT, at::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min, ENC_WINDOW,
