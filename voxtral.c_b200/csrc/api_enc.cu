@@ -58,7 +58,7 @@ void enc_state_free(vox_cuda_state *s) {
     enc_fast_free(s);
     enc_small_free(e->small);
     void *ptrs[] = {e->kv_k, e->kv_v, e->mel_in, e->c0, e->x, e->xn, e->qkv, e->att, e->gu, e->hh, e->encout, e->mid,
-                    e->mel_hi, e->mel_lo, e->c0_hi, e->c0_lo};
+                    e->mel_hi, e->mel_lo, e->c0_hi, e->c0_lo, e->attn_part, e->attn_cnt};
     for (void *p : ptrs) if (p) cudaFree(p);
     vox_mem_account(-(long)(2 * e->kv_bytes));
     if (e->h_stage) cudaFreeHost(e->h_stage);

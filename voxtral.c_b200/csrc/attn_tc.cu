@@ -332,7 +332,11 @@ template <int TERMS>
 __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     const float *__restrict__ qkv, long ldq, const float *__restrict__ kc, const float *__restrict__ vc,
     int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split,
-    const int *__restrict__ pos_dev) {
+    const int *__restrict__ pos_dev, float *__restrict__ part, unsigned *__restrict__ cnt, int n_splits) {
+    // n_splits == 0: blockIdx.x = tile of 128 queries, the CTA walks all its key tiles.
+    // n_splits  > 0 (streaming chunks, M <= 128: ONE query tile against a full window would be 32 CTAs walking 13 key tiles
+    // one after the other): blockIdx.x = key split; every CTA takes its share of the key tiles and leaves an unnormalised
+    // partial (o, m, l) in `part`; the CTA that arrives last for a head (cnt[head]) merges the partials and writes the rows.
     extern __shared__ unsigned char smraw[];
     unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)smraw + 1023) & ~(uintptr_t)1023);   // swizzle atoms are 1024-byte aligned
     uint64_t *bar_s = reinterpret_cast<uint64_t *>(sm + OFF_END), *bar_o = bar_s + 1;      // S products done / P V products done
@@ -341,7 +345,20 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     pdl_wait();
     if (pos_dev) { pos0 = pos_dev[0]; first_valid = pos_dev[1]; }
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int head = blockIdx.y, q0 = blockIdx.x * BQ;
+    const int head = blockIdx.y, q0 = n_splits ? 0 : blockIdx.x * BQ;
+    const int gq = pos0 + q0 + tid;                                                  // logical position of this thread's query
+    const int gmin = pos0 + q0, gmax = pos0 + min(q0 + BQ - 1, M - 1);
+    int k_lo = gmin - (window - 1);
+    if (k_lo < first_valid) k_lo = first_valid;
+    int k_end = gmax, n_active = 1;                                                  // last key of this CTA's share; splits that have keys
+    if (n_splits) {
+        const int n_tiles = (gmax - k_lo) / BK + 1, tps = (n_tiles + n_splits - 1) / n_splits;
+        const int t0 = blockIdx.x * tps;
+        if (t0 >= n_tiles) return;                                                   // whole CTA: this split has no keys (it does not arrive either)
+        n_active = (n_tiles + tps - 1) / tps;
+        k_end = min(gmax, k_lo + (t0 + tps) * BK - 1);
+        k_lo += t0 * BK;
+    }
 
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(tmem_slot)), "n"(TMEM_COLS));
@@ -372,11 +389,6 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16), t_o = t_s + 128;     // this warp's 32 lanes: S buffers at columns 0 / 64, O at 128
-
-    const int gq = pos0 + q0 + tid;                                                  // logical position of this thread's query
-    const int gmin = pos0 + q0, gmax = pos0 + min(q0 + BQ - 1, M - 1);
-    int k_lo = gmin - (window - 1);
-    if (k_lo < first_valid) k_lo = first_valid;
 
     float o[HD];
     #pragma unroll
@@ -409,13 +421,13 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     tc_fence_before();
     __syncthreads();
     if (tid == 0) issue_s(0);
-    if (k_lo + BK <= gmax) load_k(kreg, kc, head, k_lo + BK, gmax, ring_mask);
+    if (k_lo + BK <= k_end) load_k(kreg, kc, head, k_lo + BK, gmax, ring_mask);
 
     unsigned ph_s = 0, ph_o = 0;
     float corr_prev = 0.f;
     int buf = 0;
-    for (int kt = k_lo; kt <= gmax; kt += BK, buf ^= 1) {
-        const bool has_next = kt + BK <= gmax, first = kt == k_lo;
+    for (int kt = k_lo; kt <= k_end; kt += BK, buf ^= 1) {
+        const bool has_next = kt + BK <= k_end, first = kt == k_lo;
         // ---- S row of this tile -> registers ----
         mb_wait(bar_s, ph_s); ph_s ^= 1u;
         tc_fence_after();
@@ -500,7 +512,7 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
         // ---- rows of the tiles after next: in flight during the next iteration ----
         if (has_next) {
             load_v(va, vb, vc, head, kt + BK, gmax, ring_mask);
-            if (kt + 2 * BK <= gmax) load_k(kreg, kc, head, kt + 2 * BK, gmax, ring_mask);
+            if (kt + 2 * BK <= k_end) load_k(kreg, kc, head, kt + 2 * BK, gmax, ring_mask);
         }
     }
     {   // last tile's P V
@@ -514,9 +526,47 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
             for (int i = 0; i < 32; i++) o[hlf * 32 + i] = fmaf(o[hlf * 32 + i], corr_prev, __uint_as_float(r[i]));
         }
     }
-    // ---- normalise, split, store this thread's row ----
     const int row = q0 + tid;
-    if (row < M) {
+    if (n_splits && n_active > 1) {
+        // ---- key-split mode: leave the partial, the last CTA of this head merges ----
+        constexpr int PL = HD + 2;                                                   // o[64], m, l - stored [item][row]: coalesced over threads
+        float *mine = part + ((size_t)head * n_splits + blockIdx.x) * PL * BQ;
+        if (row < M) {
+            #pragma unroll
+            for (int i = 0; i < HD; i++) mine[i * BQ + tid] = o[i];
+            mine[HD * BQ + tid] = m;
+            mine[(HD + 1) * BQ + tid] = l;
+        }
+        __threadfence();
+        __syncthreads();
+        int *s_last = reinterpret_cast<int *>(sm + OFF_END + 32);
+        if (tid == 0) {
+            const unsigned old = atomicAdd(cnt + head, 1u);
+            *s_last = (old + 1u == (unsigned)n_active) ? 1 : 0;
+            if (*s_last) cnt[head] = 0u;                                             // clean for the next launch
+        }
+        __syncthreads();
+        if (*s_last && row < M) {
+            __threadfence();
+            const float *base = part + (size_t)head * n_splits * PL * BQ;
+            float mm = -INFINITY;
+            for (int sp = 0; sp < n_active; sp++) mm = fmaxf(mm, __ldcg(base + (size_t)sp * PL * BQ + HD * BQ + tid));
+            #pragma unroll
+            for (int i = 0; i < HD; i++) o[i] = 0.f;
+            l = 0.f;
+            for (int sp = 0; sp < n_active; sp++) {
+                const float *ps_ = base + (size_t)sp * PL * BQ;
+                const float ms = __ldcg(ps_ + HD * BQ + tid);
+                const float e = (ms == -INFINITY) ? 0.f : ex2((ms - mm) * LOG2E);
+                l = fmaf(e, __ldcg(ps_ + (HD + 1) * BQ + tid), l);
+                #pragma unroll
+                for (int i = 0; i < HD; i++) o[i] = fmaf(e, __ldcg(ps_ + i * BQ + tid), o[i]);
+            }
+        }
+        if (!*s_last) l = -1.f;                                                      // not the merger: nothing to store
+    }
+    // ---- normalise, split, store this thread's row ----
+    if (row < M && l >= 0.f) {
         const float inv = l > 0.f ? 1.0f / l : 0.f;
         uint16_t *oh = out + (size_t)row * ldo + head * HD;
         #pragma unroll
@@ -551,18 +601,38 @@ static int attn_mma_mode(void) {
     return v;
 }
 
+// VOX_CUDA_ENC_ATTN_KSPLIT=0: streaming chunks walk their key tiles in one CTA per head (A/B runs)
+static int attn_ksplit_mode(void) {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("VOX_CUDA_ENC_ATTN_KSPLIT"); v = (e && !atoi(e)) ? 0 : 1; }
+    return v;
+}
+
 static int enc_attention_launch(vox_cuda_state *s, const float *qkv, const float *kc, const float *vc, int M, int pos0,
                                 uint16_t *out_b, long ldo, int split, int terms, const int *pos_dev) {
     EncState *e = (EncState *)s->enc_priv;
     cudaStream_t st = s->stream;
     if (!attn_mma_mode()) {
-        dim3 grid((M + at5::BQ - 1) / at5::BQ, ENC_HEADS);
+        // one query tile (streaming chunks): split the keys over CTAs instead of walking them in one
+        int n_splits = 0;
+        if (M <= at5::BQ && attn_ksplit_mode()) {
+            if (!e->attn_part) {                  // first use (never under graph capture: a chunk shape runs eagerly first)
+                const size_t pb = (size_t)ENC_HEADS * ATTN_KSPLITS * (ENC_HD + 2) * at5::BQ * sizeof(float);
+                if (cudaMalloc((void **)&e->attn_part, pb) != cudaSuccess || cudaMalloc((void **)&e->attn_cnt, ENC_HEADS * sizeof(unsigned)) != cudaSuccess ||
+                    cudaMemset(e->attn_cnt, 0, ENC_HEADS * sizeof(unsigned)) != cudaSuccess) {
+                    vox_set_error("enc_attention: key-split scratch alloc failed");
+                    return -1;
+                }
+            }
+            n_splits = ATTN_KSPLITS;
+        }
+        dim3 grid(n_splits ? n_splits : (M + at5::BQ - 1) / at5::BQ, ENC_HEADS);
         if (terms == 3)
             CUDA_TRY(launch_pdl(at5::enc_attn_tc5_kernel<3>, grid, at5::NT, at5::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min,
-                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev));
+                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev, e->attn_part, e->attn_cnt, n_splits));
         else
             CUDA_TRY(launch_pdl(at5::enc_attn_tc5_kernel<1>, grid, at5::NT, at5::SMEM_BYTES, st, qkv, 3L * ENC_QKV, kc, vc, M, pos0, e->pos_min,
-                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev));
+                                ENC_WINDOW, ENC_RING - 1, out_b, ldo, split, pos_dev, e->attn_part, e->attn_cnt, n_splits));
         LAUNCHED();
         return 0;
     }

@@ -5,6 +5,7 @@
 constexpr int ENC_CHUNK = 3328;    // max encoder positions per internal pass (26 row tiles: a 60 s clip = 3196 positions is ONE pass,
                                    // so its N = 1280 products are 125 tiles in one wave instead of 80 + 45 in two)
 constexpr int ENC_MAXMEL = 6656;   // max mel frames per internal pass (= 2 * ENC_CHUNK)
+constexpr int ATTN_KSPLITS = 14;   // key splits of the streaming attention: ceil((750 + 128) / 64) tiles, one per CTA
 constexpr int ENC_RING = 4096;     // KV ring slots (>= ENC_CHUNK + ENC_WINDOW - 1 = 4077), power of two
 static_assert(ENC_RING >= ENC_CHUNK + 750 - 1 && ENC_MAXMEL == 2 * ENC_CHUNK, "encoder pass limits");
 
@@ -29,6 +30,8 @@ struct EncState {
     float *h_stage;            // pinned host staging
     void *fast;                // EncFast*, enc_fast.cu
     void *small;               // EncSmall*, enc_fast.cu (M <= 128 streaming path)
+    float *attn_part;          // key-split attention partials [32 heads][ATTN_KSPLITS][66][128] (attn_tc.cu, M <= 128), lazily
+    unsigned *attn_cnt;        // [32] arrival counters of the key splits (self-resetting)
     uint16_t *mel_hi, *mel_lo; // bf16 planes of mel_in (tensor-core conv stem)
     uint16_t *c0_hi, *c0_lo;   // bf16 planes of c0
 };
