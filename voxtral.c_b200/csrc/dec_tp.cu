@@ -51,21 +51,73 @@ __device__ __forceinline__ void tp_ll_settle4(const TpDev &td, const uint2 *src,
     }
 }
 
+// Cluster gather (round 2, opt-in): with every CTA polling all G x 24 KB of exchange words the read volume grows with
+// G while the GEMV shrinks (8 GPUs measured SLOWER than 4) - the hypothesis this tests; see tp_cluster_size for the result.  Launched as clusters of TP_CS CTAs, each CTA polls and sums
+// only 1 / TP_CS of the row (G x 6 KB), stores its quarter into the shared memory of every cluster member (DSMEM), and
+// one cluster barrier later every CTA has the whole reduced row.  Same summation order (rank order) as the plain path.
+constexpr int TP_CS = 4;
+__device__ __forceinline__ unsigned tp_cluster_rank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void tp_st_cluster(float4 *local_slot, unsigned cta, float4 v) {
+    unsigned la = (unsigned)__cvta_generic_to_shared(local_slot), ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(cta));
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(ra), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void tp_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 template <bool REDUCE>
 __device__ __forceinline__ void tp_load_x_norm(float4 *xA, float4 *xB, float *red, const TpDev &td, int a_idx,
                                                const float *__restrict__ x_in, float *__restrict__ x_out,
-                                               const float *__restrict__ nw, const float *__restrict__ ada) {
+                                               const float *__restrict__ nw, const float *__restrict__ ada,
+                                               float4 *xs = nullptr /* [768] shared: cluster gather */) {
     constexpr int NP = DEC_DIM / 4 / TP_THREADS;       // 3 pieces per thread
     const int t = threadIdx.x;
     float4 x[NP], wn[NP], wd[NP];
+    const bool clustered = REDUCE && xs != nullptr;
     #pragma unroll
     for (int i = 0; i < NP; i++) {
         const int hc = t + i * TP_THREADS;
-        x[i] = *reinterpret_cast<const float4 *>(x_in + hc * 4);
+        if (!clustered) x[i] = *reinterpret_cast<const float4 *>(x_in + hc * 4);
         wn[i] = *reinterpret_cast<const float4 *>(nw + hc * 4);
         if (ada) wd[i] = *reinterpret_cast<const float4 *>(ada + hc * 4);
     }
-    if (REDUCE) {
+    if (clustered) {
+        constexpr int PPC = DEC_DIM / 4 / TP_CS;          // 192 pieces of 4 floats per cluster member
+        const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
+        if (t < PPC) {
+            const int hc = (int)tp_cluster_rank() * PPC + t;
+            float4 xv = *reinterpret_cast<const float4 *>(x_in + hc * 4);
+            uint4 v[TP_MAX][2];
+            #pragma unroll
+            for (int pp = 0; pp < TP_MAX; pp++)
+                if (pp < td.world) {
+                    const uint2 *src = td.self->part[a_idx & 1][pp] + hc * 4;
+                    v[pp][0] = ld_ll2(src); v[pp][1] = ld_ll2(src + 2);
+                }
+            #pragma unroll
+            for (int pp = 0; pp < TP_MAX; pp++)
+                if (pp < td.world) {
+                    tp_ll_settle4(td, td.self->part[a_idx & 1][pp] + hc * 4, pp, seq, v[pp]);
+                    xv.x += __uint_as_float(v[pp][0].x); xv.y += __uint_as_float(v[pp][0].z);
+                    xv.z += __uint_as_float(v[pp][1].x); xv.w += __uint_as_float(v[pp][1].z);
+                }
+            #pragma unroll
+            for (unsigned c = 0; c < (unsigned)TP_CS; c++) tp_st_cluster(xs + hc, c, xv);
+        }
+        tp_cluster_sync();
+        #pragma unroll
+        for (int i = 0; i < NP; i++) x[i] = xs[t + i * TP_THREADS];
+        if (blockIdx.x == 0 && x_out) {
+            #pragma unroll
+            for (int i = 0; i < NP; i++) *reinterpret_cast<float4 *>(x_out + (t + i * TP_THREADS) * 4) = x[i];
+        }
+    } else if (REDUCE) {
         const unsigned seq = *td.epoch * (unsigned)td.ars + (unsigned)a_idx + 1u;
         for (int p0 = 0; p0 < td.world; p0 += 4) {
             uint4 v[NP][4][2];
@@ -123,8 +175,9 @@ template <bool REDUCE>
 __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     TpDev td, int a_idx, const DecStepParams *__restrict__ p, const float *__restrict__ x_in,
     float *__restrict__ x_out, const float *__restrict__ attn_norm, const uint16_t *__restrict__ wqkv,
-    const float *__restrict__ rope, float *__restrict__ q_out, float *__restrict__ kc, float *__restrict__ vc) {
+    const float *__restrict__ rope, float *__restrict__ q_out, float *__restrict__ kc, float *__restrict__ vc, int cs) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
+    __shared__ float4 xs[DEC_DIM / 4];               // cluster gather buffer (cs > 1)
     __shared__ float red[TP_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = DEC_QDIM / td.world, nk = DEC_KVDIM / td.world;
@@ -140,7 +193,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, wqkv + (size_t)grow_of(b) * DEC_DIM, DEC_DIM, DEC_DIM);
     if (!REDUCE) tcx::pdl_wait();        // layer 0: x comes from the embed kernel; else see "PDL ordering" above
     tcx::pdl_launch_dependents();
-    tp_load_x_norm<REDUCE>(xA, xB, red, td, a_idx, x_in, x_out, attn_norm, nullptr);
+    tp_load_x_norm<REDUCE>(xA, xB, red, td, a_idx, x_in, x_out, attn_norm, nullptr, cs > 1 ? xs : nullptr);
     const int slot = p->pos & (DEC_WINDOW - 1);
     while (b < nbatch) {
         float acc[FULL_NW];
@@ -230,8 +283,9 @@ __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
 __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
     TpDev td, int a_idx, const float *__restrict__ x_in, float *__restrict__ x_out,
     const float *__restrict__ ffn_norm, const float *__restrict__ ada, const uint16_t *__restrict__ w13,
-    float *__restrict__ h) {
+    float *__restrict__ h, int cs) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
+    __shared__ float4 xs[DEC_DIM / 4];
     __shared__ float red[TP_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nrows = 2 * DEC_HIDDEN / td.world, row_base = td.rank * nrows;
@@ -240,7 +294,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
     uint4 w[FULL_NW][FULL_NCH];
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, w13 + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
     tcx::pdl_launch_dependents();        // no PDL wait: the exchange words are the dependency ("PDL ordering" above)
-    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, x_out, ffn_norm, ada);
+    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, x_out, ffn_norm, ada, cs > 1 ? xs : nullptr);
     while (b < nbatch) {
         float acc[FULL_NW];
         tp_wdot<FULL_NW, FULL_NCH>(w, xA, xB, DEC_DIM, acc);
@@ -256,8 +310,9 @@ __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
     TpDev td, int a_idx, const float *__restrict__ x_in, const float *__restrict__ norm,
-    const uint16_t *__restrict__ tok_emb, float *__restrict__ logits, float *__restrict__ blockmax) {
+    const uint16_t *__restrict__ tok_emb, float *__restrict__ logits, float *__restrict__ blockmax, int cs) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
+    __shared__ float4 xs[DEC_DIM / 4];
     __shared__ float red[TP_WARPS];
     __shared__ float bvs[TP_WARPS];
     __shared__ int bis[TP_WARPS];
@@ -268,7 +323,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
     uint4 w[FULL_NW][FULL_NCH];
     if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, tok_emb + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
     tcx::pdl_launch_dependents();        // no PDL wait: the exchange words are the dependency
-    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, nullptr, norm, nullptr);
+    tp_load_x_norm<true>(xA, xB, red, td, a_idx, x_in, nullptr, norm, nullptr, cs > 1 ? xs : nullptr);
     float bv = -INFINITY; int bi = 0x7fffffff;
     while (b < nbatch) {
         float acc[FULL_NW];
@@ -552,6 +607,30 @@ static cudaError_t tp_partial(cudaStream_t st, const TpDev &td, int a_idx, const
     return tp_launch_partial<8, 5>(st, td, a_idx, v, W, K);
 }
 
+// PDL launch of an exchange consumer, as clusters of TP_CS CTAs when the cluster gather is on (cs > 1)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl_cs(void (*kernel)(KArgs...), int grid, int cs, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TP_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = (unsigned)cs; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = cs > 1 ? 2 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+// cluster gather: OFF by default - measured on 8 GPUs it is slower (1.002 vs 0.942 ms per token, profiles/r02_tp8.md): the
+// exchange read volume is not what limits 8 GPUs, and the cluster barrier + DSMEM hop add latency to each of the 53
+// exchanges.  VOX_CUDA_TP_CLUSTER=1 turns it on for every world > 1 (parity-tested in lock step); grids are rounded down
+// to a multiple of TP_CS
+static int tp_cluster_size(int world, int grid) {
+    static int mode = -2;
+    if (mode == -2) { const char *e = getenv("VOX_CUDA_TP_CLUSTER"); mode = e ? (atoi(e) ? 1 : 0) : -1; }
+    const bool on = mode == 1 && world > 1;
+    return (on && grid >= TP_CS) ? TP_CS : 1;
+}
+
 static int tp_grid_cap(void) {
     static int cap = 0;
     if (!cap) { const char *e = getenv("VOX_CUDA_TP_GRID"); cap = e && atoi(e) > 0 ? atoi(e) : 148; }
@@ -580,10 +659,14 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
             const DecStepParams *pp = R.d_params;
             if (l == 0)
                 CUDA_TRY(launch_pdl(tp_qkv_kernel<false>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
-                                    (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc));
-            else
-                CUDA_TRY(launch_pdl(tp_qkv_kernel<true>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
-                                    R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc));
+                                    (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, 1));
+            else {
+                int g = tp_grid(DEC_QKV / G);
+                const int cs = tp_cluster_size(G, g);
+                g -= g % cs;
+                CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
+                                       R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, cs));
+            }
         }
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
@@ -593,17 +676,22 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
         for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM));
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
-            CUDA_TRY(launch_pdl(tp_ffn_kernel, tp_grid(2 * DEC_HIDDEN / G), TP_THREADS, 0, st, R.dev, 2 * l, (const float *)R.xbuf, R.xbuf + DEC_DIM,
-                                W.ffn_norm, (const float *)(m->ada_scale + (size_t)l * DEC_DIM), W.w13, s->d_h));
+            int g = tp_grid(2 * DEC_HIDDEN / G);
+            const int cs = tp_cluster_size(G, g);
+            g -= g % cs;
+            CUDA_TRY(launch_pdl_cs(tp_ffn_kernel, g, cs, st, R.dev, 2 * l, (const float *)R.xbuf, R.xbuf + DEC_DIM,
+                                   W.ffn_norm, (const float *)(m->ada_scale + (size_t)l * DEC_DIM), W.w13, s->d_h, cs));
         }
         for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN));
     }
     int nblk = (VOCAB / G / FULL_NW + TP_WARPS - 1) / TP_WARPS;      // 100-400 MB: bandwidth-bound, one CTA per SM
     if (nblk > 148) nblk = 148;
+    const int lcs = tp_cluster_size(G, nblk);
+    nblk -= nblk % lcs;
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
-        CUDA_TRY(launch_pdl(tp_logits_kernel, nblk, TP_THREADS, 0, st, R.dev, 2 * L - 1, (const float *)(R.xbuf + DEC_DIM), m->dec_norm,
-                            m->tok_emb, s->d_logits, R.blockmax));
+        CUDA_TRY(launch_pdl_cs(tp_logits_kernel, nblk, lcs, st, R.dev, 2 * L - 1, (const float *)(R.xbuf + DEC_DIM), m->dec_norm,
+                               m->tok_emb, s->d_logits, R.blockmax, lcs));
     }
     for (int i = 0; i < NL; i++) tp_argmax_pub_kernel<<<1, 1024, 0, st>>>(tp->r[i].dev, tp->r[i].blockmax, nblk);
     for (int i = 0; i < NL; i++) tp_argmax_fin_kernel<<<1, 32, 0, st>>>(tp->r[i].dev, tp->r[i].d_params, tp->r[i].d_tokens);
