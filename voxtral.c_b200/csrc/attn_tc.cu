@@ -230,8 +230,9 @@ __global__ void __launch_bounds__(NT) enc_attn_kernel(
 // ======================================================================================================
 // tcgen05 version (round 2): S = Q K^T and O_tile = P V on the 5th-generation tensor cores, accumulators in TMEM.
 //
-//   CTA = 128 queries of one head, 128 threads; thread t owns query row t = TMEM lane t, so the online softmax needs
-//   no cross-lane reductions.  Key tiles of 64 keys.  Shared memory holds K-major SWIZZLE_128B operand tiles of 64 bf16
+//   CTA = 128 queries of one head, 256 threads; threads t and t + 128 share query row t & 127 (= TMEM lane), each takes 32 of
+//   the 64 key columns of a tile and 32 of the 64 output dims: the online softmax needs no shuffles, only one row-maximum
+//   exchange through shared memory that rides on a barrier the pipeline has anyway.  Key tiles of 64 keys.  Shared memory holds K-major SWIZZLE_128B operand tiles of 64 bf16
 //   columns (128-byte rows, 8-row groups 1024 B apart - the layout TMA would produce; here the tiles are written by the
 //   threads, because K / V live in the fp32 ring and are split into hi + lo bf16 terms on the way in):
 //       Q  [128 q   x 64 d]   hi, lo   (A operand of S)        K  [64 keys x 64 d]    hi, lo  (B operand of S)
@@ -245,11 +246,12 @@ namespace at5 {
 
 using namespace tcx;
 
-constexpr int BQ = 128, BK = 64, HD = ENC_HD, NT = 128;
+constexpr int BQ = 128, BK = 64, HD = ENC_HD, NT = 256;         // two threads per query row: 32 key columns / 32 output dims each
 constexpr int Q_BYTES = BQ * 128, K_BYTES = BK * 128;              // one bf16 plane of a tile
 constexpr int OFF_QH = 0, OFF_QL = Q_BYTES, OFF_KH = 2 * Q_BYTES, OFF_KL = OFF_KH + K_BYTES, OFF_VH = OFF_KL + K_BYTES,
               OFF_VL = OFF_VH + K_BYTES, OFF_PH = OFF_VL + K_BYTES, OFF_PL = OFF_PH + Q_BYTES, OFF_END = OFF_PL + Q_BYTES;
-constexpr int SMEM_BYTES = OFF_END + 1024 + 64;                    // + alignment slack + barrier / TMEM slot
+constexpr int OFF_XM = OFF_END + 64;                                // row maxima exchanged between the two threads of a row: [2][128] floats
+constexpr int SMEM_BYTES = OFF_XM + 2 * BQ * 4 + 1024;             // + alignment slack
 constexpr uint32_t IDESC = umma_idesc(128, 64);
 constexpr uint32_t TMEM_COLS = 256;                                // two S buffers (64 + 64) + O tile (64), power of two
 
@@ -273,47 +275,47 @@ __device__ __forceinline__ void store_chunk(unsigned char *ph, unsigned char *pl
     *reinterpret_cast<uint4 *>(pl + sw_off(r, c)) = l;
 }
 
-// K tile: thread t stages dims (t & 1) * 32 .. +31 of key (t >> 1): two threads read one 256-byte row (coalesced).
-// Load and store are separate so that the loads of tile t+1 are in flight while tile t is worked on.
-__device__ __forceinline__ void load_k(float4 (&v)[8], const float *__restrict__ kc, int head, int kt, int gmax, int ring_mask) {
-    const int key = threadIdx.x >> 1, half = threadIdx.x & 1, j = kt + key;
+// K tile (256 threads): thread t stages dims (t & 3) * 16 .. +15 of key (t >> 2): four threads read one 256-byte row.
+// Load and store are separate so that the loads of the next tile are in flight while the current one is worked on.
+__device__ __forceinline__ void load_k(float4 (&v)[4], const float *__restrict__ kc, int head, int kt, int gmax, int ring_mask) {
+    const int key = threadIdx.x >> 2, q4 = threadIdx.x & 3, j = kt + key;
     if (j <= gmax) {
-        const float4 *src = reinterpret_cast<const float4 *>(kc + (size_t)(j & ring_mask) * ENC_QKV + head * HD + half * 32);
+        const float4 *src = reinterpret_cast<const float4 *>(kc + (size_t)(j & ring_mask) * ENC_QKV + head * HD + q4 * 16);
         #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
+        for (int i = 0; i < 4; i++) v[i] = __ldg(src + i);
     } else {
         #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < 4; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
-__device__ __forceinline__ void store_k(unsigned char *kh, unsigned char *kl, const float4 (&v)[8]) {
-    const int key = threadIdx.x >> 1, half = threadIdx.x & 1;
+__device__ __forceinline__ void store_k(unsigned char *kh, unsigned char *kl, const float4 (&v)[4]) {
+    const int key = threadIdx.x >> 2, q4 = threadIdx.x & 3;
     #pragma unroll
-    for (int c = 0; c < 4; c++) store_chunk(kh, kl, key, half * 4 + c, v[2 * c], v[2 * c + 1], 1.0f);
+    for (int c = 0; c < 2; c++) store_chunk(kh, kl, key, q4 * 2 + c, v[2 * c], v[2 * c + 1], 1.0f);
 }
 
-// V tile, transposed: thread t owns keys 2 * (t >> 2), +1 and dims i * 16 + (t & 3) * 4 .. +3 (i < 4); it writes, for each of its
-// 16 dims, one 4-byte word = that dim of its two keys into row (dim) of Vt
-__device__ __forceinline__ void load_v(float4 (&a)[4], float4 (&b)[4], const float *__restrict__ vc, int head, int kt, int gmax, int ring_mask) {
-    const int kp = threadIdx.x >> 2, q4 = threadIdx.x & 3;
+// V tile, transposed (256 threads): thread t owns keys 2 * (t >> 3), +1 and dims i * 32 + (t & 7) * 4 .. +3 (i < 2); it writes, for
+// each of its 8 dims, one 4-byte word = that dim of its two keys into row (dim) of Vt
+__device__ __forceinline__ void load_v(float4 (&a)[2], float4 (&b)[2], const float *__restrict__ vc, int head, int kt, int gmax, int ring_mask) {
+    const int kp = threadIdx.x >> 3, s8 = threadIdx.x & 7;
     const int j0 = kt + 2 * kp, j1 = j0 + 1;
     #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        a[i] = (j0 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j0 & ring_mask) * ENC_QKV + head * HD + i * 16 + q4 * 4))
+    for (int i = 0; i < 2; i++) {
+        a[i] = (j0 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j0 & ring_mask) * ENC_QKV + head * HD + i * 32 + s8 * 4))
                             : make_float4(0.f, 0.f, 0.f, 0.f);
-        b[i] = (j1 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j1 & ring_mask) * ENC_QKV + head * HD + i * 16 + q4 * 4))
+        b[i] = (j1 <= gmax) ? __ldg(reinterpret_cast<const float4 *>(vc + (size_t)(j1 & ring_mask) * ENC_QKV + head * HD + i * 32 + s8 * 4))
                             : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
-__device__ __forceinline__ void store_vt(unsigned char *vh, unsigned char *vl, const float4 (&a)[4], const float4 (&b)[4]) {
-    const int kp = threadIdx.x >> 2, q4 = threadIdx.x & 3;
+__device__ __forceinline__ void store_vt(unsigned char *vh, unsigned char *vl, const float4 (&a)[2], const float4 (&b)[2]) {
+    const int kp = threadIdx.x >> 3, s8 = threadIdx.x & 7;
     const int col = 2 * kp;                                        // key column of the pair inside the 64-key row
     #pragma unroll
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < 2; i++) {
         const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w}, bv[4] = {b[i].x, b[i].y, b[i].z, b[i].w};
         #pragma unroll
         for (int e = 0; e < 4; e++) {
-            const int d = i * 16 + q4 * 4 + e;
+            const int d = i * 32 + s8 * 4 + e;
             uint32_t h, l;
             split_pk(av[e], bv[e], h, l);
             const uint32_t off = sw_off(d, col >> 3) + (uint32_t)((col & 7) * 2);
@@ -329,7 +331,7 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 template <int TERMS>
-__global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
+__global__ void __launch_bounds__(NT, 2) enc_attn_tc5_kernel(
     const float *__restrict__ qkv, long ldq, const float *__restrict__ kc, const float *__restrict__ vc,
     int M, int pos0, int first_valid, int window, int ring_mask, uint16_t *__restrict__ out, long ldo, int split,
     const int *__restrict__ pos_dev, float *__restrict__ part, unsigned *__restrict__ cnt, int n_splits) {
@@ -341,12 +343,16 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)smraw + 1023) & ~(uintptr_t)1023);   // swizzle atoms are 1024-byte aligned
     uint64_t *bar_s = reinterpret_cast<uint64_t *>(sm + OFF_END), *bar_o = bar_s + 1;      // S products done / P V products done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sm + OFF_END + 16);
+    int *s_last = reinterpret_cast<int *>(sm + OFF_END + 32);
+    float *xm = reinterpret_cast<float *>(sm + OFF_XM);                                    // [2][128]
     pdl_launch_dependents();
     pdl_wait();
     if (pos_dev) { pos0 = pos_dev[0]; first_valid = pos_dev[1]; }
-    const int tid = threadIdx.x, warp = tid >> 5;
+    // thread t: query row r = t & 127 (= TMEM lane; warp w reads the lane quarter w % 4), half hf = t >> 7: key columns
+    // hf * 32 .. +31 of every S tile, output dims hf * 32 .. +31
+    const int tid = threadIdx.x, warp = tid >> 5, r = tid & (BQ - 1), hf = tid >> 7;
     const int head = blockIdx.y, q0 = n_splits ? 0 : blockIdx.x * BQ;
-    const int gq = pos0 + q0 + tid;                                                  // logical position of this thread's query
+    const int gq = pos0 + q0 + r;                                                    // logical position of this thread's query
     const int gmin = pos0 + q0, gmax = pos0 + min(q0 + BQ - 1, M - 1);
     int k_lo = gmin - (window - 1);
     if (k_lo < first_valid) k_lo = first_valid;
@@ -369,31 +375,32 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
         mb_init(bar_o, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    // Q tile: thread t = query row t, pre-scaled by 1/sqrt(64) (an exact power of two)
+    // Q tile: this thread's half row, pre-scaled by 1/sqrt(64) (an exact power of two)
     {
-        const int row = q0 + tid;
-        float4 v[16];
+        const int row = q0 + r;
+        float4 v[8];
         if (row < M) {
-            const float4 *src = reinterpret_cast<const float4 *>(qkv + (size_t)row * ldq + head * HD);
+            const float4 *src = reinterpret_cast<const float4 *>(qkv + (size_t)row * ldq + head * HD + hf * 32);
             #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = __ldg(src + i);
+            for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
         } else {
             #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = 0; i < 8; i++) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         #pragma unroll
-        for (int c = 0; c < 8; c++) store_chunk(sm + OFF_QH, sm + OFF_QL, tid, c, v[2 * c], v[2 * c + 1], 0.125f);
+        for (int c = 0; c < 4; c++) store_chunk(sm + OFF_QH, sm + OFF_QL, r, hf * 4 + c, v[2 * c], v[2 * c + 1], 0.125f);
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16), t_o = t_s + 128;     // this warp's 32 lanes: S buffers at columns 0 / 64, O at 128
+    const uint32_t t_lane = tmem + ((uint32_t)((warp & 3) * 32) << 16);             // this warp's 32 lanes
+    const uint32_t t_s = t_lane + (uint32_t)(hf * 32), t_o = t_lane + 128 + (uint32_t)(hf * 32);   // S buffers at columns 0 / 64, O at 128
 
-    float o[HD];
+    float o[32];
     #pragma unroll
-    for (int i = 0; i < HD; i++) o[i] = 0.f;
-    float m = -INFINITY, l = 0.f;
+    for (int i = 0; i < 32; i++) o[i] = 0.f;
+    float m = -INFINITY, l = 0.f;                                                    // l: this thread's 32 key columns only
     const uint32_t a_q[2] = {s32(sm + OFF_QH), s32(sm + OFF_QL)}, a_k[2] = {s32(sm + OFF_KH), s32(sm + OFF_KL)};
     const uint32_t a_p[2] = {s32(sm + OFF_PH), s32(sm + OFF_PL)}, a_v[2] = {s32(sm + OFF_VH), s32(sm + OFF_VL)};
     constexpr float LOG2E = 1.4426950408889634f;
@@ -413,7 +420,7 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
 
     // Software pipeline over the key tiles: while the threads do the softmax of tile t, the tensor core computes S of tile
     // t+1 (second S buffer) and finishes P V of tile t-1; the K / V rows of the next tile travel in registers.
-    float4 kreg[8], va[4], vb[4];
+    float4 kreg[4], va[2], vb[2];
     load_k(kreg, kc, head, k_lo, gmax, ring_mask);
     load_v(va, vb, vc, head, k_lo, gmax, ring_mask);
     store_k(sm + OFF_KH, sm + OFF_KL, kreg);
@@ -428,12 +435,27 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     int buf = 0;
     for (int kt = k_lo; kt <= k_end; kt += BK, buf ^= 1) {
         const bool has_next = kt + BK <= k_end, first = kt == k_lo;
-        // ---- S row of this tile -> registers ----
+        // ---- this thread's 32 columns of the S row -> registers; mask (boundary tiles only); local maximum ----
         mb_wait(bar_s, ph_s); ph_s ^= 1u;
         tc_fence_after();
-        uint32_t sr[2][32];
-        tmem_ld32(t_s + (uint32_t)(buf * 64), sr[0]);
-        tmem_ld32(t_s + (uint32_t)(buf * 64) + 32, sr[1]);
+        uint32_t sr[32];
+        tmem_ld32(t_s + (uint32_t)(buf * 64), sr);
+        const bool interior = kt + BK - 1 <= gmin && kt > gmax - window && kt >= first_valid;    // uniform over the CTA
+        float mx = -INFINITY;
+        if (interior) {
+            #pragma unroll
+            for (int i = 0; i < 32; i++) mx = fmaxf(mx, __uint_as_float(sr[i]));
+        } else {
+            #pragma unroll
+            for (int i = 0; i < 32; i++) {
+                const int jk = kt + hf * 32 + i;
+                const bool ok = jk <= gq && jk > gq - window && jk >= first_valid;
+                const float v = ok ? __uint_as_float(sr[i]) : -INFINITY;
+                sr[i] = __float_as_uint(v);
+                mx = fmaxf(mx, v);
+            }
+        }
+        xm[hf * BQ + r] = mx;                                           // for the other thread of this row
         // ---- next K tile -> smem (S of this tile has retired, so the K planes are free), S(t+1) starts now ----
         if (has_next) {
             store_k(sm + OFF_KH, sm + OFF_KL, kreg);
@@ -442,22 +464,8 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
         tc_fence_before();
         __syncthreads();
         if (has_next && tid == 0) issue_s(buf ^ 1);
-        // ---- mask (boundary tiles only) + online softmax in registers ----
-        const bool interior = kt + BK - 1 <= gmin && kt > gmax - window && kt >= first_valid;    // uniform over the CTA
-        float mx = -INFINITY;
-        if (interior) {
-            #pragma unroll
-            for (int i = 0; i < BK; i++) mx = fmaxf(mx, __uint_as_float(sr[i >> 5][i & 31]));
-        } else {
-            #pragma unroll
-            for (int i = 0; i < BK; i++) {
-                const int jk = kt + i;
-                const bool ok = jk <= gq && jk > gq - window && jk >= first_valid;
-                const float v = ok ? __uint_as_float(sr[i >> 5][i & 31]) : -INFINITY;
-                sr[i >> 5][i & 31] = __float_as_uint(v);
-                mx = fmaxf(mx, v);
-            }
-        }
+        // ---- online softmax in registers; both threads of a row use the same maximum ----
+        mx = fmaxf(mx, xm[(hf ^ 1) * BQ + r]);
         const float mn = fmaxf(m, mx);
         const float mu = (mn == -INFINITY) ? 0.f : mn;
         const float corr = (m == -INFINITY) ? 0.f : ex2((m - mu) * LOG2E);
@@ -465,9 +473,9 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
         m = mn;
         float ps = 0.f;
         #pragma unroll
-        for (int i = 0; i < BK; i++) {
-            const float pv = ex2(fmaf(__uint_as_float(sr[i >> 5][i & 31]), LOG2E, -mu2));    // 2^-inf = 0 for masked keys
-            sr[i >> 5][i & 31] = __float_as_uint(pv);
+        for (int i = 0; i < 32; i++) {
+            const float pv = ex2(fmaf(__uint_as_float(sr[i]), LOG2E, -mu2));     // 2^-inf = 0 for masked keys
+            sr[i] = __float_as_uint(pv);
             ps += pv;
         }
         l = l * corr + ps;
@@ -475,25 +483,22 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
         if (!first) {
             mb_wait(bar_o, ph_o); ph_o ^= 1u;
             tc_fence_after();
+            uint32_t rr[32];
+            tmem_ld32(t_o, rr);
             #pragma unroll
-            for (int hlf = 0; hlf < 2; hlf++) {
-                uint32_t r[32];
-                tmem_ld32(t_o + hlf * 32, r);
-                #pragma unroll
-                for (int i = 0; i < 32; i++) o[hlf * 32 + i] = fmaf(o[hlf * 32 + i], corr_prev, __uint_as_float(r[i]));
-            }
+            for (int i = 0; i < 32; i++) o[i] = fmaf(o[i], corr_prev, __uint_as_float(rr[i]));
         }
         corr_prev = corr;
         // ---- P and the transposed V tile -> smem (their planes are free: P V of the previous tile has retired) ----
         #pragma unroll
-        for (int c = 0; c < BK / 8; c++) {
+        for (int c = 0; c < 4; c++) {
             uint4 h, lo4;
-            #define PV_(e) __uint_as_float(sr[(c * 8 + (e)) >> 5][(c * 8 + (e)) & 31])
+            #define PV_(e) __uint_as_float(sr[c * 8 + (e)])
             split_pk(PV_(0), PV_(1), h.x, lo4.x); split_pk(PV_(2), PV_(3), h.y, lo4.y);
             split_pk(PV_(4), PV_(5), h.z, lo4.z); split_pk(PV_(6), PV_(7), h.w, lo4.w);
             #undef PV_
-            *reinterpret_cast<uint4 *>(sm + OFF_PH + sw_off(tid, c)) = h;
-            if (TERMS > 1) *reinterpret_cast<uint4 *>(sm + OFF_PL + sw_off(tid, c)) = lo4;
+            *reinterpret_cast<uint4 *>(sm + OFF_PH + sw_off(r, hf * 4 + c)) = h;
+            if (TERMS > 1) *reinterpret_cast<uint4 *>(sm + OFF_PL + sw_off(r, hf * 4 + c)) = lo4;
         }
         store_vt(sm + OFF_VH, sm + OFF_VL, va, vb);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -518,28 +523,28 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
     {   // last tile's P V
         mb_wait(bar_o, ph_o);
         tc_fence_after();
+        uint32_t rr[32];
+        tmem_ld32(t_o, rr);
         #pragma unroll
-        for (int hlf = 0; hlf < 2; hlf++) {
-            uint32_t r[32];
-            tmem_ld32(t_o + hlf * 32, r);
-            #pragma unroll
-            for (int i = 0; i < 32; i++) o[hlf * 32 + i] = fmaf(o[hlf * 32 + i], corr_prev, __uint_as_float(r[i]));
-        }
+        for (int i = 0; i < 32; i++) o[i] = fmaf(o[i], corr_prev, __uint_as_float(rr[i]));
     }
-    const int row = q0 + tid;
+    // ---- the row sum is the sum of the two threads' halves (same reference maximum m) ----
+    xm[hf * BQ + r] = l;
+    __syncthreads();
+    l += xm[(hf ^ 1) * BQ + r];
+
+    const int row = q0 + r;
     if (n_splits && n_active > 1) {
         // ---- key-split mode: leave the partial, the last CTA of this head merges ----
         constexpr int PL = HD + 2;                                                   // o[64], m, l - stored [item][row]: coalesced over threads
         float *mine = part + ((size_t)head * n_splits + blockIdx.x) * PL * BQ;
         if (row < M) {
             #pragma unroll
-            for (int i = 0; i < HD; i++) mine[i * BQ + tid] = o[i];
-            mine[HD * BQ + tid] = m;
-            mine[(HD + 1) * BQ + tid] = l;
+            for (int i = 0; i < 32; i++) mine[(hf * 32 + i) * BQ + r] = o[i];
+            if (hf == 0) { mine[HD * BQ + r] = m; mine[(HD + 1) * BQ + r] = l; }
         }
         __threadfence();
         __syncthreads();
-        int *s_last = reinterpret_cast<int *>(sm + OFF_END + 32);
         if (tid == 0) {
             const unsigned old = atomicAdd(cnt + head, 1u);
             *s_last = (old + 1u == (unsigned)n_active) ? 1 : 0;
@@ -550,27 +555,27 @@ __global__ void __launch_bounds__(NT) enc_attn_tc5_kernel(
             __threadfence();
             const float *base = part + (size_t)head * n_splits * PL * BQ;
             float mm = -INFINITY;
-            for (int sp = 0; sp < n_active; sp++) mm = fmaxf(mm, __ldcg(base + (size_t)sp * PL * BQ + HD * BQ + tid));
+            for (int sp = 0; sp < n_active; sp++) mm = fmaxf(mm, __ldcg(base + (size_t)sp * PL * BQ + HD * BQ + r));
             #pragma unroll
-            for (int i = 0; i < HD; i++) o[i] = 0.f;
+            for (int i = 0; i < 32; i++) o[i] = 0.f;
             l = 0.f;
             for (int sp = 0; sp < n_active; sp++) {
                 const float *ps_ = base + (size_t)sp * PL * BQ;
-                const float ms = __ldcg(ps_ + HD * BQ + tid);
+                const float ms = __ldcg(ps_ + HD * BQ + r);
                 const float e = (ms == -INFINITY) ? 0.f : ex2((ms - mm) * LOG2E);
-                l = fmaf(e, __ldcg(ps_ + (HD + 1) * BQ + tid), l);
+                l = fmaf(e, __ldcg(ps_ + (HD + 1) * BQ + r), l);
                 #pragma unroll
-                for (int i = 0; i < HD; i++) o[i] = fmaf(e, __ldcg(ps_ + i * BQ + tid), o[i]);
+                for (int i = 0; i < 32; i++) o[i] = fmaf(e, __ldcg(ps_ + (hf * 32 + i) * BQ + r), o[i]);
             }
         }
         if (!*s_last) l = -1.f;                                                      // not the merger: nothing to store
     }
-    // ---- normalise, split, store this thread's row ----
+    // ---- normalise, split, store this thread's 32 dims of the row ----
     if (row < M && l >= 0.f) {
         const float inv = l > 0.f ? 1.0f / l : 0.f;
-        uint16_t *oh = out + (size_t)row * ldo + head * HD;
+        uint16_t *oh = out + (size_t)row * ldo + head * HD + hf * 32;
         #pragma unroll
-        for (int c = 0; c < HD / 8; c++) {
+        for (int c = 0; c < 4; c++) {
             uint4 h, lo4;
             split_pk(o[8 * c] * inv, o[8 * c + 1] * inv, h.x, lo4.x); split_pk(o[8 * c + 2] * inv, o[8 * c + 3] * inv, h.y, lo4.y);
             split_pk(o[8 * c + 4] * inv, o[8 * c + 5] * inv, h.z, lo4.z); split_pk(o[8 * c + 6] * inv, o[8 * c + 7] * inv, h.w, lo4.w);
