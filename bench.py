@@ -139,9 +139,19 @@ def run_cuda(args, rank, world):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # NCCL prints its version banner on stdout; stdout carries ONE JSON line
-        dist.init_process_group("nccl")
+        # NCCL writes its "NCCL version ..." banner to fd 1 when the first communicator comes up (NCCL_DEBUG = VERSION
+        # or WARN); stdout carries ONE JSON line, so fd 1 points at stderr until the first collective has run
+        sys.stdout.flush()
+        fd1 = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl")
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(fd1, 1)
+            os.close(fd1)
 
     def barrier():
         if dist is not None:

@@ -79,6 +79,24 @@ typedef struct {
     const float *ada_scale;                   /* [n_dec_layers*3072] f32, voxtral.c:47-80 */
 } vox_cuda_weights_t;
 
+/* Q8 container: what the reference's loader hands out for a dtype "Q8" tensor -
+ * safetensors_get_q8_data_direct / _scales_direct (voxtral_safetensors.c:457-468), fields *_weight_q8 /
+ * *_scale_q8 of vox_enc_layer_t / vox_dec_layer_t / vox_adapter_t (voxtral.h:56-182): int8 rows, one
+ * fp32 scale per row, w[r][c] = q[r][c] * scale[r] (quantize.py:34-43). */
+typedef struct {
+    const int8_t *q;                          /* [rows, cols] row-major */
+    const float *scale;                       /* [rows] */
+} vox_cuda_q8_t;
+
+typedef struct { vox_cuda_q8_t wq, wk, wv, wo, w1, w2, w3; } vox_cuda_layer_q8_t;   /* shapes as the bf16 tables above */
+
+typedef struct {
+    vox_cuda_layer_q8_t enc[VOX_CUDA_ENC_LAYERS];
+    vox_cuda_q8_t adapter_w0, adapter_w1;     /* [3072,5120], [3072,3072] */
+    vox_cuda_q8_t tok_embeddings;             /* [131072,3072] (tied LM head; embedding row = q * scale, voxtral.c:443-452) */
+    vox_cuda_layer_q8_t dec[VOX_CUDA_DEC_LAYERS];
+} vox_cuda_weights_q8_t;
+
 typedef struct vox_cuda_model vox_cuda_model_t;   /* weights in HBM, shared by streams */
 typedef struct vox_cuda_state vox_cuda_state_t;   /* one stream's device state */
 typedef struct vox_cuda_group vox_cuda_group_t;   /* B streams decoded in lock step (one weight pass per step) */
@@ -95,6 +113,15 @@ size_t vox_cuda_memory_used(void);   /* vox_metal_memory_used, voxtral_metal.h:2
 /* ---- weights (replaces the warm-up block in vox_load, voxtral.c:186-285:
  *      vox_metal_warmup_bf16 / _merged_2 / _merged_3 / _decoder_ops) ------- */
 vox_cuda_model_t *vox_cuda_model_create(const vox_cuda_weights_t *w);
+/* Q8 checkpoint (ctx->use_q8, voxtral.c:175-181): `w` supplies the fp32 tensors (conv stem, biases, norms,
+ * ada_scale; its bf16 pointers are ignored), `q` every 2-D matrix.  Arithmetic follows the reference's Q8 CPU
+ * path: y = (sum_k q[n][k] * x[k]) * scale[n] with the sum exact to fp32 class (voxtral_kernels.c:277-310 for
+ * M = 1; for M > 1 the reference widens q * scale to fp32 and calls sgemm, :322-336 - the same product up to
+ * one fp32 rounding per weight).  The single-stream decoder streams the int8 rows (half the bytes per token);
+ * encoder, adapter and prompt prefill run on the tcgen05 GEMMs with the scale in the epilogue.  Stream groups,
+ * the tensor-parallel decoder and vox_cuda_sgemm_bf16 refuse a Q8 model (error, not a fallback). */
+vox_cuda_model_t *vox_cuda_model_create_q8(const vox_cuda_weights_t *w, const vox_cuda_weights_q8_t *q);
+int  vox_cuda_model_is_q8(const vox_cuda_model_t *m);
 /* vox_set_delay recomputes ada_scale on the host (voxtral.c:1681-1687). */
 int  vox_cuda_model_set_ada_scale(vox_cuda_model_t *m, const float *ada_scale);
 void vox_cuda_model_free(vox_cuda_model_t *m);

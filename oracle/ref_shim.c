@@ -92,7 +92,34 @@ void refshim_fill_weights(const vox_ctx_t *c, vox_cuda_weights_t *w) {
     w->ada_scale = c->ada_scale;
 }
 
+/* Q8 checkpoint (ctx->use_q8): the *_weight_q8 / *_scale_q8 pairs of the reference's tables (voxtral.h:56-182)
+ * -> vox_cuda_weights_q8_t.  Returns ctx->use_q8. */
+int refshim_fill_weights_q8(const vox_ctx_t *c, vox_cuda_weights_q8_t *q) {
+    memset(q, 0, sizeof(*q));
+#define Q8BIND(dst, src) do { (dst).q = (src##_weight_q8); (dst).scale = (src##_scale_q8); } while (0)
+    for (int i = 0; i < VOX_ENC_LAYERS; i++) {
+        const vox_enc_layer_t *l = &c->encoder.layers[i];
+        vox_cuda_layer_q8_t *d = &q->enc[i];
+        Q8BIND(d->wq, l->wq); Q8BIND(d->wk, l->wk); Q8BIND(d->wv, l->wv); Q8BIND(d->wo, l->wo);
+        Q8BIND(d->w1, l->w1); Q8BIND(d->w2, l->w2); Q8BIND(d->w3, l->w3);
+    }
+    Q8BIND(q->adapter_w0, c->adapter.linear0); Q8BIND(q->adapter_w1, c->adapter.linear1);
+    q->tok_embeddings.q = c->decoder.tok_embeddings_q8;
+    q->tok_embeddings.scale = c->decoder.tok_embeddings_scale_q8;
+    for (int i = 0; i < VOX_DEC_LAYERS; i++) {
+        const vox_dec_layer_t *l = &c->decoder.layers[i];
+        vox_cuda_layer_q8_t *d = &q->dec[i];
+        Q8BIND(d->wq, l->wq); Q8BIND(d->wk, l->wk); Q8BIND(d->wv, l->wv); Q8BIND(d->wo, l->wo);
+        Q8BIND(d->w1, l->w1); Q8BIND(d->w2, l->w2); Q8BIND(d->w3, l->w3);
+    }
+#undef Q8BIND
+    return c->use_q8;
+}
+const int8_t *refshim_tok_embeddings_q8(vox_ctx_t *c) { return c->decoder.tok_embeddings_q8; }
+const float *refshim_tok_embeddings_scale_q8(vox_ctx_t *c) { return c->decoder.tok_embeddings_scale_q8; }
+
 int refshim_sizeof_weights(void) { return (int)sizeof(vox_cuda_weights_t); }
+int refshim_sizeof_weights_q8(void) { return (int)sizeof(vox_cuda_weights_q8_t); }
 
 /* ---- mel helpers (the incremental ctx is opaque in voxtral_audio.h) ---- */
 /* Runs the reference streaming mel exactly as vox_stream_* drives it

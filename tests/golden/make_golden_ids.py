@@ -13,6 +13,9 @@ checkpoint (tools/gen_model.c, seed 1234) - the pin for BASELINE configs 1-4:
   clip60_i20 config 3: 16000-sample pieces, interval 2.0
   long_head  config 4 (i): the first 62 s of the 30-minute clip (seed 2), fed without
              finish - by causality its ids equal the head of the full run
+  jfk_q8, clip60_q8   SURVEY 8(f3): the same two jobs on the Q8 container of the same weights
+             (gen_model --q8 = the reference's quantize.py, tests/golden/q8_quantizer.json), i.e. the
+             reference's own Q8 CPU path (voxtral_kernels.c:277-393); not part of "all"
 
 Every decoder call of the reference's stream path is recorded by the --wrap recorder in
 oracle/ref_shim.c (token id + top-2 logit margin), every encoder call by its row count.
@@ -51,6 +54,8 @@ def job_audio(job):
         s16 = np.round(x * 32768.0).astype(np.int16)
         assert np.array_equal(s16.astype(np.float32) / 32768.0, x)      # mono 16 kHz s16: no resampling
         return x, s16
+    if job == "jfk_q8":
+        return job_audio("jfk")
     if job.startswith("clip60"):
         return bench.synth_clip(60.0, 1), None
     if job == "long_head":
@@ -60,7 +65,7 @@ def job_audio(job):
 
 def run_job(job):
     x, s16 = job_audio(job)
-    ref = rh.Ref(rh.model_dir())
+    ref = rh.Ref(rh.model_dir(extra=("--q8",)) if job.endswith("_q8") else rh.model_dir())
     L = ref.L
     L.vox_stream_init.restype = C.c_void_p
     L.vox_stream_init.argtypes = [C.c_void_p]
@@ -77,7 +82,7 @@ def run_job(job):
     L.refshim_log_reset()
     s = L.vox_stream_init(ref.ctx)
     assert s
-    if job == "jfk":
+    if job.startswith("jfk"):
         L.vox_stream_set_alt(s, ALT_N, C.c_float(ALT_CUTOFF))
     piece = len(x)
     if job == "clip60_i05":
@@ -122,7 +127,7 @@ def run_job(job):
     assert np.array_equal(alts[:, 0], text_ids), (alts[:8, 0], text_ids[:8])
     out = {"ids": ids.astype(np.int32), "margins": margins.astype(np.float32), "enc_call_rows": enc_rows.astype(np.int32),
            "top_logits": top.astype(np.float32),     # [steps][5]: logit of the id, then the 4 best other text logits
-           "alts": alts, "alt_n": np.int32(ALT_N), "alt_cutoff": np.float32(ALT_CUTOFF if job == "jfk" else 0.0),
+           "alts": alts, "alt_n": np.int32(ALT_N), "alt_cutoff": np.float32(ALT_CUTOFF if job.startswith("jfk") else 0.0),
            "n_samples": np.int64(len(x)), "cpu_seconds": np.float32(time.time() - t0)}
     if s16 is not None:
         out["pcm_s16"] = s16

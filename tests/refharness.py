@@ -137,8 +137,20 @@ class Ref:
         tok = self.L.vox_decoder_forward(self.ctx, x.ctypes.data_as(f32p), logits.ctypes.data_as(f32p))
         return tok, logits
 
+    def fill_weights_q8(self, q):
+        """binds the reference's Q8 tables; returns ctx->use_q8"""
+        return self.L.refshim_fill_weights_q8(self.ctx, C.byref(q))
+
     def tok_embedding(self, token):
         p = self.L.refshim_tok_embeddings(self.ctx)
+        if not p:                             # Q8 checkpoint: row = q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
+            self.L.refshim_tok_embeddings_q8.restype = C.POINTER(C.c_int8)
+            self.L.refshim_tok_embeddings_q8.argtypes = [C.c_void_p]
+            self.L.refshim_tok_embeddings_scale_q8.restype = f32p
+            self.L.refshim_tok_embeddings_scale_q8.argtypes = [C.c_void_p]
+            q = np.ctypeslib.as_array(self.L.refshim_tok_embeddings_q8(self.ctx), shape=(131072, 3072))[token]
+            sc = np.ctypeslib.as_array(self.L.refshim_tok_embeddings_scale_q8(self.ctx), shape=(131072,))[token]
+            return q.astype(np.float32) * np.float32(sc)
         row = np.ctypeslib.as_array(p, shape=(131072, 3072))[token]
         return (row.astype(np.uint32) << 16).view(np.float32)
 

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Decoder-step probe (GPU): ms/step from CUDA events plus the megakernel's
-cycle breakdown (VOX_CUDA_MEGA_PROF=1).  usage: dec_probe.py [steps] [start_pos]"""
+cycle breakdown (VOX_CUDA_MEGA_PROF=1).  usage: dec_probe.py [steps] [start_pos] [q8]   (q8: the Q8 container)"""
 import ctypes as C
 import os
 import sys
@@ -19,8 +19,10 @@ steps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 start = int(sys.argv[2]) if len(sys.argv) > 2 else 38
 L = vc.lib()
 assert L.vox_cuda_init() == 1, vc.last_error()
-hm = hostmodel.HostModel(rh.model_dir())
-model = vc.check(L.vox_cuda_model_create(C.byref(hm.weights)), "model")
+Q8 = len(sys.argv) > 3 and sys.argv[3] == "q8"
+hm = hostmodel.HostModel(rh.model_dir(extra=("--q8",)) if Q8 else rh.model_dir())
+model = vc.check(hm.create_model(L), "model")
+WEIGHT_BYTES = 6857687040 // 2 + 4 * 2 * (26 * (6144 + 3072 + 18432 + 3072) + 131072) if Q8 else 6857687040   # int8 + scale + row sum
 st = vc.check(L.vox_cuda_state_create(model), "state")
 rng = np.random.default_rng(0)
 ad = (0.5 * rng.standard_normal((steps, 3072))).astype(np.float32)
@@ -31,7 +33,7 @@ for rep in range(3):
     toks = np.empty(steps, np.int32)
     ms = L.vox_cuda_bench_decoder_steps(st, 32, 0, steps, vc.iptr(toks))
     prof = (C.c_double * 7)()
-    line = f"rep {rep}: {ms:.4f} ms/step  ({6857687040 / ms / 1e6:.0f} GB/s)  uniq tokens {len(set(toks.tolist()))}"
+    line = f"rep {rep}: {ms:.4f} ms/step  ({WEIGHT_BYTES / ms / 1e6:.0f} GB/s)  uniq tokens {len(set(toks.tolist()))}"
     if L.vox_cuda_debug_mega_profile(st, prof) == 0 and prof[0] > 0:
         t = prof[0]
         line += (f" | cycles/step {t / steps:.0f}: wait-tiles {100 * prof[1] / t:.1f}% grid-sync {100 * prof[2] / t:.1f}% "

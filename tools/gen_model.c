@@ -14,7 +14,12 @@
  * Irwin-Hall sum), hence bit-identical on every host.
  *
  *   gen_model <out_dir> [--seed N] [--enc-layers N] [--dec-layers N]
- *             [--emb-sigma F] [--gain F] [--bias-sigma F] [--no-tokenizer]
+ *             [--emb-sigma F] [--gain F] [--bias-sigma F] [--no-tokenizer] [--q8]
+ *
+ * --q8 writes the SAME weights in the reference's Q8 container (what /root/reference/quantize.py:34-43,86-129
+ * makes of the BF16 file): every 2-D tensor becomes dtype "Q8" = [rows x f32 scale][rows x cols int8] with
+ * scale = amax/127 (double division, stored as f32), q = rint(w / scale) (f32 division, half to even), clipped to
+ * [-128, 127]; every other tensor is widened to F32.  tests/golden/q8_quantizer.json pins this twin to quantize.py.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -75,12 +80,12 @@ static inline uint16_t f32_to_bf16(float f) {
 int main(int argc, char **argv) {
     if (argc < 2) {
         fprintf(stderr, "usage: %s <out_dir> [--seed N] [--enc-layers N] [--dec-layers N]"
-                        " [--emb-sigma F] [--gain F] [--bias-sigma F] [--ffn-out-gain F] [--attn-out-gain F] [--adapter-gain F] [--no-tokenizer]\n", argv[0]);
+                        " [--emb-sigma F] [--gain F] [--bias-sigma F] [--ffn-out-gain F] [--attn-out-gain F] [--adapter-gain F] [--no-tokenizer] [--q8]\n", argv[0]);
         return 2;
     }
     const char *out = argv[1];
     uint64_t seed = 1234;
-    int enc_layers = 32, dec_layers = 26, tokenizer = 1;
+    int enc_layers = 32, dec_layers = 26, tokenizer = 1, q8 = 0;
     /* Defaults = the repo's standard checkpoint (init "v2").  Chosen on the reference's CPU path so that the
      * greedy ids depend on the audio (15 distinct ids in 61 steps of the bench clip, top-2 margins 0.03-1.6)
      * instead of collapsing to one id at every step, which is what unit gains everywhere give. */
@@ -96,6 +101,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--attn-out-gain") && i + 1 < argc) attn_out_gain = (float)atof(argv[++i]);
         else if (!strcmp(argv[i], "--adapter-gain") && i + 1 < argc) adapter_gain = (float)atof(argv[++i]);
         else if (!strcmp(argv[i], "--no-tokenizer")) tokenizer = 0;
+        else if (!strcmp(argv[i], "--q8")) q8 = 1;
         else { fprintf(stderr, "gen_model: bad argument %s\n", argv[i]); return 2; }
     }
 
@@ -149,14 +155,15 @@ int main(int argc, char **argv) {
     for (int i = 0; i < NT; i++) {
         tensor_t *t = &T[i];
         t->offset = off;
-        size_t nb = t->numel * 2;
+        const int is_q8 = q8 && t->ndim == 2;
+        size_t nb = is_q8 ? (size_t)t->shape[0] * 4 + t->numel : (q8 ? t->numel * 4 : t->numel * 2);
         char shp[64];
         if (t->ndim == 1) snprintf(shp, sizeof(shp), "[%ld]", t->shape[0]);
         else if (t->ndim == 2) snprintf(shp, sizeof(shp), "[%ld,%ld]", t->shape[0], t->shape[1]);
         else snprintf(shp, sizeof(shp), "[%ld,%ld,%ld]", t->shape[0], t->shape[1], t->shape[2]);
         hlen += (size_t)snprintf(hdr + hlen, hcap - hlen,
-            "%s\"%s\":{\"dtype\":\"BF16\",\"shape\":%s,\"data_offsets\":[%zu,%zu]}",
-            i ? "," : "", t->name, shp, off, off + nb);
+            "%s\"%s\":{\"dtype\":\"%s\",\"shape\":%s,\"data_offsets\":[%zu,%zu]}",
+            i ? "," : "", t->name, is_q8 ? "Q8" : (q8 ? "F32" : "BF16"), shp, off, off + nb);
         off += nb;
     }
     hdr[hlen++] = '}';
@@ -174,6 +181,18 @@ int main(int argc, char **argv) {
     for (int i = 0; i < NT; i++) if (T[i].numel > maxel) maxel = T[i].numel;
     uint16_t *buf = (uint16_t *)malloc(maxel * 2);
     if (!buf) { fprintf(stderr, "gen_model: out of memory\n"); return 1; }
+    float *fbuf = NULL;       /* --q8: row scales, or the widened copy of a non-2-D tensor */
+    int8_t *qbuf = NULL;
+    if (q8) {
+        size_t maxf = 16;
+        for (int i = 0; i < NT; i++) {
+            const size_t nf = T[i].ndim == 2 ? (size_t)T[i].shape[0] : T[i].numel;
+            if (nf > maxf) maxf = nf;
+        }
+        fbuf = (float *)malloc(maxf * sizeof(float));
+        qbuf = (int8_t *)malloc(maxel);
+        if (!fbuf || !qbuf) { fprintf(stderr, "gen_model: out of memory\n"); return 1; }
+    }
 
     for (int ti = 0; ti < NT; ti++) {
         tensor_t *t = &T[ti];
@@ -202,7 +221,33 @@ int main(int argc, char **argv) {
             buf[i] = f32_to_bf16(shift + scale * std_normal(key, i));
         if (t->kind == K_EMB)  /* EOS (id 2) row zero: greedy never stops by chance */
             memset(buf + (size_t)2 * 3072, 0, 3072 * 2);
-        if (fwrite(buf, 2, ne, f) != ne) { perror("fwrite"); return 1; }
+        if (!q8) {
+            if (fwrite(buf, 2, ne, f) != ne) { perror("fwrite"); return 1; }
+        } else if (t->ndim == 2) {
+            const long rows = t->shape[0], cols = t->shape[1];
+            #pragma omp parallel for schedule(static)
+            for (long r = 0; r < rows; r++) {
+                const uint16_t *src = buf + (size_t)r * cols;
+                float amax = 0.0f;
+                for (long c = 0; c < cols; c++) {
+                    uint32_t u = (uint32_t)src[c] << 16; float v; memcpy(&v, &u, 4);
+                    v = fabsf(v); if (v > amax) amax = v;
+                }
+                const float sc = amax == 0.0f ? 0.0f : (float)((double)amax / 127.0);
+                fbuf[r] = sc;
+                for (long c = 0; c < cols; c++) {
+                    uint32_t u = (uint32_t)src[c] << 16; float v; memcpy(&v, &u, 4);
+                    float q = amax == 0.0f ? 0.0f : rintf(v / sc);
+                    if (q < -128.0f) q = -128.0f;
+                    if (q > 127.0f) q = 127.0f;
+                    qbuf[(size_t)r * cols + c] = (int8_t)q;
+                }
+            }
+            if (fwrite(fbuf, 4, (size_t)rows, f) != (size_t)rows || fwrite(qbuf, 1, ne, f) != ne) { perror("fwrite"); return 1; }
+        } else {
+            for (size_t i = 0; i < ne; i++) { uint32_t u = (uint32_t)buf[i] << 16; memcpy(&fbuf[i], &u, 4); }
+            if (fwrite(fbuf, 4, ne, f) != ne) { perror("fwrite"); return 1; }
+        }
     }
     fclose(f);
     free(buf);

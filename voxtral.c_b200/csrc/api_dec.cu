@@ -74,6 +74,7 @@ extern "C" vox_cuda_state_t *vox_cuda_state_create_ex(vox_cuda_model_t *m, int k
         const char *env = getenv("VOX_CUDA_DEC_GRAPH");
         s->use_graph_steps = (env && atoi(env)) ? 1 : 0;
         if (s->use_graph_steps && s->kv16) { vox_set_error("state_create: fp16 K/V needs the default (persistent kernel) engine"); goto fail; }
+        if (s->use_graph_steps && m->q8) { vox_set_error("state_create: a Q8 model needs the default (persistent kernel) engine"); goto fail; }
     }
     s->alt_n = 1;
     if (dec_mega_init(s)) goto fail;
@@ -407,10 +408,12 @@ static int ensure_pf(vox_cuda_state *s) {
     return 0;
 }
 
-static TcEpilogue pf_epi(float *of, long ldf, uint16_t *ob, long ldb, int flags, long split_off = 0) {
+static TcEpilogue pf_epi(float *of, long ldf, uint16_t *ob, long ldb, int flags, long split_off = 0,
+                         const float *col_scale = nullptr) {
     TcEpilogue t;
     t.out_f32 = of; t.ldo_f32 = ldf; t.out_bf16 = ob; t.ldo_bf16 = ldb; t.bias = nullptr; t.flags = flags;
     t.split_off = split_off;
+    t.col_scale = col_scale;             // Q8 model: row scales of the quantised matrix, else null
     return t;
 }
 
@@ -433,6 +436,7 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
     uint16_t *att_b = (uint16_t *)gu;     // [PF_ROWS][2*4096]   (gu is unused in this mode)
     uint16_t *hh_b = (uint16_t *)hh;      // [PF_ROWS][2*9216]
     const bool tcm = !prefill_f32_mode();
+    if (!tcm && m->q8) { vox_set_error("prefill: VOX_CUDA_PREFILL_F32 is not available for a Q8 model"); return -1; }
     for (int r0 = 0; r0 < seq_len; r0 += PF_ROWS) {
         const int M = seq_len - r0 < PF_ROWS ? seq_len - r0 : PF_ROWS;
         float *x = x_dev + (size_t)r0 * DEC_DIM;
@@ -445,7 +449,7 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
             if (tcm) {
                 if (rows_rmsnorm_bf16(st, x, DEC_DIM, L.attn_norm, nullptr, xn_b, 2 * DEC_DIM, M, DEC_DIM, 1)) return -1;
                 if (gemm_tc(st, M, DEC_QKV, DEC_DIM, 2 * DEC_DIM, xn_b, 2 * DEC_DIM, L.wqkv,
-                            pf_epi(qkv, DEC_QKV, nullptr, 0, TC_OUT_F32))) return -1;
+                            pf_epi(qkv, DEC_QKV, nullptr, 0, TC_OUT_F32, 0, L.s_wqkv))) return -1;
             } else {
                 if (rows_rmsnorm(st, x, DEC_DIM, L.attn_norm, nullptr, xn, DEC_DIM, M, DEC_DIM)) return -1;
                 if (sgemm_bf16w(st, M, DEC_QKV, DEC_DIM, xn, DEC_DIM, L.wqkv, qkv, DEC_QKV, nullptr, EPI_NONE)) return -1;
@@ -457,12 +461,12 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
             if (tcm) {
                 if (f32_to_bf16_rows(st, att, DEC_QDIM, att_b, 2 * DEC_QDIM, M, DEC_QDIM, 1)) return -1;
                 if (gemm_tc(st, M, DEC_DIM, DEC_QDIM, 2 * DEC_QDIM, att_b, 2 * DEC_QDIM, L.wo,
-                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL))) return -1;
+                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL, 0, L.s_wo))) return -1;
                 if (rows_rmsnorm_bf16(st, x, DEC_DIM, L.ffn_norm, ada, xn_b, 2 * DEC_DIM, M, DEC_DIM, 1)) return -1;
                 if (gemm_tc(st, M, 2 * DEC_HIDDEN, DEC_DIM, 2 * DEC_DIM, xn_b, 2 * DEC_DIM, L.w13,
-                            pf_epi(nullptr, 0, hh_b, 2 * DEC_HIDDEN, TC_SWIGLU | TC_OUT_BF16 | TC_OUT_SPLIT, DEC_HIDDEN))) return -1;
+                            pf_epi(nullptr, 0, hh_b, 2 * DEC_HIDDEN, TC_SWIGLU | TC_OUT_BF16 | TC_OUT_SPLIT, DEC_HIDDEN, L.s_w13))) return -1;
                 if (gemm_tc(st, M, DEC_DIM, DEC_HIDDEN, 2 * DEC_HIDDEN, hh_b, 2 * DEC_HIDDEN, L.w2,
-                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL))) return -1;
+                            pf_epi(x, DEC_DIM, nullptr, 0, TC_RESIDUAL, 0, L.s_w2))) return -1;
             } else {
                 if (sgemm_bf16w(st, M, DEC_DIM, DEC_QDIM, att, DEC_QDIM, L.wo, x, DEC_DIM, nullptr, EPI_RESIDUAL)) return -1;
                 if (rows_rmsnorm(st, x, DEC_DIM, L.ffn_norm, ada, xn, DEC_DIM, M, DEC_DIM)) return -1;
@@ -528,9 +532,18 @@ extern "C" int vox_cuda_decoder_prefill(vox_cuda_state_t *s, const float *x, int
 __global__ void __launch_bounds__(256) embed_rows_kernel(const int *__restrict__ tokens,
                                                          const float *__restrict__ adapter,
                                                          const uint16_t *__restrict__ tok_emb,
+                                                         const int8_t *__restrict__ q_tok_emb,
+                                                         const float *__restrict__ s_tok_emb,
                                                          float *__restrict__ x) {
     const int r = blockIdx.x;
     const float *a = adapter + (size_t)r * DEC_DIM;
+    if (q_tok_emb) {                      // Q8: embedding row = q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
+        const int8_t *e = q_tok_emb + (size_t)tokens[r] * DEC_DIM;
+        const float sc = s_tok_emb[tokens[r]];
+        for (int i = threadIdx.x; i < DEC_DIM; i += 256)
+            x[(size_t)r * DEC_DIM + i] = a[i] + (float)e[i] * sc;
+        return;
+    }
     const uint16_t *e = tok_emb + (size_t)tokens[r] * DEC_DIM;
     for (int i = threadIdx.x; i < DEC_DIM; i += 256)
         x[(size_t)r * DEC_DIM + i] = a[i] + __uint_as_float(((uint32_t)e[i]) << 16);
@@ -551,7 +564,7 @@ extern "C" int vox_cuda_decoder_prefill_fused(vox_cuda_state_t *s, const int *to
     int rc = -1;
     if (cudaMemcpyAsync(td, tokens, (size_t)seq_len * 4, cudaMemcpyHostToDevice, s->stream) == cudaSuccess) {
         embed_rows_kernel<<<seq_len, 256, 0, s->stream>>>(td, s->adapter_buf + (size_t)phys * DEC_DIM,
-                                                          s->m->tok_emb, xd);
+                                                          s->m->tok_emb, s->m->q_tok_emb, s->m->s_tok_emb, xd);
         LAUNCHED();
         rc = prefill_device(s, xd, seq_len);
     }

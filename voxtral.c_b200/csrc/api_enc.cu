@@ -198,6 +198,7 @@ static int enc_precise_mode(void) {
 }
 
 static int enc_layers(vox_cuda_state *s, float *x, int M, float *out) {
+    if (enc_precise_mode() && s->m->q8) { vox_set_error("encoder: VOX_CUDA_ENC_PRECISE is not available for a Q8 model"); return -1; }
     if (enc_precise_mode()) return enc_layers_precise(s, x, M, out);
     return (M <= 128 && enc_small_mode()) ? enc_layers_small(s, x, M, out) : enc_layers_fast(s, x, M, out);
 }
@@ -205,7 +206,7 @@ static int enc_layers(vox_cuda_state *s, float *x, int M, float *out) {
 // ---- adapter (vox_adapter_forward, voxtral_encoder.c:699-737) -----------------------
 static int adapter_device(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *mid, float *out) {
     vox_cuda_model *m = s->m;
-    if (!enc_precise_mode()) return adapter_fast(s, enc_rows, k_tokens, out);
+    if (!enc_precise_mode() || m->q8) return adapter_fast(s, enc_rows, k_tokens, out);
     if (sgemm_bf16w(s->stream, k_tokens, DEC_DIM, 4 * ENC_DIM, enc_rows, 4 * ENC_DIM, m->adapter_w0, mid,
                     DEC_DIM, nullptr, EPI_GELU)) return -1;
     return sgemm_bf16w(s->stream, k_tokens, DEC_DIM, DEC_DIM, mid, DEC_DIM, m->adapter_w1, out, DEC_DIM,

@@ -119,6 +119,7 @@ extern "C" vox_cuda_group_t *vox_cuda_group_create_ex(vox_cuda_model_t *m, int n
         vox_set_error("group_create: need 1..%d streams, max_positions >= 2, kv_bits 32 or 16", MAX_STREAMS);
         return nullptr;
     }
+    if (m->q8) { vox_set_error("group_create: stream groups do not take a Q8 model (single-stream decoder only)"); return nullptr; }
     vox_cuda_group *g = (vox_cuda_group *)calloc(1, sizeof(vox_cuda_group));
     if (!g) return nullptr;
     g->m = m; g->B = n_streams; g->max_pos = max_positions; g->kv16 = kv_bits == 16;

@@ -48,8 +48,9 @@ constexpr int PART_LD = DEC_HD + 4;         // acc[128], m, l, pad (16-byte rows
 constexpr int MAX_SPLITS = 32;
 constexpr int KMAX = DEC_HIDDEN;            // longest activation vector (w2 input)
 
-template <int K> struct TileRows { static constexpr int v = STAGE_BYTES / (K * 2); };
+template <int K, int EB = 2> struct TileRows { static constexpr int v = STAGE_BYTES / (K * EB); };   // EB = bytes per weight
 static_assert(TileRows<3072>::v == 4 && TileRows<4096>::v == 3 && TileRows<9216>::v == 1, "");
+static_assert(TileRows<3072, 1>::v == 8 && TileRows<4096, 1>::v == 6 && TileRows<9216, 1>::v == 2, "");
 
 // Activation vector of the current phase, split so that lane l reads conflict-free
 // float4s: xa[c] = x[8c..8c+3], xb[c] = x[8c+4..8c+7].  The attention phase (which
@@ -75,6 +76,15 @@ struct Smem {
     float resid[64];                        // residual values of the rows this CTA owns in wo / w2
     float altv[CW][4];                      // per-warp top-4 text logits of the vocabulary phase (--alt)
     int alti[CW][4];
+};
+
+// Q8 weights (vox_cuda_model_create_q8): the activation vector of a phase as four planes of unsigned 8-bit digits
+// (see prep_digits) and the int32 partial sums of a row group.  Only the Q8 instantiations allocate this part.
+constexpr int QDIG = 4;                     // digit planes: 32-bit offset-binary fixed point
+constexpr int QPLANE = KMAX + 64;           // plane pitch in bytes (+64: the four planes start in different banks)
+struct SmemQ : Smem {
+    alignas(16) unsigned char dig[QDIG][QPLANE];
+    int partq[2][GROWS][QDIG][CW];
 };
 
 struct Top4 {
@@ -111,6 +121,9 @@ struct Params {
     const DecLayerDev *layers;              // device array [n_dec]
     int n_dec;
     const uint16_t *tok_emb;
+    const int8_t *q_tok_emb;                // Q8 model: int8 rows, row scales, row sums of the tied embedding / LM head
+    const float *s_tok_emb;
+    const int *qs_tok_emb;
     const float *dec_norm, *ada_scale, *inv_freq;
     void *kv_k, *kv_v;                      // rings of float or __half rows (kernel template parameter KV)
     float *x, *q, *attn_part, *h, *logits, *blockmax;
@@ -267,15 +280,15 @@ __device__ __forceinline__ void cta_rows(int R, int unit, int c, int G, int &r0,
 // tile g lives in ring stage g % NSTAGE during mbarrier phase (g / NSTAGE) & 1.
 
 // ---- producer ----------------------------------------------------------------------
-template <int K>
-__device__ __forceinline__ void produce(Smem &sm, unsigned &g, const uint16_t *W, int R, int unit, int c, int G,
+template <int K, int EB = 2>
+__device__ __forceinline__ void produce(Smem &sm, unsigned &g, const void *W, int R, int unit, int c, int G,
                                         unsigned long long policy, unsigned inflight, unsigned *err) {
-    constexpr int TR = TileRows<K>::v;
+    constexpr int TR = TileRows<K, EB>::v;
     int r0, r1;
     cta_rows(R, unit, c, G, r0, r1);
     for (int r = r0; r < r1; r += TR, g++) {
         const int n = min(TR, r1 - r);
-        const unsigned bytes = (unsigned)n * K * 2u;
+        const unsigned bytes = (unsigned)n * K * (unsigned)EB;
         const unsigned stage = g % NSTAGE, ph = (g / NSTAGE) & 1u;
         mbar_wait(&sm.empty[stage], ph ^ 1u, err, 0x80000000u | g);
         if (g >= inflight) {
@@ -285,7 +298,7 @@ __device__ __forceinline__ void produce(Smem &sm, unsigned &g, const uint16_t *W
             mbar_wait(&sm.full[f % NSTAGE], (f / NSTAGE) & 1u, err, 0x40000000u | g);
         }
         mbar_expect_tx(&sm.full[stage], bytes);
-        bulk_g2s(sm.ring[stage], W + (size_t)r * K, bytes, &sm.full[stage], policy);
+        bulk_g2s(sm.ring[stage], reinterpret_cast<const unsigned char *>(W) + (size_t)r * K * EB, bytes, &sm.full[stage], policy);
         sm.issued = g + 1;
     }
 }
@@ -430,6 +443,168 @@ __device__ __forceinline__ void consume(Smem &sm, unsigned &g0, int &pbuf, int R
                     for (int k = 0; k < CW; k++) v0 += sm.part[pbuf][lane][k];
                     epi(rbase + lane, v0, 0.f);
                 }
+            }
+        }
+        pbuf ^= 1;
+    }
+    g0 += (unsigned)n_tiles;
+}
+
+// ---- Q8 consumers: int8 weight tiles on the integer tensor cores --------------------------------------
+// q8_matvec_fused (/root/reference/voxtral_kernels.c:277-310): y[n] = (sum_k q[n][k] x[k]) * scale[n].
+// The activation vector is turned into 32-bit fixed point ONCE per phase (prep_digits): X[k] = rint(x[k] 2^(30-e)) with
+// 2^e > max|x|, stored offset-binary (U = X + 2^31) as four planes of unsigned bytes.  A weight tile then needs no
+// conversion at all: mma.sync.m16n8k32.s32.u8.s8 takes the digit planes as its A rows (4 of 16 used) and 8 weight
+// rows straight from the shared-memory tile as its B columns, int32 accumulation is exact, and per row
+//     sum_k q x = 2^(e-30) (D0 + 2^8 D1 + 2^16 D2 + 2^24 D3 - 2^31 sum_k q[k])       D_j = sum_k q[k] u_j[k]
+// in 64-bit integers - the only rounding of the whole dot product is X itself (2^-30 of the vector's maximum; the
+// reference's sequential fp32 sum carries more).  ~30 instructions per thread per 24 KB tile instead of ~180 for
+// an unpack + FFMA loop over twice the weights of a bf16 tile.
+template <int K> struct GroupTilesQ { static constexpr int v = (K == 9216) ? 8 : 2; };
+
+__device__ __forceinline__ void imma_u8s8(int (&d)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+    const uint32_t z = 0u;               // A rows 8..15 are not used
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a0), "r"(z), "r"(a2), "r"(z), "r"(b0), "r"(b1));
+}
+
+// Digit planes of this phase's activation vector.  xr = the lane's slice in the layout of load_slice (element
+// 4j + i of xr is x[j*1024 + col0 + i]); dg[sp] = the 16 digits of plane (lane >> 2) that this lane feeds to the two
+// MMAs of step pair sp (k = (sp*8 + w)*64 + (lane & 3)*16 .. +15: the same bytes it reads of every weight row).
+template <int K>
+__device__ __forceinline__ void prep_digits(SmemQ &sm, const float (&xr)[K / 256], int col0, uint4 (&dg)[K / 512],
+                                            float &unit_scale) {
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float mx = 0.f;
+    #pragma unroll
+    for (int i = 0; i < K / 256; i++) mx = fmaxf(mx, fabsf(xr[i]));
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    consumer_sync();                       // previous readers of red[] and of the digit planes are done
+    if (lane == 0) sm.red[w] = mx;
+    consumer_sync();
+    #pragma unroll
+    for (int k = 0; k < CW; k++) mx = fmaxf(mx, sm.red[k]);
+    // 2^e > max|x| (e = biased exponent - 126), clamped so that both scale factors are normal numbers
+    int e = (int)((__float_as_uint(mx) >> 23) & 255u) - 126;
+    e = max(-90, min(e, 96));
+    const float up = __uint_as_float((unsigned)(127 + 30 - e) << 23);       // 2^(30-e)
+    unit_scale = __uint_as_float((unsigned)(127 + e - 30) << 23);           // 2^(e-30)
+    #pragma unroll
+    for (int j = 0; j < K / 1024; j++) {
+        uint32_t u[4];
+        #pragma unroll
+        for (int i = 0; i < 4; i++) u[i] = (uint32_t)__float2int_rn(xr[4 * j + i] * up) ^ 0x80000000u;
+        // 4 x 4 byte transpose: plane p gets byte p of the four words
+        const uint32_t t0 = __byte_perm(u[0], u[1], 0x5140), t1 = __byte_perm(u[2], u[3], 0x5140);
+        const uint32_t t2 = __byte_perm(u[0], u[1], 0x7362), t3 = __byte_perm(u[2], u[3], 0x7362);
+        const int k = j * 1024 + col0;
+        *reinterpret_cast<uint32_t *>(&sm.dig[0][k]) = __byte_perm(t0, t1, 0x5410);
+        *reinterpret_cast<uint32_t *>(&sm.dig[1][k]) = __byte_perm(t0, t1, 0x7632);
+        *reinterpret_cast<uint32_t *>(&sm.dig[2][k]) = __byte_perm(t2, t3, 0x5410);
+        *reinterpret_cast<uint32_t *>(&sm.dig[3][k]) = __byte_perm(t2, t3, 0x7632);
+    }
+    consumer_sync();
+    const int m = lane >> 2, cq = lane & 3;
+    #pragma unroll
+    for (int sp = 0; sp < K / 512; sp++)
+        dg[sp] = (m < QDIG) ? *reinterpret_cast<const uint4 *>(&sm.dig[m & (QDIG - 1)][(sp * 8 + w) * 64 + cq * 16])
+                            : make_uint4(0u, 0u, 0u, 0u);
+}
+
+// Same contract as consume<>: epi(row, v0, v1) by one lane per output row (pair).  scale / rowsum are indexed by the
+// matrix row; unit_scale = 2^(e-30) of prep_digits.
+template <int K, bool PAIR, typename Epi>
+__device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, int R, int unit, int c, int G,
+                                           const uint4 (&dg)[K / 512], float unit_scale, const float *__restrict__ scale,
+                                           const int *__restrict__ rowsum, unsigned *err, long long &t_wait, Epi epi) {
+    constexpr int TR = TileRows<K, 1>::v, GT = GroupTilesQ<K>::v, SP = K / 512;
+    static_assert(GT * TR <= GROWS && TR <= 8, "");
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, rq = lane >> 2, cq = lane & 3;
+    int r0, r1;
+    cta_rows(R, unit, c, G, r0, r1);
+    const int n_tiles = (r1 - r0 + TR - 1) / TR;
+    int grp = 0;
+    for (int tg = 0; tg < n_tiles; tg += GT, grp++) {
+        // scale and row sum of the row(s) this lane would finish, requested before the group's tiles are multiplied: the
+        // epilogue warp must not sit in an L2 round trip while the other seven wait for it at the next group
+        const int rbase = r0 + tg * TR;
+        const int rows = min(r1 - rbase, GT * TR);
+        const int er = PAIR ? 2 * lane : lane;
+        float esc[2] = {0.f, 0.f};
+        int ers[2] = {0, 0};
+        if (er < rows) {
+            esc[0] = __ldg(scale + rbase + er); ers[0] = __ldg(rowsum + rbase + er);
+            if (PAIR) { esc[1] = __ldg(scale + rbase + er + 1); ers[1] = __ldg(rowsum + rbase + er + 1); }
+        }
+        #pragma unroll
+        for (int ti = 0; ti < GT; ti++) {
+            const int t = tg + ti;
+            if (t >= n_tiles) break;                       // uniform across the CTA
+            const unsigned g = g0 + (unsigned)t;
+            const unsigned stage = g % NSTAGE, ph = (g / NSTAGE) & 1u;
+            if (MK_PROF) {
+                const long long tw = clock64();
+                mbar_wait(&sm.full[stage], ph, err, g);
+                t_wait += clock64() - tw;
+            } else {
+                mbar_wait(&sm.full[stage], ph, err, g);
+            }
+            // lane (rq, cq) holds 16 consecutive weights of row rq per step pair; rows beyond the tile's row count read
+            // whatever the stage holds - their products land in columns nobody reads
+            const unsigned char *tp = sm.ring[stage] + (size_t)rq * K + w * 64 + cq * 16;
+            // the tile's weights go to registers in batches of <= 9 step pairs (72 registers for K = 9216 would not
+            // leave room for the digit registers); the stage is released once the last batch has been read
+            constexpr int SB = SP > 9 ? 9 : SP;
+            static_assert(SP % SB == 0, "");
+            // NCH independent accumulator chains: a single chain of 12-36 dependent MMAs is bound by the MMA latency
+            constexpr int NCH = 4;
+            int dch[NCH][4];
+            #pragma unroll
+            for (int ch = 0; ch < NCH; ch++) { dch[ch][0] = dch[ch][1] = dch[ch][2] = dch[ch][3] = 0; }
+            #pragma unroll
+            for (int b0 = 0; b0 < SP; b0 += SB) {
+                uint4 wv[SB];
+                #pragma unroll
+                for (int sp = 0; sp < SB; sp++)
+                    wv[sp] = (rq < TR) ? *reinterpret_cast<const uint4 *>(tp + (b0 + sp) * 512) : make_uint4(0u, 0u, 0u, 0u);
+                if (b0 + SB == SP) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.empty[stage]);  // release orders the loads above before the refill
+                }
+                #pragma unroll
+                for (int sp = 0; sp < SB; sp++) {
+                    imma_u8s8(dch[(2 * sp) % NCH], dg[b0 + sp].x, dg[b0 + sp].y, wv[sp].x, wv[sp].y);
+                    imma_u8s8(dch[(2 * sp + 1) % NCH], dg[b0 + sp].z, dg[b0 + sp].w, wv[sp].z, wv[sp].w);
+                }
+            }
+            int d[2];
+            d[0] = (dch[0][0] + dch[1][0]) + (dch[2][0] + dch[3][0]);
+            d[1] = (dch[0][1] + dch[1][1]) + (dch[2][1] + dch[3][1]);
+            // d[0], d[1] = digit plane rq (< QDIG) x tile rows 2cq, 2cq + 1, this warp's K-slice
+            if (rq < QDIG) {
+                if (2 * cq < TR) sm.partq[pbuf][ti * TR + 2 * cq][rq][w] = d[0];
+                if (2 * cq + 1 < TR) sm.partq[pbuf][ti * TR + 2 * cq + 1][rq][w] = d[1];
+            }
+        }
+        consumer_sync();
+        auto row_value = [&](int lr, float sc, int rs) -> float {
+            long long y = 0;
+            #pragma unroll
+            for (int j = QDIG - 1; j >= 0; j--) {
+                const int4 a = *reinterpret_cast<const int4 *>(&sm.partq[pbuf][lr][j][0]);
+                const int4 b = *reinterpret_cast<const int4 *>(&sm.partq[pbuf][lr][j][4]);
+                const int dj = a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;      // |.| <= K * 128 * 255 < 2^31
+                y = (y << 8) + (long long)dj;
+            }
+            y -= (long long)rs << 31;
+            return __ll2float_rn(y) * unit_scale * sc;
+        };
+        if (w == (grp & (CW - 1))) {                        // epilogue duty rotates over the warps
+            if (PAIR) {
+                if (lane < (rows >> 1)) epi(rbase + er, row_value(er, esc[0], ers[0]), row_value(er + 1, esc[1], ers[1]));
+            } else {
+                if (lane < rows) epi(rbase + er, row_value(er, esc[0], ers[0]), 0.f);
             }
         }
         pbuf ^= 1;
@@ -679,10 +854,12 @@ __device__ __forceinline__ void norm_slice(Smem &sm, float (&xr)[DEC_DIM / 256],
     }
 }
 
-template <typename KV>
+// KV = element type of the K/V rings; Q8 = the weights are int8 rows + row scales (vox_cuda_model_create_q8)
+template <typename KV, bool Q8>
 __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
+    SmemQ &smq = *reinterpret_cast<SmemQ *>(smem_raw);      // the digit planes exist in the Q8 instantiations only
     const int tid = threadIdx.x;
     const int c = blockIdx.x, G = gridDim.x;
 
@@ -700,7 +877,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     if (tid >= CT) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         // =========================== PRODUCER ===========================
-        if (tid == CT + 32 && P.l2_ahead > 0) {
+        if (!Q8 && tid == CT + 32 && P.l2_ahead > 0) {
             unsigned fg = 0;
             for (int step = 0; step < P.n_steps; step++) {
                 for (int l = 0; l < n_dec; l++) {
@@ -720,12 +897,13 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         for (int step = 0; step < P.n_steps; step++) {
             for (int l = 0; l < n_dec; l++) {
                 const DecLayerDev L = P.layers[l];
-                produce<DEC_DIM>(sm, pg, L.wqkv, DEC_QKV, 2, c, G, policy, (unsigned)P.inflight, P.err);
-                produce<DEC_QDIM>(sm, pg, L.wo, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
-                produce<DEC_DIM>(sm, pg, L.w13, 2 * DEC_HIDDEN, 2, c, G, policy, (unsigned)P.inflight, P.err);
-                produce<DEC_HIDDEN>(sm, pg, L.w2, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
+                constexpr int EB = Q8 ? 1 : 2;
+                produce<DEC_DIM, EB>(sm, pg, Q8 ? (const void *)L.q_wqkv : (const void *)L.wqkv, DEC_QKV, 2, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_QDIM, EB>(sm, pg, Q8 ? (const void *)L.q_wo : (const void *)L.wo, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_DIM, EB>(sm, pg, Q8 ? (const void *)L.q_w13 : (const void *)L.w13, 2 * DEC_HIDDEN, 2, c, G, policy, (unsigned)P.inflight, P.err);
+                produce<DEC_HIDDEN, EB>(sm, pg, Q8 ? (const void *)L.q_w2 : (const void *)L.w2, DEC_DIM, 1, c, G, policy, (unsigned)P.inflight, P.err);
             }
-            produce<DEC_DIM>(sm, pg, P.tok_emb, VOCAB, 1, c, G, policy, (unsigned)P.inflight, P.err);
+            produce<DEC_DIM, Q8 ? 1 : 2>(sm, pg, Q8 ? (const void *)P.q_tok_emb : (const void *)P.tok_emb, VOCAB, 1, c, G, policy, (unsigned)P.inflight, P.err);
         }
         return;
     }
@@ -807,8 +985,14 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                         if (use_host_embed) v = __ldcg(reinterpret_cast<const float4 *>(P.embed_in + col));
                         else {
                             v = __ldcg(reinterpret_cast<const float4 *>(P.adapter + (size_t)adapter_index * DEC_DIM + col));
-                            const uint2 e = *reinterpret_cast<const uint2 *>(P.tok_emb + (size_t)prev_token * DEC_DIM + col);
-                            v.x += bf16_lo(e.x); v.y += bf16_hi(e.x); v.z += bf16_lo(e.y); v.w += bf16_hi(e.y);
+                            if constexpr (Q8) {     // embedding row = q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
+                                const char4 e = *reinterpret_cast<const char4 *>(P.q_tok_emb + (size_t)prev_token * DEC_DIM + col);
+                                const float sc = __ldg(P.s_tok_emb + prev_token);
+                                v.x += (float)e.x * sc; v.y += (float)e.y * sc; v.z += (float)e.z * sc; v.w += (float)e.w * sc;
+                            } else {
+                                const uint2 e = *reinterpret_cast<const uint2 *>(P.tok_emb + (size_t)prev_token * DEC_DIM + col);
+                                v.x += bf16_lo(e.x); v.y += bf16_hi(e.x); v.z += bf16_lo(e.y); v.w += bf16_hi(e.y);
+                            }
                         }
                         if (c == 0) *reinterpret_cast<float4 *>(P.x + col) = v;
                         xr[4 * j] = v.x; xr[4 * j + 1] = v.y; xr[4 * j + 2] = v.z; xr[4 * j + 3] = v.w;
@@ -818,9 +1002,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                     ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 }
                 norm_slice(sm, xr, ss, L.attn_norm, nullptr, col0);
-                t_pro += clock64() - tp;
-                consume<DEC_DIM, true>(sm, gt, pbuf, DEC_QKV, 2, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float v1) {
+                auto epi_qkv = [&](int row, float v0, float v1) {
                         if (row < DEC_QDIM + DEC_KVDIM) {
                             const int d = (row & (DEC_HD - 1)) >> 1;
                             const float cs = sm.rope[2 * d], sn = sm.rope[2 * d + 1];
@@ -830,7 +1012,17 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                         if (row < DEC_QDIM) *reinterpret_cast<float2 *>(P.q + row) = make_float2(v0, v1);
                         else if (row < DEC_QDIM + DEC_KVDIM) st_kv2(kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM), v0, v1);
                         else st_kv2(vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM), v0, v1);
-                    });
+                    };
+                if constexpr (Q8) {
+                    uint4 dg[DEC_DIM / 512];
+                    float us;
+                    prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                    t_pro += clock64() - tp;
+                    consume_q8<DEC_DIM, true>(smq, gt, pbuf, DEC_QKV, 2, c, G, dg, us, L.s_wqkv, L.qs_wqkv, P.err, t_wait, epi_qkv);
+                } else {
+                    t_pro += clock64() - tp;
+                    consume<DEC_DIM, true>(sm, gt, pbuf, DEC_QKV, 2, c, G, xr, P.err, t_wait, epi_qkv);
+                }
             }
             // q / k / v rows of this CTA are written: tell the attention CTAs of the kv heads they belong to
             layer_phases += 1u;
@@ -857,9 +1049,17 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_QDIM / 256];
                 (void)load_slice<DEC_QDIM>(P.attn, col0, xr);     // rows merged by the last split of each kv head
-                t_pro += clock64() - tp;
-                consume<DEC_QDIM, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
+                auto epi_res = [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; };
+                if constexpr (Q8) {
+                    uint4 dg[DEC_QDIM / 512];
+                    float us;
+                    prep_digits<DEC_QDIM>(smq, xr, col0, dg, us);
+                    t_pro += clock64() - tp;
+                    consume_q8<DEC_QDIM, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_wo, L.qs_wo, P.err, t_wait, epi_res);
+                } else {
+                    t_pro += clock64() - tp;
+                    consume<DEC_QDIM, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait, epi_res);
+                }
             }
             MK_GRID_SYNC();
             // ---------------- phase 4: rmsnorm * (1 + ada) -> w1|w3 -> SwiGLU ----------------
@@ -868,9 +1068,17 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 float xr[DEC_DIM / 256];
                 const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
-                t_pro += clock64() - tp;
-                consume<DEC_DIM, true>(sm, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float v1) { P.h[row >> 1] = silu(v0) * v1; });
+                auto epi_glu = [&](int row, float v0, float v1) { P.h[row >> 1] = silu(v0) * v1; };
+                if constexpr (Q8) {
+                    uint4 dg[DEC_DIM / 512];
+                    float us;
+                    prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                    t_pro += clock64() - tp;
+                    consume_q8<DEC_DIM, true>(smq, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, dg, us, L.s_w13, L.qs_w13, P.err, t_wait, epi_glu);
+                } else {
+                    t_pro += clock64() - tp;
+                    consume<DEC_DIM, true>(sm, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, xr, P.err, t_wait, epi_glu);
+                }
             }
             MK_GRID_SYNC();
             // ---------------- phase 5: w2 -> residual ----------------
@@ -879,9 +1087,17 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_HIDDEN / 256];
                 (void)load_slice<DEC_HIDDEN>(P.h, col0, xr);
-                t_pro += clock64() - tp;
-                consume<DEC_HIDDEN, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; });
+                auto epi_res = [&](int row, float v0, float) { P.x[row] = sm.resid[row - rr0] + v0; };
+                if constexpr (Q8) {
+                    uint4 dg[DEC_HIDDEN / 512];
+                    float us;
+                    prep_digits<DEC_HIDDEN>(smq, xr, col0, dg, us);
+                    t_pro += clock64() - tp;
+                    consume_q8<DEC_HIDDEN, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_w2, L.qs_w2, P.err, t_wait, epi_res);
+                } else {
+                    t_pro += clock64() - tp;
+                    consume<DEC_HIDDEN, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait, epi_res);
+                }
             }
             MK_GRID_SYNC();
         }
@@ -891,20 +1107,27 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             float xr[DEC_DIM / 256];
             const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
             norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
-            t_pro += clock64() - tp;
             float bv = -INFINITY;
             int bi = 0x7fffffff;
             Top4 top;
             top.clear();
-            if (P.alt_on)
-                consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float) {
+            auto epi_alt = [&](int row, float v0, float) {
                         P.logits[row] = v0; argmax_merge(bv, bi, v0, row);
                         if (row >= 1000) top.insert(v0, row);            // TOKEN_TEXT_MIN, voxtral.c:399,986
-                    });
-            else
-                consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait,
-                    [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); });
+                    };
+            auto epi_max = [&](int row, float v0, float) { P.logits[row] = v0; argmax_merge(bv, bi, v0, row); };
+            if constexpr (Q8) {
+                uint4 dg[DEC_DIM / 512];
+                float us;
+                prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                t_pro += clock64() - tp;
+                if (P.alt_on) consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_alt);
+                else consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_max);
+            } else {
+                t_pro += clock64() - tp;
+                if (P.alt_on) consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait, epi_alt);
+                else consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait, epi_max);
+            }
             if (P.alt_on) {
                 top.merge_warp();
                 if (lane == 0) {
@@ -1014,11 +1237,18 @@ int dec_mega_init(vox_cuda_state *s) {
     int dev = 0, sms = 0, occ = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)sizeof(mk::Smem)));
-    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)sizeof(mk::Smem)));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float>, mk::NT, sizeof(mk::Smem)));
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(mk::SmemQ)));
+    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(mk::SmemQ)));
+    if (s->m->q8)
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float, true>, mk::NT, sizeof(mk::SmemQ)));
+    else
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float, false>, mk::NT, sizeof(mk::Smem)));
     if (occ < 1 || sms < 8) { vox_set_error("dec_mega: kernel does not fit (occupancy %d, %d SMs)", occ, sms); return -1; }
     h->grid = sms;
     h->barriers_per_step = 3 * s->m->n_dec + 1;       // after wo, w1|w3, w2 of every layer + after the logits
@@ -1074,7 +1304,8 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     vox_cuda_model *m = s->m;
     mk::Params P;
     P.layers = h->d_layers; P.n_dec = m->n_dec;
-    P.tok_emb = m->tok_emb; P.dec_norm = m->dec_norm; P.ada_scale = m->ada_scale; P.inv_freq = m->inv_freq_dec;
+    P.tok_emb = m->tok_emb; P.q_tok_emb = m->q_tok_emb; P.s_tok_emb = m->s_tok_emb; P.qs_tok_emb = m->qs_tok_emb;
+    P.dec_norm = m->dec_norm; P.ada_scale = m->ada_scale; P.inv_freq = m->inv_freq_dec;
     P.kv_k = s->kv16 ? (void *)s->kv_k16 : (void *)s->kv_k; P.kv_v = s->kv16 ? (void *)s->kv_v16 : (void *)s->kv_v;
     P.attn = s->d_attn; P.attn_cnt = h->d_bar + 8;
     P.x = s->d_x; P.q = s->d_q; P.attn_part = s->d_attn_part; P.h = s->d_h; P.logits = s->d_logits;
@@ -1085,9 +1316,10 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
     P.bar = h->d_bar; P.bar_base = h->bar_count; P.n_steps = n_steps; P.inflight = h->inflight; P.l2_ahead = h->l2_ahead; P.spin_ns = h->spin_ns; P.err = h->d_err; P.prof = h->d_prof;
     CUDA_TRY(cudaMemsetAsync(h->d_bar + 8, 0, mk::SYNC_WORDS * sizeof(unsigned), s->stream));   // hand-over counters start at 0
     void *args[] = {&P};
-    const void *fn = s->kv16 ? (const void *)mk::dec_mega_kernel<__half> : (const void *)mk::dec_mega_kernel<float>;
+    const void *fn = m->q8 ? (s->kv16 ? (const void *)mk::dec_mega_kernel<__half, true> : (const void *)mk::dec_mega_kernel<float, true>)
+                           : (s->kv16 ? (const void *)mk::dec_mega_kernel<__half, false> : (const void *)mk::dec_mega_kernel<float, false>);
     CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(h->grid), dim3(mk::NT), args,
-                                         sizeof(mk::Smem), s->stream));
+                                         m->q8 ? sizeof(mk::SmemQ) : sizeof(mk::Smem), s->stream));
     h->bar_count += (unsigned)h->grid * (unsigned)h->barriers_per_step * (unsigned)n_steps;
     LAUNCHED();
     return 0;

@@ -499,6 +499,7 @@ extern "C" void vox_cuda_tp_free(vox_cuda_tp_t *tp) {
 
 // One rank of a world of `world` processes (one per GPU).  Peers are attached with export / connect.
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int world) {
+    if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
     vox_cuda_tp *tp = tp_alloc(m, world);
     if (!tp) return nullptr;
     if (rank < 0 || rank >= world) { vox_set_error("tp: rank %d outside world %d", rank, world); vox_cuda_tp_free(tp); return nullptr; }
@@ -519,6 +520,7 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
 // arithmetic, the exchange windows and the sequence numbers are those of the multi-GPU run, so one GPU is
 // enough to check them (tests/test_gpu_tp.py).  Not a fast path: every kernel is launched `world` times.
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create_local(vox_cuda_model_t *m, int world) {
+    if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
     vox_cuda_tp *tp = tp_alloc(m, world);
     if (!tp) return nullptr;
     for (int i = 0; i < world; i++) {

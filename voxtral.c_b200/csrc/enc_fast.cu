@@ -95,10 +95,12 @@ void enc_fast_free(vox_cuda_state *s) {
     e->fast = nullptr;
 }
 
-static TcEpilogue epi(float *of, long ldf, uint16_t *ob, long ldb, const float *bias, int flags, long split_off = 0) {
+static TcEpilogue epi(float *of, long ldf, uint16_t *ob, long ldb, const float *bias, int flags, long split_off = 0,
+                      const float *col_scale = nullptr) {
     TcEpilogue t;
     t.out_f32 = of; t.ldo_f32 = ldf; t.out_bf16 = ob; t.ldo_bf16 = ldb; t.bias = bias; t.flags = flags;
     t.split_off = split_off;
+    t.col_scale = col_scale;             // Q8 model: row scales of the quantised matrix, else null
     return t;
 }
 
@@ -119,16 +121,16 @@ int enc_layers_fast(vox_cuda_state *s, float *x, int M, float *out) {
         float *kc = e->kv_k + l * kv_layer, *vc = e->kv_v + l * kv_layer;
         if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.attn_norm, nullptr, f->xn_b, (1 + s_qkv) * ENC_DIM, M, ENC_DIM, s_qkv)) return -1;
         if (gemm_tc(st, M, 3 * ENC_QKV, ENC_DIM, (1 + s_qkv) * ENC_DIM, f->xn_b, (1 + s_qkv) * ENC_DIM, L.wqkv,
-                    epi(e->qkv, 3 * ENC_QKV, nullptr, 0, L.bqkv, TC_BIAS | TC_OUT_F32))) return -1;
+                    epi(e->qkv, 3 * ENC_QKV, nullptr, 0, L.bqkv, TC_BIAS | TC_OUT_F32, 0, L.s_wqkv))) return -1;
         if (rows_rope_kv(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc)) return -1;
         if (enc_attention_terms(s, e->qkv, kc, vc, M, pos0, f->att_b, (1 + s_wo) * ENC_QKV, s_wo, s_att ? 3 : 1)) return -1;
         if (gemm_tc(st, M, ENC_DIM, ENC_QKV, (1 + s_wo) * ENC_QKV, f->att_b, (1 + s_wo) * ENC_QKV, L.wo,
-                    epi(x, ENC_DIM, nullptr, 0, L.bo, TC_BIAS | TC_RESIDUAL))) return -1;
+                    epi(x, ENC_DIM, nullptr, 0, L.bo, TC_BIAS | TC_RESIDUAL, 0, L.s_wo))) return -1;
         if (rows_rmsnorm_bf16(st, x, ENC_DIM, L.ffn_norm, nullptr, f->xn_b, (1 + s_w13) * ENC_DIM, M, ENC_DIM, s_w13)) return -1;
         if (gemm_tc(st, M, 2 * ENC_HIDDEN, ENC_DIM, (1 + s_w13) * ENC_DIM, f->xn_b, (1 + s_w13) * ENC_DIM, L.w13,
-                    epi(nullptr, 0, f->hh_b, (1 + s_w2) * ENC_HIDDEN, nullptr, TC_SWIGLU | TC_OUT_BF16 | (s_w2 ? TC_OUT_SPLIT : 0), ENC_HIDDEN))) return -1;
+                    epi(nullptr, 0, f->hh_b, (1 + s_w2) * ENC_HIDDEN, nullptr, TC_SWIGLU | TC_OUT_BF16 | (s_w2 ? TC_OUT_SPLIT : 0), ENC_HIDDEN, L.s_w13))) return -1;
         if (gemm_tc(st, M, ENC_DIM, ENC_HIDDEN, (1 + s_w2) * ENC_HIDDEN, f->hh_b, (1 + s_w2) * ENC_HIDDEN, L.w2,
-                    epi(x, ENC_DIM, nullptr, 0, L.b2, TC_BIAS | TC_RESIDUAL))) return -1;
+                    epi(x, ENC_DIM, nullptr, 0, L.b2, TC_BIAS | TC_RESIDUAL, 0, L.s_w2))) return -1;
     }
     if (rows_rmsnorm(st, x, ENC_DIM, m->enc_norm, nullptr, out, ENC_DIM, M, ENC_DIM)) return -1;
     e->pos += M;
@@ -146,9 +148,9 @@ int adapter_fast(vox_cuda_state *s, const float *enc_rows, int k_tokens, float *
     const int K0 = 4 * ENC_DIM;
     if (f32_to_bf16_rows(st, enc_rows, K0, f->enc_b, mul * K0, k_tokens, K0, sp)) return -1;
     if (gemm_tc(st, k_tokens, DEC_DIM, K0, mul * K0, f->enc_b, mul * K0, m->adapter_w0,
-                epi(nullptr, 0, f->mid_b, mul * DEC_DIM, nullptr, TC_GELU | TC_OUT_BF16 | (sp ? TC_OUT_SPLIT : 0), DEC_DIM))) return -1;
+                epi(nullptr, 0, f->mid_b, mul * DEC_DIM, nullptr, TC_GELU | TC_OUT_BF16 | (sp ? TC_OUT_SPLIT : 0), DEC_DIM, m->s_adapter0))) return -1;
     return gemm_tc(st, k_tokens, DEC_DIM, DEC_DIM, mul * DEC_DIM, f->mid_b, mul * DEC_DIM, m->adapter_w1,
-                   epi(out, DEC_DIM, nullptr, 0, nullptr, TC_OUT_F32));
+                   epi(out, DEC_DIM, nullptr, 0, nullptr, TC_OUT_F32, 0, m->s_adapter1));
 }
 
 // ---- small-M path (streaming chunks: M <= 128 new positions per call) -----------------------------
@@ -342,6 +344,7 @@ static int small_graph_mode(void) {
 int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
     EncState *e = (EncState *)s->enc_priv;
     if (x1_mask()) return enc_layers_fast(s, x, M, out);       // single-bf16 products live on the large-tile path only
+    if (s->m->q8) return enc_layers_fast(s, x, M, out);        // Q8 row scales are applied in the large-tile epilogue only
     if (!fast_get(s)) return -1;
     const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
     EncSmall *q = small_get(s, NB);

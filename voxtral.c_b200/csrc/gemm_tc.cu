@@ -62,6 +62,7 @@ struct KParams {
     long ldo_bf16;
     const float *bias;
     int flags;
+    const float *col_scale;
 };
 
 // bf16 store of NV consecutive values; TC_OUT_SPLIT adds the rounding residual lo = bf16(v - hi)
@@ -88,6 +89,13 @@ __device__ __forceinline__ void epilogue_row(const KParams &p, int row, int col,
     float v[32];
     #pragma unroll
     for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+    if (p.col_scale) {
+        #pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+            const float4 s = *reinterpret_cast<const float4 *>(p.col_scale + col + i);
+            v[i] *= s.x; v[i + 1] *= s.y; v[i + 2] *= s.z; v[i + 3] *= s.w;
+        }
+    }
     if (p.flags & TC_BIAS) {
         #pragma unroll
         for (int i = 0; i < 32; i += 4) {
@@ -306,7 +314,7 @@ static int gemm_tc_impl(cudaStream_t st, int M, int N, int K, int KA, const uint
     p.lo_sep = A_lo ? 1 : 0;
     p.M = M; p.N = N; p.K = KA; p.Kw = K; p.split_off = epi.split_off;
     p.out_f32 = epi.out_f32; p.ldo_f32 = epi.ldo_f32; p.out_bf16 = epi.out_bf16; p.ldo_bf16 = epi.ldo_bf16;
-    p.bias = epi.bias; p.flags = epi.flags;
+    p.bias = epi.bias; p.flags = epi.flags; p.col_scale = epi.col_scale;
     const int total = (N / BN) * mt;
     const int grid = total < g_sms ? total : g_sms;
     if (BN == 256) CUDA_TRY(launch_pdl(tc::gemm_tc_kernel<256>, grid, tc::NT, tc::Cfg<256>::SMEM_BYTES, st, ma, mlo, mb, p));

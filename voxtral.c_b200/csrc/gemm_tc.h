@@ -21,6 +21,9 @@ struct TcEpilogue {
     const float *bias;
     int flags;
     long split_off;     // TC_OUT_SPLIT: lo part goes to out_bf16[row][split_off + col]
+    // Q8 weights: W holds the int8 values as bf16 and the product is multiplied by col_scale[n] (the row scale of the
+    // quantised matrix, voxtral_kernels.c:277-310) before bias / activation; null = plain bf16 weights
+    const float *col_scale = nullptr;
 };
 
 // A: device bf16 [M rows, K] with row stride lda (elements; rows may overlap: lda < K is allowed,

@@ -26,6 +26,13 @@ struct DecLayerDev {
     const uint16_t *w2;     // [3072,9216]
     const float *attn_norm; // [3072]
     const float *ffn_norm;  // [3072]
+    // Q8 model (vox_cuda_model_create_q8): the bf16 matrices above hold the int8 values exactly (|q| <= 128) for the
+    // M > 1 tensor-core products, s_* are the per-row scales in the merged row order (applied in the epilogue),
+    // q_* the int8 rows themselves for the single-token kernel, qs_* = sum_k q[row][k] (offset-binary correction,
+    // dec_mega.cu).  All null for a bf16 model.
+    const float *s_wqkv, *s_wo, *s_w13, *s_w2;
+    const int8_t *q_wqkv, *q_wo, *q_w13, *q_w2;
+    const int *qs_wqkv, *qs_wo, *qs_w13, *qs_w2;
 };
 
 struct EncLayerDev {
@@ -38,6 +45,7 @@ struct EncLayerDev {
     const float *b2;        // [1280]
     const float *attn_norm; // [1280]
     const float *ffn_norm;  // [1280]
+    const float *s_wqkv, *s_wo, *s_w13, *s_w2;   // Q8 model: per-row scales (merged row order), else null
 };
 
 struct vox_cuda_model {
@@ -48,7 +56,12 @@ struct vox_cuda_model {
     size_t arena_bytes;
     DecLayerDev dec[VOX_CUDA_DEC_LAYERS];
     EncLayerDev enc[VOX_CUDA_ENC_LAYERS];
-    const uint16_t *tok_emb;   // [131072,3072]
+    const uint16_t *tok_emb;   // [131072,3072] (null for a Q8 model)
+    int q8;                    // 1: created by vox_cuda_model_create_q8
+    const int8_t *q_tok_emb;   // [131072,3072] int8
+    const float *s_tok_emb;    // [131072]
+    const int *qs_tok_emb;     // [131072] row sums of q
+    const float *s_adapter0, *s_adapter1;   // [3072] each
     const float *dec_norm;     // [3072]
     float *ada_scale;          // [n_dec,3072]
     const float *enc_norm;     // [1280]

@@ -62,21 +62,48 @@ static void fill_weights(const vox_ctx_t *c, vox_cuda_weights_t *w) {
     w->ada_scale = c->ada_scale;
 }
 
+/* Q8 checkpoint (ctx->use_q8, voxtral.c:175-181): the *_weight_q8 / *_scale_q8 pairs the loaders took straight from
+ * the mmap (voxtral_encoder.c:94-110, voxtral_decoder.c:109-125, voxtral.c:113-120) */
+static void fill_weights_q8(const vox_ctx_t *c, vox_cuda_weights_q8_t *q) {
+    memset(q, 0, sizeof(*q));
+#define Q8BIND(dst, src) do { (dst).q = (src##_weight_q8); (dst).scale = (src##_scale_q8); } while (0)
+    for (int i = 0; i < VOX_ENC_LAYERS; i++) {
+        const vox_enc_layer_t *l = &c->encoder.layers[i];
+        vox_cuda_layer_q8_t *d = &q->enc[i];
+        Q8BIND(d->wq, l->wq); Q8BIND(d->wk, l->wk); Q8BIND(d->wv, l->wv); Q8BIND(d->wo, l->wo);
+        Q8BIND(d->w1, l->w1); Q8BIND(d->w2, l->w2); Q8BIND(d->w3, l->w3);
+    }
+    Q8BIND(q->adapter_w0, c->adapter.linear0); Q8BIND(q->adapter_w1, c->adapter.linear1);
+    q->tok_embeddings.q = c->decoder.tok_embeddings_q8;
+    q->tok_embeddings.scale = c->decoder.tok_embeddings_scale_q8;
+    for (int i = 0; i < VOX_DEC_LAYERS; i++) {
+        const vox_dec_layer_t *l = &c->decoder.layers[i];
+        vox_cuda_layer_q8_t *d = &q->dec[i];
+        Q8BIND(d->wq, l->wq); Q8BIND(d->wk, l->wk); Q8BIND(d->wv, l->wv); Q8BIND(d->wo, l->wo);
+        Q8BIND(d->w1, l->w1); Q8BIND(d->w2, l->w2); Q8BIND(d->w3, l->w3);
+    }
+#undef Q8BIND
+}
+
 int vox_cuda_dropin_load(vox_ctx_t *ctx) {
     if (!vox_cuda_init()) { complain("vox_cuda_init"); return -1; }
-    if (!ctx->decoder.tok_embeddings_bf16) {
-        fprintf(stderr, "voxtral (CUDA): this build reads bf16 checkpoints only (no Q8 path)\n");
-        return -1;
-    }
     slot_t *s = find(NULL);
     for (int i = 0; i < 8 && !s; i++) if (!g_slots[i].ctx) s = &g_slots[i];
     if (!s) { fprintf(stderr, "voxtral (CUDA): too many contexts\n"); return -1; }
     vox_cuda_weights_t *w = (vox_cuda_weights_t *)malloc(sizeof(*w));
     if (!w) return -1;
     fill_weights(ctx, w);
-    s->model = vox_cuda_model_create(w);
+    if (ctx->use_q8) {
+        vox_cuda_weights_q8_t *q = (vox_cuda_weights_q8_t *)malloc(sizeof(*q));
+        if (!q) { free(w); return -1; }
+        fill_weights_q8(ctx, q);
+        s->model = vox_cuda_model_create_q8(w, q);
+        free(q);
+    } else {
+        s->model = vox_cuda_model_create(w);
+    }
     free(w);
-    if (!s->model) { complain("vox_cuda_model_create"); return -1; }
+    if (!s->model) { complain(ctx->use_q8 ? "vox_cuda_model_create_q8" : "vox_cuda_model_create"); return -1; }
     s->state = vox_cuda_state_create(s->model);
     if (!s->state) { complain("vox_cuda_state_create"); vox_cuda_model_free(s->model); s->model = NULL; return -1; }
     s->ctx = ctx;

@@ -192,6 +192,12 @@ vox_b200_ctx *vox_b200_load(const char *model_dir) {
     c->data = c->map + 8 + hlen;
     c->map_bytes -= 8 + (size_t)hlen;              /* offsets are relative to the data section */
 
+    if (memmem(c->json, c->json_len, "\"dtype\":\"Q8\"", 12)) {
+        /* Q8 containers reach the backend through vox_cuda_model_create_q8 - bound by the drop-in host
+         * (dropin/vox_cuda_dropin.c, the reference's own loader) and by hostmodel.py; this small host reads bf16 only */
+        fprintf(stderr, "vox_b200_load: %s is a Q8 container - use voxtral_cuda (make dropin) for Q8 checkpoints\n", path);
+        goto fail;
+    }
     vox_cuda_weights_t *w = &c->w;
     w->n_enc_layers = count_layers(c, ENC_PREFIX ".transformer.layers.%d.attention.wq.weight", VOX_CUDA_ENC_LAYERS);
     w->n_dec_layers = count_layers(c, "layers.%d.attention.wq.weight", VOX_CUDA_DEC_LAYERS);

@@ -2,7 +2,11 @@
 /root/reference/voxtral.c:131-184): mmap consolidated.safetensors, hand bf16
 matrices to the CUDA backend as pointers into the mapping, convert the small
 tensors to f32, precompute ada_scale (voxtral.c:31-80).  Used by bench.py and
-the tests; the C host in host/ does the same for the CLI."""
+the tests; the C host in host/ does the same for the CLI.
+
+A Q8 container (dtype "Q8" = [rows x f32 scale][rows x cols int8], /root/reference/quantize.py:111-129,
+loader voxtral_safetensors.c:393-410,453-468) is detected from the file: the matrices go to the backend as
+(int8 rows, scales) pointer pairs (vox_cuda_weights_q8_t), everything else is F32 in such a file."""
 import ctypes as C
 import json
 import mmap
@@ -39,7 +43,15 @@ class HostModel:
         self.keep = []
         self.n_enc = sum(1 for k in self.header if k.endswith("attention.wq.weight") and k.startswith(ENC))
         self.n_dec = sum(1 for k in self.header if k.endswith("attention.wq.weight") and k.startswith("layers."))
+        self.q8 = self.header["layers.0.attention.wq.weight"]["dtype"] == "Q8"      # ctx->use_q8, voxtral.c:175-176
+        self.weights_q8 = vc.WeightsQ8() if self.q8 else None
         self.weights = self._build(delay_tokens)
+
+    def create_model(self, L):
+        """vox_cuda_model_create / _create_q8, whichever the file calls for"""
+        if self.q8:
+            return L.vox_cuda_model_create_q8(C.byref(self.weights), C.byref(self.weights_q8))
+        return L.vox_cuda_model_create(C.byref(self.weights))
 
     def u16(self, name):
         t = self.header[name]
@@ -48,9 +60,43 @@ class HostModel:
         return self.raw[self.base + a:self.base + b].view(np.uint16)
 
     def f32(self, name):
-        arr = np.ascontiguousarray(bf16_to_f32(self.u16(name)))
+        t = self.header[name]
+        if t["dtype"] == "F32":
+            a, b = t["data_offsets"]
+            arr = np.ascontiguousarray(self.raw[self.base + a:self.base + b].view(np.float32))
+        else:
+            arr = np.ascontiguousarray(bf16_to_f32(self.u16(name)))
         self.keep.append(arr)
         return arr
+
+    def q8_parts(self, name):
+        """(int8 [rows, cols], f32 scales [rows]) views of a Q8 tensor"""
+        t = self.header[name]
+        assert t["dtype"] == "Q8", name
+        rows, cols = t["shape"]
+        a, b = t["data_offsets"]
+        assert b - a == rows * 4 + rows * cols
+        sc = self.raw[self.base + a:self.base + a + rows * 4].view(np.float32)
+        q = self.raw[self.base + a + rows * 4:self.base + b].view(np.int8).reshape(rows, cols)
+        return q, sc
+
+    def dense_f32(self, name):
+        """a small matrix as fp32, whatever the container (safetensors_get_f32, voxtral_safetensors.c:362-410)"""
+        t = self.header[name]
+        if t["dtype"] == "Q8":
+            q, sc = self.q8_parts(name)
+            return q.astype(np.float32) * sc[:, None]
+        if t["dtype"] == "F32":
+            return self.f32(name).reshape(t["shape"])
+        return bf16_to_f32(self.u16(name)).reshape(t["shape"])
+
+    def _mat(self, holder, field, holder_q8, name):
+        """bind one 2-D matrix: bf16 pointer, or the (int8, scale) pair in the Q8 table"""
+        if self.q8:
+            q, sc = self.q8_parts(name)
+            setattr(holder_q8, field, vc.Q8(C.cast(q.ctypes.data, vc.i8p), C.cast(sc.ctypes.data, vc.f32p)))
+        else:
+            setattr(holder, field, self._p16(name))
 
     def _p16(self, name):
         a = self.u16(name)
@@ -67,13 +113,14 @@ class HostModel:
         t_cond = np.concatenate([np.cos(emb), np.sin(emb)]).astype(np.float32)
         out = np.empty((self.n_dec, 3072), np.float32)
         for l in range(self.n_dec):
-            down = bf16_to_f32(self.u16(f"layers.{l}.ada_rms_norm_t_cond.0.weight")).reshape(32, 3072)
-            up = bf16_to_f32(self.u16(f"layers.{l}.ada_rms_norm_t_cond.2.weight")).reshape(3072, 32)
+            down = self.dense_f32(f"layers.{l}.ada_rms_norm_t_cond.0.weight").reshape(32, 3072)
+            up = self.dense_f32(f"layers.{l}.ada_rms_norm_t_cond.2.weight").reshape(3072, 32)
             out[l] = up @ gelu_tanh(down @ t_cond)
         return out
 
     def _build(self, delay_tokens):
         w = vc.Weights()
+        q = self.weights_q8
         w.n_enc_layers, w.n_dec_layers = self.n_enc, self.n_dec
         w.conv0_weight = self._p32(f"{ENC}.conv_layers.0.conv.weight")
         w.conv0_bias = self._p32(f"{ENC}.conv_layers.0.conv.bias")
@@ -81,10 +128,11 @@ class HostModel:
         w.conv1_bias = self._p32(f"{ENC}.conv_layers.1.conv.bias")
         for i in range(self.n_enc):
             p, d = f"{ENC}.transformer.layers.{i}.", w.enc[i]
+            dq = q.enc[i] if q is not None else None
             for n in ("wq", "wk", "wv", "wo"):
-                setattr(d, n, self._p16(p + f"attention.{n}.weight"))
+                self._mat(d, n, dq, p + f"attention.{n}.weight")
             for n in ("w1", "w2", "w3"):
-                setattr(d, n, self._p16(p + f"feed_forward.{n}.weight"))
+                self._mat(d, n, dq, p + f"feed_forward.{n}.weight")
             d.wq_bias = self._p32(p + "attention.wq.bias")
             d.wv_bias = self._p32(p + "attention.wv.bias")
             d.wo_bias = self._p32(p + "attention.wo.bias")
@@ -92,15 +140,16 @@ class HostModel:
             d.attention_norm = self._p32(p + "attention_norm.weight")
             d.ffn_norm = self._p32(p + "ffn_norm.weight")
         w.enc_norm = self._p32(f"{ENC}.transformer.norm.weight")
-        w.adapter_w0 = self._p16("mm_streams_embeddings.embedding_module.audio_language_projection.0.weight")
-        w.adapter_w1 = self._p16("mm_streams_embeddings.embedding_module.audio_language_projection.2.weight")
-        w.tok_embeddings = self._p16("mm_streams_embeddings.embedding_module.tok_embeddings.weight")
+        self._mat(w, "adapter_w0", q, "mm_streams_embeddings.embedding_module.audio_language_projection.0.weight")
+        self._mat(w, "adapter_w1", q, "mm_streams_embeddings.embedding_module.audio_language_projection.2.weight")
+        self._mat(w, "tok_embeddings", q, "mm_streams_embeddings.embedding_module.tok_embeddings.weight")
         for i in range(self.n_dec):
             p, d = f"layers.{i}.", w.dec[i]
+            dq = q.dec[i] if q is not None else None
             for n in ("wq", "wk", "wv", "wo"):
-                setattr(d, n, self._p16(p + f"attention.{n}.weight"))
+                self._mat(d, n, dq, p + f"attention.{n}.weight")
             for n in ("w1", "w2", "w3"):
-                setattr(d, n, self._p16(p + f"feed_forward.{n}.weight"))
+                self._mat(d, n, dq, p + f"feed_forward.{n}.weight")
             d.attention_norm = self._p32(p + "attention_norm.weight")
             d.ffn_norm = self._p32(p + "ffn_norm.weight")
         w.dec_norm = self._p32("norm.weight")

@@ -40,6 +40,22 @@ class Weights(C.Structure):
                 ("dec", DecLayerW * DEC_LAYERS), ("dec_norm", f32p), ("ada_scale", f32p)]
 
 
+i8p = C.POINTER(C.c_int8)
+
+
+class Q8(C.Structure):                      # vox_cuda_q8_t
+    _fields_ = [("q", i8p), ("scale", f32p)]
+
+
+class LayerQ8(C.Structure):                 # vox_cuda_layer_q8_t
+    _fields_ = [(n, Q8) for n in ("wq", "wk", "wv", "wo", "w1", "w2", "w3")]
+
+
+class WeightsQ8(C.Structure):               # vox_cuda_weights_q8_t
+    _fields_ = [("enc", LayerQ8 * ENC_LAYERS), ("adapter_w0", Q8), ("adapter_w1", Q8), ("tok_embeddings", Q8),
+                ("dec", LayerQ8 * DEC_LAYERS)]
+
+
 _lib = None
 
 # name -> (restype, argtypes); also the list the CPU test checks against the header
@@ -52,6 +68,8 @@ SIGNATURES = {
     "vox_cuda_launch_count": (C.c_ulonglong, []),
     "vox_cuda_bench_encoder": (C.c_float, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_model_create": (C.c_void_p, [C.POINTER(Weights)]),
+    "vox_cuda_model_create_q8": (C.c_void_p, [C.POINTER(Weights), C.POINTER(WeightsQ8)]),
+    "vox_cuda_model_is_q8": (C.c_int, [C.c_void_p]),
     "vox_cuda_model_set_ada_scale": (C.c_int, [C.c_void_p, f32p]),
     "vox_cuda_model_free": (None, [C.c_void_p]),
     "vox_cuda_state_create": (C.c_void_p, [C.c_void_p]),
