@@ -18,6 +18,8 @@ mode (log-mel -> conv stem -> 32-layer encoder -> adapter -> 38-token prefill ->
             own vox_stream_feed/finish produced for this clip (tests/golden/ids_clip60.npz)
   stream / full_window  BASELINE configs 3 and 4 measured live: ms per 50- and 200-frame encoder
             call (-I 0.5 / -I 2.0) and ms per token at the full 8192-key window
+  q8        SURVEY 8(f3): the same clip on the Q8 container of the same weights (int8 rows + row scales): host PCM -> ids
+            throughput, ms per token and HBM fraction on the Q8 bytes, ids compared with the reference's Q8 CPU path
 
 `--impl reference` times the reference's own CPU implementation (oracle/_ref,
 all host threads) on a bounded sample of the same workload.
@@ -39,6 +41,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 CLIP_SECONDS = 60.0
 DEC_BYTES_PER_TOKEN = 26 * 232783872 + 805306368
+Q8_ROWS_PER_TOKEN = 26 * (6144 + 3072 + 18432 + 3072) + 131072
+Q8_BYTES_PER_TOKEN = DEC_BYTES_PER_TOKEN // 2 + 8 * Q8_ROWS_PER_TOKEN   # int8 rows + fp32 scale + int32 row sum per row
 ENC_FLOP_PER_POSITION = 2.15e9                     # linear 1.929 + attention <= 0.197 + stem + adapter
 METRIC = "audio_seconds_per_second"
 WORKLOAD = ("60s synthetic clip per GPU, batch mode (log-mel -> conv stem -> 32-layer encoder -> adapter -> 38-row prefill -> "
@@ -250,6 +254,38 @@ def run_cuda(args, rank, world):
                                   "clip_ids_equal_fp32_kv": int((ids16 == toks_e2e[:n16]).sum()) if n16 == n_tok else None,
                                   "clip_steps": int(n16)}
         L.vox_cuda_state_free(st16)
+    # ---- SURVEY 8(f3) leg: the same clip on the Q8 container of the same weights (gen_model --q8 = the reference's
+    # quantize.py); ids compared with the reference's own Q8 CPU path (tests/golden/ids_clip60_q8.npz) ----
+    q8_leg = None
+    if rank == 0 and not args.no_extra and not args.no_q8:
+        hq = hostmodel.HostModel(rh.model_dir(extra=("--q8",)))
+        mq = vc.check(hq.create_model(L), "model_create_q8")
+        sq = vc.check(L.vox_cuda_state_create(mq), "state_create")
+        tq = np.empty(max_tok, np.int32)
+
+        def one_q8():
+            return vc.check(L.vox_cuda_transcribe(sq, vc.fptr(pinned), len(buf), nf, PROMPT_LEN, vc.iptr(tq), max_tok, None), "transcribe")
+
+        nq = one_q8()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            nq = one_q8()
+        tq_s = (time.perf_counter() - t0) / args.steps
+        ids_q8 = tq[:nq].copy()
+        vc.check(L.vox_cuda_decoder_set_position(sq, 38, 38), "set_position")
+        ms_q8 = float(L.vox_cuda_bench_decoder_steps(sq, 32, 38, nq, None))
+        gq = os.path.join(ROOT, "tests", "golden", "ids_clip60_q8.npz")
+        par = None
+        if args.clip_seconds == CLIP_SECONDS and os.path.exists(gq):
+            wq = np.load(gq)["ids"]
+            par = bool(len(wq) == nq and np.array_equal(wq, ids_q8))
+        q8_leg = {"e2e": {"value": args.clip_seconds / tq_s, "unit": UNIT, "ms_per_step": 1e3 * tq_s},
+                  "ms_per_token": ms_q8, "bytes_per_token": Q8_BYTES_PER_TOKEN,
+                  "hbm_gbs": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9, "frac": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9 / peak_hbm(),
+                  "parity_ids": par, "ids_equal_bf16_run": int((ids_q8 == toks_e2e[:nq]).sum()) if nq == n_tok else None,
+                  "api": "vox_cuda_model_create_q8 + vox_cuda_transcribe(host PCM) -> ids; reference = its Q8 CPU path"}
+        L.vox_cuda_state_free(sq)
+        L.vox_cuda_model_free(mq)
     # ---- config 5 leg: S independent clips per GPU through a stream group (lock-step decode, one pass
     # over the weights per step); host PCM in, token ids out, inside the timed region ----
     multi = None
@@ -404,6 +440,8 @@ def run_cuda(args, rank, world):
             line["stream"] = stream_leg
         if full_window is not None:
             line["full_window"] = full_window
+        if q8_leg is not None:
+            line["q8"] = q8_leg
         if not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(mdir)
         line["config"] = {"workload": WORKLOAD if args.clip_seconds == CLIP_SECONDS else f"{args.clip_seconds:g}s clip (profiling run)",
@@ -479,6 +517,7 @@ def main():
     ap.add_argument("--streams", type=int, default=64,
                     help="streams per GPU of the multi-stream leg (BASELINE config 5: 64 independent clips); 0 = skip")
     ap.add_argument("--no-extra", action="store_true", help="skip the stream / full-window legs and check one group slot only")
+    ap.add_argument("--no-q8", action="store_true", help="skip the Q8 leg (second checkpoint, SURVEY 8 f3)")
     ap.add_argument("--no-tp", action="store_true", help="skip the tensor-parallel decode leg of an N > 1 run")
     ap.add_argument("--clip-seconds", type=float, default=CLIP_SECONDS, help="profiling only; the headline is 60 s")
     args = ap.parse_args()

@@ -168,6 +168,19 @@ __global__ void __launch_bounds__(256) q8_expand_kernel(const int8_t *__restrict
     }
 }
 
+// In place: swap the two 64-byte halves of every 128 bytes on odd rows (the layout dec_mega.cu's Q8 consumers and the
+// embedding gathers expect: q8_swz).  One CTA per odd row.
+__global__ void __launch_bounds__(256) q8_swizzle_kernel(int8_t *__restrict__ q, size_t K) {
+    const size_t r = 2 * (size_t)blockIdx.x + 1;
+    uint4 *row = reinterpret_cast<uint4 *>(q + r * K);
+    for (size_t i = threadIdx.x; i < K / 32; i += blockDim.x) {          // i -> 16-byte unit (i % 4) of the even half of pair i / 4
+        const size_t a = (i / 4) * 8 + (i % 4), b = a + 4;
+        const uint4 t = row[a];
+        row[a] = row[b];
+        row[b] = t;
+    }
+}
+
 // One merged Q8 matrix being assembled: parts are copied to rows row0, row0 + step, ... of q / scale, then finish()
 // expands.  `q` lives in the arena when the single-token kernel streams it (decoder, vocabulary), else in `stage`.
 struct Q8Mat {
@@ -194,6 +207,7 @@ struct Q8Up {
     void finish(const Q8Mat &t) {
         if (u.dry || u.fail) return;
         q8_expand_kernel<<<(unsigned)t.R, 256>>>(t.q, t.K, t.bf, t.qs);
+        if (t.qs) q8_swizzle_kernel<<<(unsigned)(t.R / 2), 256>>>(t.q, t.K);   // kept int8 rows: the single-token kernel's layout
         if (cudaDeviceSynchronize() != cudaSuccess) u.fail = 1;      // the staging buffer is reused by the next matrix
     }
 };

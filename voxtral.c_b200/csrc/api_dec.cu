@@ -540,8 +540,9 @@ __global__ void __launch_bounds__(256) embed_rows_kernel(const int *__restrict__
     if (q_tok_emb) {                      // Q8: embedding row = q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
         const int8_t *e = q_tok_emb + (size_t)tokens[r] * DEC_DIM;
         const float sc = s_tok_emb[tokens[r]];
+        const int swz = (tokens[r] & 1) << 6;             // odd rows: 64-byte halves swapped (q8_swizzle_kernel, api_core.cu)
         for (int i = threadIdx.x; i < DEC_DIM; i += 256)
-            x[(size_t)r * DEC_DIM + i] = a[i] + (float)e[i] * sc;
+            x[(size_t)r * DEC_DIM + i] = a[i] + (float)e[i ^ swz] * sc;
         return;
     }
     const uint16_t *e = tok_emb + (size_t)tokens[r] * DEC_DIM;

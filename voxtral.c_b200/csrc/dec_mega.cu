@@ -34,6 +34,9 @@ namespace mk {
 #ifndef MK_PROF
 #define MK_PROF 0                           // 1: per-tile wait timing of the consumers (VOX_CUDA_MEGA_PROF readout); `make prof`
 #endif
+#ifndef MK_Q8_TPW
+#define MK_Q8_TPW 0                         // Q8, K = 3072 / 4096 phases: 1 = tile-per-warp consumer (consume_q8_w), 0 = K-split (consume_q8)
+#endif
 #ifndef MK_NSTAGE
 #define MK_NSTAGE 6                         // ring depth: 4 / 6 / 8 stages measured 1.434 / 1.427 / 1.470 ms per token
 #endif
@@ -84,7 +87,7 @@ constexpr int QDIG = 4;                     // digit planes: 32-bit offset-binar
 constexpr int QPLANE = KMAX + 64;           // plane pitch in bytes (+64: the four planes start in different banks)
 struct SmemQ : Smem {
     alignas(16) unsigned char dig[QDIG][QPLANE];
-    int partq[2][GROWS][QDIG][CW];
+    int partq[2][QDIG][CW][GROWS];           // [buffer][digit plane][warp][row of the group]
 };
 
 struct Top4 {
@@ -471,7 +474,7 @@ __device__ __forceinline__ void imma_u8s8(int (&d)[4], uint32_t a0, uint32_t a2,
 // Digit planes of this phase's activation vector.  xr = the lane's slice in the layout of load_slice (element
 // 4j + i of xr is x[j*1024 + col0 + i]); dg[sp] = the 16 digits of plane (lane >> 2) that this lane feeds to the two
 // MMAs of step pair sp (k = (sp*8 + w)*64 + (lane & 3)*16 .. +15: the same bytes it reads of every weight row).
-template <int K>
+template <int K, bool WANT_DG>
 __device__ __forceinline__ void prep_digits(SmemQ &sm, const float (&xr)[K / 256], int col0, uint4 (&dg)[K / 512],
                                             float &unit_scale) {
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -505,11 +508,99 @@ __device__ __forceinline__ void prep_digits(SmemQ &sm, const float (&xr)[K / 256
         *reinterpret_cast<uint32_t *>(&sm.dig[3][k]) = __byte_perm(t2, t3, 0x7632);
     }
     consumer_sync();
-    const int m = lane >> 2, cq = lane & 3;
-    #pragma unroll
-    for (int sp = 0; sp < K / 512; sp++)
-        dg[sp] = (m < QDIG) ? *reinterpret_cast<const uint4 *>(&sm.dig[m & (QDIG - 1)][(sp * 8 + w) * 64 + cq * 16])
-                            : make_uint4(0u, 0u, 0u, 0u);
+    if (WANT_DG) {                         // K-split consumer (consume_q8): the lane's digits stay in registers
+        const int m = lane >> 2, cq = lane & 3;
+        #pragma unroll
+        for (int sp = 0; sp < K / 512; sp++)
+            dg[sp] = (m < QDIG) ? *reinterpret_cast<const uint4 *>(&sm.dig[m & (QDIG - 1)][(sp * 8 + w) * 64 + cq * 16])
+                                : make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+// Loads that must be issued where they are written (the compiler would otherwise sink them to their first use,
+// an L2 round trip in front of the epilogue)
+__device__ __forceinline__ float ldg_f32_now(const float *p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ int ldg_s32_now(const int *p) {
+    int v;
+    asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+// The int8 rows are stored with the two 64-byte halves of every 128 bytes swapped on odd rows (q8_swizzle_kernel,
+// api_core.cu): the 8 rows of a tile, whose pitch K is a multiple of 128, then spread over all 32 banks
+__device__ __forceinline__ int q8_swz(int row) { return (row & 1) << 6; }
+
+// Tile-per-warp consumer for K = 3072 / 4096: a warp multiplies every NSTAGE-th tile of the CTA's list on its own - all K
+// columns of the tile's <= 8 rows, digits read from the shared planes - so the GEMV phase has no CTA-wide barrier, no
+// partial-sum exchange and no shared epilogue duty: the row sums end in the warp that owns the tile (digit planes
+// combined with two 64-bit shuffles), lanes 0..3 finish rows (2c, 2c + 1).  The warp stands in for all CW arrivals
+// on the stage's `empty` barrier.  Up to NSTAGE tiles are in work by different warps at the same time.
+template <int K, bool PAIR, typename Epi>
+__device__ __forceinline__ void consume_q8_w(SmemQ &sm, unsigned &g0, int R, int unit, int c, int G, float unit_scale,
+                                             const float *__restrict__ scale, const int *__restrict__ rowsum,
+                                             unsigned *err, Epi epi) {
+    constexpr int TR = TileRows<K, 1>::v, NP = K / 64;
+    static_assert(TR <= 8 && (TR & 1) == 0, "");
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, rq = lane >> 2, cq = lane & 3;
+    int r0, r1;
+    cta_rows(R, unit, c, G, r0, r1);
+    const int n_tiles = (r1 - r0 + TR - 1) / TR;
+    const unsigned char *dp = &sm.dig[rq & (QDIG - 1)][cq * 16];
+    // Warp w owns ring stage w: it takes the tiles whose GLOBAL index is w (mod NSTAGE), so it sees every phase of
+    // that stage's mbarriers in turn.  (A parity wait may run at most one phase ahead of its barrier: a warp that
+    // skipped tiles of its stage would take the completion of an older tile for the one it waits for.)  Six warps
+    // multiply - more than the integer tensor pipe of one SM sustains - and warps 6, 7 have no tile in these phases.
+    constexpr int NWK = NSTAGE < CW ? NSTAGE : CW;
+    static_assert(NSTAGE <= CW, "a stage needs its own warp");
+    const int first = (int)(((unsigned)w + (unsigned)NSTAGE - g0 % (unsigned)NSTAGE) % (unsigned)NSTAGE);
+    for (int t = first; w < NWK && t < n_tiles; t += NSTAGE) {
+        const int row0 = r0 + t * TR;
+        const int n = min(TR, r1 - row0);
+        // scale / row sum of the two rows this lane may finish, in flight while the tile is multiplied
+        const int ea = min(row0 + 2 * cq, r1 - 1), eb = min(row0 + 2 * cq + 1, r1 - 1);
+        const float sc0 = ldg_f32_now(scale + ea), sc1 = ldg_f32_now(scale + eb);
+        const int rs0 = ldg_s32_now(rowsum + ea), rs1 = ldg_s32_now(rowsum + eb);
+        const unsigned g = g0 + (unsigned)t;
+        const unsigned stage = g % NSTAGE, ph = (g / NSTAGE) & 1u;
+        mbar_wait(&sm.full[stage], ph, err, g);
+        const int rr = min(rq, TR - 1);                     // lanes beyond the tile's rows re-read its last row (columns nobody uses)
+        const unsigned char *tp = sm.ring[stage] + (size_t)rr * K + cq * 16;
+        const int swz = q8_swz(row0 + rr);
+        int dch[4][4];
+        #pragma unroll
+        for (int ch = 0; ch < 4; ch++) { dch[ch][0] = dch[ch][1] = dch[ch][2] = dch[ch][3] = 0; }
+        #pragma unroll 8
+        for (int p = 0; p < NP; p++) {
+            const uint4 wv = *reinterpret_cast<const uint4 *>(tp + ((p * 64) ^ swz));
+            uint4 dv = make_uint4(0u, 0u, 0u, 0u);
+            if (rq < QDIG) dv = *reinterpret_cast<const uint4 *>(dp + p * 64);
+            imma_u8s8(dch[(2 * p) & 3], dv.x, dv.y, wv.x, wv.y);
+            imma_u8s8(dch[(2 * p + 1) & 3], dv.z, dv.w, wv.z, wv.w);
+        }
+        __syncwarp();
+        if (lane < CW) mbar_arrive(&sm.empty[stage]);       // release orders the loads above before the refill
+        // digit plane rq of rows 2cq, 2cq + 1 -> 64-bit sums over the planes (lanes 4m + cq, m < 4)
+        long long y0 = 0, y1 = 0;
+        if (rq < QDIG) {
+            y0 = (long long)((dch[0][0] + dch[1][0]) + (dch[2][0] + dch[3][0])) << (8 * rq);
+            y1 = (long long)((dch[0][1] + dch[1][1]) + (dch[2][1] + dch[3][1])) << (8 * rq);
+        }
+        y0 += __shfl_xor_sync(0xffffffffu, y0, 4); y1 += __shfl_xor_sync(0xffffffffu, y1, 4);
+        y0 += __shfl_xor_sync(0xffffffffu, y0, 8); y1 += __shfl_xor_sync(0xffffffffu, y1, 8);
+        if (rq == 0 && 2 * cq < n) {
+            const float v0 = __ll2float_rn(y0 - ((long long)rs0 << 31)) * unit_scale * sc0;
+            const float v1 = __ll2float_rn(y1 - ((long long)rs1 << 31)) * unit_scale * sc1;
+            if (PAIR) epi(row0 + 2 * cq, v0, v1);
+            else {
+                epi(row0 + 2 * cq, v0, 0.f);
+                if (2 * cq + 1 < n) epi(row0 + 2 * cq + 1, v1, 0.f);
+            }
+        }
+    }
+    g0 += (unsigned)n_tiles;
 }
 
 // Same contract as consume<>: epi(row, v0, v1) by one lane per output row (pair).  scale / rowsum are indexed by the
@@ -534,8 +625,8 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
         float esc[2] = {0.f, 0.f};
         int ers[2] = {0, 0};
         if (er < rows) {
-            esc[0] = __ldg(scale + rbase + er); ers[0] = __ldg(rowsum + rbase + er);
-            if (PAIR) { esc[1] = __ldg(scale + rbase + er + 1); ers[1] = __ldg(rowsum + rbase + er + 1); }
+            esc[0] = ldg_f32_now(scale + rbase + er); ers[0] = ldg_s32_now(rowsum + rbase + er);
+            if (PAIR) { esc[1] = ldg_f32_now(scale + rbase + er + 1); ers[1] = ldg_s32_now(rowsum + rbase + er + 1); }
         }
         #pragma unroll
         for (int ti = 0; ti < GT; ti++) {
@@ -550,9 +641,9 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
             } else {
                 mbar_wait(&sm.full[stage], ph, err, g);
             }
-            // lane (rq, cq) holds 16 consecutive weights of row rq per step pair; rows beyond the tile's row count read
-            // whatever the stage holds - their products land in columns nobody reads
-            const unsigned char *tp = sm.ring[stage] + (size_t)rq * K + w * 64 + cq * 16;
+            // lane (rq, cq) holds 16 consecutive weights of row rq per step pair
+            const int rr = min(rq, TR - 1);                // lanes beyond the tile's rows re-read its last row
+            const unsigned char *tp = sm.ring[stage] + (size_t)rr * K + ((w * 64) ^ q8_swz(r0 + t * TR + rr)) + cq * 16;
             // the tile's weights go to registers in batches of <= 9 step pairs (72 registers for K = 9216 would not
             // leave room for the digit registers); the stage is released once the last batch has been read
             constexpr int SB = SP > 9 ? 9 : SP;
@@ -567,7 +658,7 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
                 uint4 wv[SB];
                 #pragma unroll
                 for (int sp = 0; sp < SB; sp++)
-                    wv[sp] = (rq < TR) ? *reinterpret_cast<const uint4 *>(tp + (b0 + sp) * 512) : make_uint4(0u, 0u, 0u, 0u);
+                    wv[sp] = *reinterpret_cast<const uint4 *>(tp + (b0 + sp) * 512);
                 if (b0 + SB == SP) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sm.empty[stage]);  // release orders the loads above before the refill
@@ -583,8 +674,8 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
             d[1] = (dch[0][1] + dch[1][1]) + (dch[2][1] + dch[3][1]);
             // d[0], d[1] = digit plane rq (< QDIG) x tile rows 2cq, 2cq + 1, this warp's K-slice
             if (rq < QDIG) {
-                if (2 * cq < TR) sm.partq[pbuf][ti * TR + 2 * cq][rq][w] = d[0];
-                if (2 * cq + 1 < TR) sm.partq[pbuf][ti * TR + 2 * cq + 1][rq][w] = d[1];
+                if (2 * cq < TR) sm.partq[pbuf][rq][w][ti * TR + 2 * cq] = d[0];
+                if (2 * cq + 1 < TR) sm.partq[pbuf][rq][w][ti * TR + 2 * cq + 1] = d[1];
             }
         }
         consumer_sync();
@@ -592,9 +683,9 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
             long long y = 0;
             #pragma unroll
             for (int j = QDIG - 1; j >= 0; j--) {
-                const int4 a = *reinterpret_cast<const int4 *>(&sm.partq[pbuf][lr][j][0]);
-                const int4 b = *reinterpret_cast<const int4 *>(&sm.partq[pbuf][lr][j][4]);
-                const int dj = a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;      // |.| <= K * 128 * 255 < 2^31
+                int dj = 0;                                                       // |.| <= K * 128 * 255 < 2^31
+                #pragma unroll
+                for (int k = 0; k < CW; k++) dj += sm.partq[pbuf][j][k][lr];     // lanes = consecutive rows: no bank conflicts
                 y = (y << 8) + (long long)dj;
             }
             y -= (long long)rs << 31;
@@ -986,7 +1077,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                         else {
                             v = __ldcg(reinterpret_cast<const float4 *>(P.adapter + (size_t)adapter_index * DEC_DIM + col));
                             if constexpr (Q8) {     // embedding row = q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
-                                const char4 e = *reinterpret_cast<const char4 *>(P.q_tok_emb + (size_t)prev_token * DEC_DIM + col);
+                                const char4 e = *reinterpret_cast<const char4 *>(P.q_tok_emb + (size_t)prev_token * DEC_DIM + (col ^ q8_swz(prev_token)));
                                 const float sc = __ldg(P.s_tok_emb + prev_token);
                                 v.x += (float)e.x * sc; v.y += (float)e.y * sc; v.z += (float)e.z * sc; v.w += (float)e.w * sc;
                             } else {
@@ -1016,9 +1107,10 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
                     t_pro += clock64() - tp;
-                    consume_q8<DEC_DIM, true>(smq, gt, pbuf, DEC_QKV, 2, c, G, dg, us, L.s_wqkv, L.qs_wqkv, P.err, t_wait, epi_qkv);
+                    if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, DEC_QKV, 2, c, G, us, L.s_wqkv, L.qs_wqkv, P.err, epi_qkv);
+                    else consume_q8<DEC_DIM, true>(smq, gt, pbuf, DEC_QKV, 2, c, G, dg, us, L.s_wqkv, L.qs_wqkv, P.err, t_wait, epi_qkv);
                 } else {
                     t_pro += clock64() - tp;
                     consume<DEC_DIM, true>(sm, gt, pbuf, DEC_QKV, 2, c, G, xr, P.err, t_wait, epi_qkv);
@@ -1053,9 +1145,10 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_QDIM / 512];
                     float us;
-                    prep_digits<DEC_QDIM>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_QDIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
                     t_pro += clock64() - tp;
-                    consume_q8<DEC_QDIM, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_wo, L.qs_wo, P.err, t_wait, epi_res);
+                    if constexpr (MK_Q8_TPW) consume_q8_w<DEC_QDIM, false>(smq, gt, DEC_DIM, 1, c, G, us, L.s_wo, L.qs_wo, P.err, epi_res);
+                    else consume_q8<DEC_QDIM, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_wo, L.qs_wo, P.err, t_wait, epi_res);
                 } else {
                     t_pro += clock64() - tp;
                     consume<DEC_QDIM, false>(sm, gt, pbuf, DEC_DIM, 1, c, G, xr, P.err, t_wait, epi_res);
@@ -1072,9 +1165,10 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
                     t_pro += clock64() - tp;
-                    consume_q8<DEC_DIM, true>(smq, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, dg, us, L.s_w13, L.qs_w13, P.err, t_wait, epi_glu);
+                    if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, 2 * DEC_HIDDEN, 2, c, G, us, L.s_w13, L.qs_w13, P.err, epi_glu);
+                    else consume_q8<DEC_DIM, true>(smq, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, dg, us, L.s_w13, L.qs_w13, P.err, t_wait, epi_glu);
                 } else {
                     t_pro += clock64() - tp;
                     consume<DEC_DIM, true>(sm, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, xr, P.err, t_wait, epi_glu);
@@ -1091,7 +1185,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_HIDDEN / 512];
                     float us;
-                    prep_digits<DEC_HIDDEN>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_HIDDEN, true>(smq, xr, col0, dg, us);
                     t_pro += clock64() - tp;
                     consume_q8<DEC_HIDDEN, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_w2, L.qs_w2, P.err, t_wait, epi_res);
                 } else {
@@ -1119,10 +1213,15 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             if constexpr (Q8) {
                 uint4 dg[DEC_DIM / 512];
                 float us;
-                prep_digits<DEC_DIM>(smq, xr, col0, dg, us);
+                prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
                 t_pro += clock64() - tp;
-                if (P.alt_on) consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_alt);
-                else consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_max);
+                if constexpr (MK_Q8_TPW) {
+                    if (P.alt_on) consume_q8_w<DEC_DIM, false>(smq, gt, VOCAB, 1, c, G, us, P.s_tok_emb, P.qs_tok_emb, P.err, epi_alt);
+                    else consume_q8_w<DEC_DIM, false>(smq, gt, VOCAB, 1, c, G, us, P.s_tok_emb, P.qs_tok_emb, P.err, epi_max);
+                } else {
+                    if (P.alt_on) consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_alt);
+                    else consume_q8<DEC_DIM, false>(smq, gt, pbuf, VOCAB, 1, c, G, dg, us, P.s_tok_emb, P.qs_tok_emb, P.err, t_wait, epi_max);
+                }
             } else {
                 t_pro += clock64() - tp;
                 if (P.alt_on) consume<DEC_DIM, false>(sm, gt, pbuf, VOCAB, 1, c, G, xr, P.err, t_wait, epi_alt);
@@ -1241,13 +1340,13 @@ int dec_mega_init(vox_cuda_state *s) {
                                   (int)sizeof(mk::Smem)));
     CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)sizeof(mk::Smem)));
-    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(mk::SmemQ)));
-    CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(mk::SmemQ)));
-    if (s->m->q8)
+    if (s->m->q8) {
+        CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(mk::SmemQ)));
+        CUDA_TRY(cudaFuncSetAttribute(mk::dec_mega_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(mk::SmemQ)));
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float, true>, mk::NT, sizeof(mk::SmemQ)));
-    else
+    } else
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mk::dec_mega_kernel<float, false>, mk::NT, sizeof(mk::Smem)));
     if (occ < 1 || sms < 8) { vox_set_error("dec_mega: kernel does not fit (occupancy %d, %d SMs)", occ, sms); return -1; }
     h->grid = sms;
