@@ -195,3 +195,20 @@ def test_q8_refused_where_not_built(q8_env):
     assert "Q8" in e.vc.last_error()
     assert not e.L.vox_cuda_tp_create_local(e.model, 2)
     assert "Q8" in e.vc.last_error()
+
+
+def test_q8_dropin_cli(q8_env, tmp_path):
+    """the reference's own host (main.c + voxtral*.c, -DUSE_CUDA) on the Q8 directory: its loader takes the Q8 branch
+    (ctx->use_q8, voxtral.c:175-181), dropin/vox_cuda_dropin.c binds the *_weight_q8 / *_scale_q8 pairs to
+    vox_cuda_model_create_q8, and the text must be the reference's Q8 CPU text"""
+    import subprocess
+    from test_gpu_ids import PKG, text_of, write_wav
+    exe = os.path.join(PKG, "voxtral_cuda")
+    if not os.path.exists(exe):
+        pytest.skip("voxtral_cuda not built (make -C voxtral.c_b200 dropin needs /root/reference)")
+    fx = np.load(os.path.join(HERE, "golden", "ids_jfk_q8.npz"))
+    wav = str(tmp_path / "jfk.wav")
+    write_wav(wav, fx["pcm_s16"].astype(np.float32) / 32768.0)
+    p = subprocess.run([exe, "-d", q8_env.mdir, "-i", wav], capture_output=True, timeout=900)
+    assert p.returncode == 0, p.stderr.decode()[-2000:]
+    assert p.stdout.decode().strip() == text_of(fx["ids"]).strip()

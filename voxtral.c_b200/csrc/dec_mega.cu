@@ -84,11 +84,18 @@ struct Smem {
 // Q8 weights (vox_cuda_model_create_q8): the activation vector of a phase as four planes of unsigned 8-bit digits
 // (see prep_digits) and the int32 partial sums of a row group.  Only the Q8 instantiations allocate this part.
 constexpr int QDIG = 4;                     // digit planes: 32-bit offset-binary fixed point
+constexpr int QROWS = 896;                  // rows of one phase per CTA: ceil(131072 / 148) = 886 with 148 CTAs (checked at launch)
 constexpr int QPLANE = KMAX + 64;           // plane pitch in bytes (+64: the four planes start in different banks)
 struct SmemQ : Smem {
     alignas(16) unsigned char dig[QDIG][QPLANE];
     int partq[2][QDIG][CW][GROWS];           // [buffer][digit plane][warp][row of the group]
+    float redm[CW];
+    // scale and row sum of the rows this CTA owns in the current phase (<= 886: the vocabulary), staged with cp.async at the
+    // start of the phase so that no epilogue waits for an L2 round trip
+    float esc[QROWS];
+    int ers[QROWS];
 };
+static_assert(NSTAGE > 6 || sizeof(SmemQ) <= 232448, "Q8 kernel: shared memory (deeper measurement rings: bf16 models only)");
 
 struct Top4 {
     float v[4]; int i[4];
@@ -474,20 +481,38 @@ __device__ __forceinline__ void imma_u8s8(int (&d)[4], uint32_t a0, uint32_t a2,
 // Digit planes of this phase's activation vector.  xr = the lane's slice in the layout of load_slice (element
 // 4j + i of xr is x[j*1024 + col0 + i]); dg[sp] = the 16 digits of plane (lane >> 2) that this lane feeds to the two
 // MMAs of step pair sp (k = (sp*8 + w)*64 + (lane & 3)*16 .. +15: the same bytes it reads of every weight row).
+__device__ __forceinline__ void cp_async4(void *dst, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+// start of a Q8 phase: row constants of the CTA's rows -> shared memory, asynchronously (consume_q8 waits for them)
+__device__ __forceinline__ void stage_row_consts(SmemQ &sm, const float *__restrict__ scale, const int *__restrict__ rowsum,
+                                                 int R, int unit, int c, int G) {
+    int r0, r1;
+    cta_rows(R, unit, c, G, r0, r1);
+    for (int i = threadIdx.x; i < r1 - r0; i += CT) {
+        cp_async4(&sm.esc[i], scale + r0 + i);
+        cp_async4(&sm.ers[i], rowsum + r0 + i);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
 template <int K, bool WANT_DG>
 __device__ __forceinline__ void prep_digits(SmemQ &sm, const float (&xr)[K / 256], int col0, uint4 (&dg)[K / 512],
-                                            float &unit_scale) {
+                                            float &unit_scale, float mx_known = -1.f) {
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float mx = 0.f;
-    #pragma unroll
-    for (int i = 0; i < K / 256; i++) mx = fmaxf(mx, fabsf(xr[i]));
-    #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    consumer_sync();                       // previous readers of red[] and of the digit planes are done
-    if (lane == 0) sm.red[w] = mx;
-    consumer_sync();
-    #pragma unroll
-    for (int k = 0; k < CW; k++) mx = fmaxf(mx, sm.red[k]);
+    float mx = mx_known;
+    if (mx_known < 0.f) {                  // (uniform) no maximum from the norm's reduction round: one of our own
+        mx = 0.f;
+        #pragma unroll
+        for (int i = 0; i < K / 256; i++) mx = fmaxf(mx, fabsf(xr[i]));
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        consumer_sync();                   // previous readers of redm[] are done
+        if (lane == 0) sm.redm[w] = mx;
+        consumer_sync();
+        #pragma unroll
+        for (int k = 0; k < CW; k++) mx = fmaxf(mx, sm.redm[k]);
+    }
     // 2^e > max|x| (e = biased exponent - 126), clamped so that both scale factors are normal numbers
     int e = (int)((__float_as_uint(mx) >> 23) & 255u) - 126;
     e = max(-90, min(e, 96));
@@ -507,15 +532,24 @@ __device__ __forceinline__ void prep_digits(SmemQ &sm, const float (&xr)[K / 256
         *reinterpret_cast<uint32_t *>(&sm.dig[2][k]) = __byte_perm(t2, t3, 0x5410);
         *reinterpret_cast<uint32_t *>(&sm.dig[3][k]) = __byte_perm(t2, t3, 0x7632);
     }
-    consumer_sync();
-    if (WANT_DG) {                         // K-split consumer (consume_q8): the lane's digits stay in registers
+    if (WANT_DG) {
+        // K-split consumer (consume_q8): the lane's digits stay in registers.  With the Q8 column map (q8_col0) the
+        // 64-byte chunks (sp*8 + w) that warp w multiplies are exactly the ones its own lanes just converted: a warp-level
+        // barrier is enough, no CTA barrier between conversion and use
+        __syncwarp();
         const int m = lane >> 2, cq = lane & 3;
         #pragma unroll
         for (int sp = 0; sp < K / 512; sp++)
             dg[sp] = (m < QDIG) ? *reinterpret_cast<const uint4 *>(&sm.dig[m & (QDIG - 1)][(sp * 8 + w) * 64 + cq * 16])
                                 : make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();                      // the next phase's conversion overwrites the planes
+    } else {
+        consumer_sync();                   // tile-per-warp consumer: every warp reads all of the planes
     }
 }
+// Column map of the Q8 kernel: lane l of warp w owns x[j*1024 + q8_col0 .. +3], chosen so that the 16 lanes of a half
+// warp convert one 64-byte chunk (sp*8 + w) of the digit planes, sp = 2j + (l >> 4) - the chunks warp w multiplies.
+__device__ __forceinline__ int q8_col0(int w, int lane) { return (lane >> 4) * 512 + w * 64 + (lane & 15) * 4; }
 
 // Loads that must be issued where they are written (the compiler would otherwise sink them to their first use,
 // an L2 round trip in front of the epilogue)
@@ -617,17 +651,9 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
     const int n_tiles = (r1 - r0 + TR - 1) / TR;
     int grp = 0;
     for (int tg = 0; tg < n_tiles; tg += GT, grp++) {
-        // scale and row sum of the row(s) this lane would finish, requested before the group's tiles are multiplied: the
-        // epilogue warp must not sit in an L2 round trip while the other seven wait for it at the next group
         const int rbase = r0 + tg * TR;
         const int rows = min(r1 - rbase, GT * TR);
         const int er = PAIR ? 2 * lane : lane;
-        float esc[2] = {0.f, 0.f};
-        int ers[2] = {0, 0};
-        if (er < rows) {
-            esc[0] = ldg_f32_now(scale + rbase + er); ers[0] = ldg_s32_now(rowsum + rbase + er);
-            if (PAIR) { esc[1] = ldg_f32_now(scale + rbase + er + 1); ers[1] = ldg_s32_now(rowsum + rbase + er + 1); }
-        }
         #pragma unroll
         for (int ti = 0; ti < GT; ti++) {
             const int t = tg + ti;
@@ -678,8 +704,11 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
                 if (2 * cq + 1 < TR) sm.partq[pbuf][rq][w][ti * TR + 2 * cq + 1] = d[1];
             }
         }
+        if (tg == 0) asm volatile("cp.async.wait_all;" ::: "memory");       // this thread's share of stage_row_consts
         consumer_sync();
-        auto row_value = [&](int lr, float sc, int rs) -> float {
+        auto row_value = [&](int lr) -> float {
+            const float sc = sm.esc[tg * TR + lr];
+            const int rs = sm.ers[tg * TR + lr];
             long long y = 0;
             #pragma unroll
             for (int j = QDIG - 1; j >= 0; j--) {
@@ -693,9 +722,9 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
         };
         if (w == (grp & (CW - 1))) {                        // epilogue duty rotates over the warps
             if (PAIR) {
-                if (lane < (rows >> 1)) epi(rbase + er, row_value(er, esc[0], ers[0]), row_value(er + 1, esc[1], ers[1]));
+                if (lane < (rows >> 1)) epi(rbase + er, row_value(er), row_value(er + 1));
             } else {
-                if (lane < rows) epi(rbase + er, row_value(er, esc[0], ers[0]), 0.f);
+                if (lane < rows) epi(rbase + er, row_value(er), 0.f);
             }
         }
         pbuf ^= 1;
@@ -945,6 +974,46 @@ __device__ __forceinline__ void norm_slice(Smem &sm, float (&xr)[DEC_DIM / 256],
     }
 }
 
+// Q8: norm_slice that also returns (an upper bound within 1e-6 of) max |normalised x| from the SAME reduction round as the
+// sum of squares - prep_digits then needs no reduction of its own (2 CTA barriers per norm phase instead of 5)
+__device__ __forceinline__ float norm_slice_max(SmemQ &sm, float (&xr)[DEC_DIM / 256], float ss, const float *nw,
+                                                const float *ada, int col0) {
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float4 wv[DEC_DIM / 1024], av[DEC_DIM / 1024];
+    float mraw = 0.f;
+    #pragma unroll
+    for (int j = 0; j < DEC_DIM / 1024; j++) {
+        wv[j] = *reinterpret_cast<const float4 *>(nw + j * 1024 + col0);
+        if (ada) {
+            av[j] = *reinterpret_cast<const float4 *>(ada + j * 1024 + col0);
+            wv[j].x *= (1.0f + av[j].x); wv[j].y *= (1.0f + av[j].y); wv[j].z *= (1.0f + av[j].z); wv[j].w *= (1.0f + av[j].w);
+        }
+        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j] * wv[j].x)), fabsf(xr[4 * j + 1] * wv[j].y));
+        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j + 2] * wv[j].z)), fabsf(xr[4 * j + 3] * wv[j].w));
+        if (ada) wv[j] = *reinterpret_cast<const float4 *>(nw + j * 1024 + col0);      // the norm below multiplies in the reference's order
+    }
+    ss = warp_sum(ss);
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mraw = fmaxf(mraw, __shfl_xor_sync(0xffffffffu, mraw, o));
+    consumer_sync();                       // previous readers of red[] / redm[] are done
+    if (lane == 0) { sm.red[w] = ss; sm.redm[w] = mraw; }
+    consumer_sync();
+    float tot = 0.f;
+    #pragma unroll
+    for (int k = 0; k < CW; k++) { tot += sm.red[k]; mraw = fmaxf(mraw, sm.redm[k]); }
+    const float rinv = 1.0f / sqrtf(tot / (float)DEC_DIM + NORM_EPS);
+    #pragma unroll
+    for (int j = 0; j < DEC_DIM / 1024; j++) {
+        xr[4 * j] = xr[4 * j] * rinv * wv[j].x; xr[4 * j + 1] = xr[4 * j + 1] * rinv * wv[j].y;
+        xr[4 * j + 2] = xr[4 * j + 2] * rinv * wv[j].z; xr[4 * j + 3] = xr[4 * j + 3] * rinv * wv[j].w;
+        if (ada) {
+            xr[4 * j] *= (1.0f + av[j].x); xr[4 * j + 1] *= (1.0f + av[j].y);
+            xr[4 * j + 2] *= (1.0f + av[j].z); xr[4 * j + 3] *= (1.0f + av[j].w);
+        }
+    }
+    return mraw * rinv * 1.000002f;        // the products above round differently from mraw's: a bound, a few ulps up
+}
+
 // KV = element type of the K/V rings; Q8 = the weights are int8 rows + row scales (vox_cuda_model_create_q8)
 template <typename KV, bool Q8>
 __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
@@ -1023,7 +1092,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     const int use_host_embed = P.params->use_host_embed;
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
     // column base of this lane for unit j: (j*256 + w*32 + lane) * 4
-    const int col0 = (w * 32 + lane) * 4;
+    const int col0 = Q8 ? q8_col0(w, lane) : (w * 32 + lane) * 4;
     // rows of the [3072]-row matrices (wo, w2) this CTA owns: residual values are staged in smem
     int rr0, rr1;
     cta_rows(DEC_DIM, 1, c, G, rr0, rr1);
@@ -1065,6 +1134,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             // ---------------- phase 1: rmsnorm -> qkv -> rope -> q / KV ring ----------------
             {
                 const long long tp = clock64();
+                if constexpr (Q8) stage_row_consts(smq, L.s_wqkv, L.qs_wqkv, DEC_QKV, 2, c, G);
                 float xr[DEC_DIM / 256];
                 float ss = 0.f;
                 if (l == 0) {
@@ -1092,7 +1162,9 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 } else {
                     ss = load_slice<DEC_DIM>(P.x, col0, xr);
                 }
-                norm_slice(sm, xr, ss, L.attn_norm, nullptr, col0);
+                float mxn = -1.f;
+                if constexpr (Q8) mxn = norm_slice_max(smq, xr, ss, L.attn_norm, nullptr, col0);
+                else norm_slice(sm, xr, ss, L.attn_norm, nullptr, col0);
                 auto epi_qkv = [&](int row, float v0, float v1) {
                         if (row < DEC_QDIM + DEC_KVDIM) {
                             const int d = (row & (DEC_HD - 1)) >> 1;
@@ -1107,7 +1179,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
                     t_pro += clock64() - tp;
                     if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, DEC_QKV, 2, c, G, us, L.s_wqkv, L.qs_wqkv, P.err, epi_qkv);
                     else consume_q8<DEC_DIM, true>(smq, gt, pbuf, DEC_QKV, 2, c, G, dg, us, L.s_wqkv, L.qs_wqkv, P.err, t_wait, epi_qkv);
@@ -1138,6 +1210,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             // ---------------- phase 3: merge partials -> wo -> residual ----------------
             {
                 const long long tp = clock64();
+                if constexpr (Q8) stage_row_consts(smq, L.s_wo, L.qs_wo, DEC_DIM, 1, c, G);
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_QDIM / 256];
                 (void)load_slice<DEC_QDIM>(P.attn, col0, xr);     // rows merged by the last split of each kv head
@@ -1159,13 +1232,16 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             {
                 const long long tp = clock64();
                 float xr[DEC_DIM / 256];
+                if constexpr (Q8) stage_row_consts(smq, L.s_w13, L.qs_w13, 2 * DEC_HIDDEN, 2, c, G);
                 const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
-                norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
+                float mxn = -1.f;
+                if constexpr (Q8) mxn = norm_slice_max(smq, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
+                else norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
                 auto epi_glu = [&](int row, float v0, float v1) { P.h[row >> 1] = silu(v0) * v1; };
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
+                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
                     t_pro += clock64() - tp;
                     if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, 2 * DEC_HIDDEN, 2, c, G, us, L.s_w13, L.qs_w13, P.err, epi_glu);
                     else consume_q8<DEC_DIM, true>(smq, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, dg, us, L.s_w13, L.qs_w13, P.err, t_wait, epi_glu);
@@ -1178,6 +1254,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             // ---------------- phase 5: w2 -> residual ----------------
             {
                 const long long tp = clock64();
+                if constexpr (Q8) stage_row_consts(smq, L.s_w2, L.qs_w2, DEC_DIM, 1, c, G);
                 if (tid < rr1 - rr0) sm.resid[tid] = __ldcg(P.x + rr0 + tid);
                 float xr[DEC_HIDDEN / 256];
                 (void)load_slice<DEC_HIDDEN>(P.h, col0, xr);
@@ -1199,8 +1276,11 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         {
             const long long tp = clock64();
             float xr[DEC_DIM / 256];
+            if constexpr (Q8) stage_row_consts(smq, P.s_tok_emb, P.qs_tok_emb, VOCAB, 1, c, G);
             const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
-            norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
+            float mxn = -1.f;
+            if constexpr (Q8) mxn = norm_slice_max(smq, xr, ss, P.dec_norm, nullptr, col0);
+            else norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
             float bv = -INFINITY;
             int bi = 0x7fffffff;
             Top4 top;
@@ -1213,7 +1293,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             if constexpr (Q8) {
                 uint4 dg[DEC_DIM / 512];
                 float us;
-                prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
+                prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
                 t_pro += clock64() - tp;
                 if constexpr (MK_Q8_TPW) {
                     if (P.alt_on) consume_q8_w<DEC_DIM, false>(smq, gt, VOCAB, 1, c, G, us, P.s_tok_emb, P.qs_tok_emb, P.err, epi_alt);
@@ -1382,6 +1462,7 @@ int dec_mega_init(vox_cuda_state *s) {
         }
     }
     if (h->grid > 8 * 64) { vox_set_error("dec_mega: grid too large"); return -1; }
+    if (s->m->q8 && (VOCAB + h->grid - 1) / h->grid + 1 > mk::QROWS) { vox_set_error("dec_mega: Q8 needs >= %d SMs", VOCAB / (mk::QROWS - 2) + 1); return -1; }
     return 0;
 }
 
