@@ -107,10 +107,20 @@ def test_q8_encoder_and_adapter(q8_env):
         d = float(np.abs(ad - ref_ad).max())
         print("Q8 adapter rows: max|d|", d, "ref rms", float(np.sqrt((ref_ad ** 2).mean())))
         assert d < TOL
-        # a 50-frame streaming chunk after it (small M: must take the scale-aware path too)
-        mel2 = e.ref.stream_mel(x)[312:312 + 56]
-        n2 = e.L.vox_cuda_encode_chunk(st, e.vc.fptr(mel2), mel2.shape[0])
-        assert n2 >= 0, e.vc.last_error()
+        # a 56-frame streaming chunk after it: 28 positions -> the small-M path (swap-AB GEMM with the row scale in ITS
+        # epilogue) must give the rows of one 368-frame call (184 positions: the large-tile path)
+        mel_all = e.ref.stream_mel(x)[:368]
+        mel2 = np.ascontiguousarray(mel_all[312:])
+        assert e.L.vox_cuda_encode_chunk(st, e.vc.fptr(mel2), mel2.shape[0]) == 46, e.vc.last_error()   # total rows so far
+        tail = np.empty((7, 3072), np.float32)
+        assert e.L.vox_cuda_adapter_read(st, 39, 7, e.vc.fptr(tail)) == 7
+        e.L.vox_cuda_state_reset_encoder(st)
+        assert e.L.vox_cuda_encode_chunk(st, e.vc.fptr(np.ascontiguousarray(mel_all)), 368) == 46, e.vc.last_error()
+        one = np.empty((46, 3072), np.float32)
+        assert e.L.vox_cuda_adapter_read(st, 0, 46, e.vc.fptr(one)) == 46
+        d2 = float(np.abs(one[39:] - tail).max())
+        print("Q8 streaming chunk (small-M path) vs one call (large tiles): max|d|", d2)
+        assert np.abs(one[:39] - ad).max() < 1e-3 and d2 < 1e-3
     finally:
         e.L.vox_cuda_state_free(st)
 

@@ -183,6 +183,40 @@ __global__ void __launch_bounds__(256) enc_sum_bias_kernel(const float *__restri
     *reinterpret_cast<float4 *>(out + (size_t)m * N + col) = a;
 }
 
+// The two kernels that followed the QKV product in one: q / k / v row = sum_s part[s] + bias (as enc_sum_bias_kernel), RoPE on
+// q and k at the row's logical position, k and v appended to the ring, q left in qkv (as rows_rope_kv_kernel, rows.cu; same
+// float expressions in the same order).
+__global__ void __launch_bounds__(256) enc_sum_bias_rope_kernel(const float *__restrict__ part, int ks, long stride,
+                                                                const float *__restrict__ bias, float *__restrict__ qkv,
+                                                                const float *__restrict__ inv_freq, int pos0,
+                                                                const int *__restrict__ pos_dev, int ring_mask,
+                                                                float *__restrict__ kc, float *__restrict__ vc) {
+    tcx::pdl_launch_dependents();
+    tcx::pdl_wait();
+    if (pos_dev) pos0 = *pos_dev;
+    constexpr int LD = 3 * ENC_QKV;
+    // grid (rows, 6): 1024 columns per CTA - y 0,1 = q, 2,3 = k, 4,5 = v; four columns (two RoPE pairs) per thread
+    const int row = blockIdx.x, pos = pos0 + row;
+    const int col = blockIdx.y * 1024 + threadIdx.x * 4;
+    const size_t slot = (size_t)(pos & ring_mask) * ENC_QKV;
+    const float *p = part + (size_t)row * LD + col;
+    float4 a = *reinterpret_cast<const float4 *>(bias + col);
+    for (int s = 0; s < ks; s++) {
+        const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    if (col >= 2 * ENC_QKV) {                                 // v: appended as it is
+        *reinterpret_cast<float4 *>(vc + slot + col - 2 * ENC_QKV) = a;
+        return;
+    }
+    const int d = (col & (ENC_HD - 1)) >> 1;                  // pair indices d, d + 1 inside the head
+    const float a0 = (float)pos * inv_freq[d], a1 = (float)pos * inv_freq[d + 1];
+    const float c0 = cosf(a0), s0 = sinf(a0), c1 = cosf(a1), s1 = sinf(a1);
+    const float4 y = make_float4(a.x * c0 - a.y * s0, a.x * s0 + a.y * c0, a.z * c1 - a.w * s1, a.z * s1 + a.w * c1);
+    if (col < ENC_QKV) *reinterpret_cast<float4 *>(qkv + (size_t)row * LD + col) = y;
+    else *reinterpret_cast<float4 *>(kc + slot + col - ENC_QKV) = y;
+}
+
 // x[m] += sum_s part[s][m] + bias; then RMSNorm(x[m]) * w -> split bf16 row (out_b) or fp32 row (out_f)
 // (wo / w2 + bias + residual, voxtral_encoder.c:644-646,677-679, followed by the next norm :562-566,652-656)
 template <int KS>
@@ -295,10 +329,18 @@ static EncSmall *small_get(vox_cuda_state *s, int NB) {
             o[1].out_f32 = q->part; o[1].ldo = ENC_DIM;
             o[2].mode = WT_OUT_SWIGLU_BF16X2; o[2].out_bf16 = q->hh_t; o[2].ldb = 2 * ENC_HIDDEN; o[2].lo_off = ENC_HIDDEN;
             o[3].out_f32 = q->part; o[3].ldo = ENC_DIM;
+            o[0].row_scale = L.s_wqkv; o[1].row_scale = L.s_wo; o[2].row_scale = L.s_w13; o[3].row_scale = L.s_w2;   // Q8 model, else null
         }
         q->ops[idx] = ops;
     }
     return q;
+}
+
+// VOX_CUDA_ENC_FUSED_ROPE=0 keeps the two-kernel form (sum + bias, then RoPE / ring append) for A/B runs
+static int small_fused_rope(void) {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("VOX_CUDA_ENC_FUSED_ROPE"); v = (e && !atoi(e)) ? 0 : 1; }
+    return v;
 }
 
 // the 32 layers for M <= 128 rows; pos_dev: device position (graph capture) or null (pos0 by value)
@@ -315,10 +357,16 @@ static int small_enqueue(vox_cuda_state *s, EncSmall *q, WtOp *ops, float *x, in
         for (int i = 0; i < 4; i++) o[i].B = M;
         o[0].split_stride = (long)M * 3 * ENC_QKV; o[1].split_stride = (long)M * ENC_DIM; o[3].split_stride = (long)M * ENC_DIM;
         if (gemm_wt_launch(st, &o[0])) return -1;
-        CUDA_TRY(launch_pdl(enc_sum_bias_kernel, dim3(M, (3 * ENC_QKV + 1023) / 1024), 256, 0, st, (const float *)q->part, SM_KS_QKV,
-                            (long)M * 3 * ENC_QKV, L.bqkv, e->qkv, 3 * ENC_QKV));
-        LAUNCHED();
-        if (rows_rope_kv_dev(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc, pos_dev)) return -1;
+        if (small_fused_rope()) {
+            CUDA_TRY(launch_pdl(enc_sum_bias_rope_kernel, dim3(M, 3 * ENC_QKV / 1024), 256, 0, st, (const float *)q->part, SM_KS_QKV, (long)M * 3 * ENC_QKV,
+                                L.bqkv, e->qkv, (const float *)m->inv_freq_enc, pos0, pos_dev, ENC_RING - 1, kc, vc));
+            LAUNCHED();
+        } else {
+            CUDA_TRY(launch_pdl(enc_sum_bias_kernel, dim3(M, (3 * ENC_QKV + 1023) / 1024), 256, 0, st, (const float *)q->part, SM_KS_QKV,
+                                (long)M * 3 * ENC_QKV, L.bqkv, e->qkv, 3 * ENC_QKV));
+            LAUNCHED();
+            if (rows_rope_kv_dev(st, e->qkv, M, ENC_QKV, ENC_QKV, ENC_HD, m->inv_freq_enc, pos0, ENC_RING - 1, kc, vc, pos_dev)) return -1;
+        }
         if (enc_attention_dev(s, e->qkv, kc, vc, M, pos0, q->att_t, 2 * ENC_QKV, 1, pos_dev)) return -1;
         if (gemm_wt_launch(st, &o[1])) return -1;
         CUDA_TRY(launch_pdl(enc_resid_norm_kernel<SM_KS_WO>, M, 320, 0, st, x, (const float *)q->part, (long)M * ENC_DIM, L.bo, L.ffn_norm,
@@ -344,7 +392,6 @@ static int small_graph_mode(void) {
 int enc_layers_small(vox_cuda_state *s, float *x, int M, float *out) {
     EncState *e = (EncState *)s->enc_priv;
     if (x1_mask()) return enc_layers_fast(s, x, M, out);       // single-bf16 products live on the large-tile path only
-    if (s->m->q8) return enc_layers_fast(s, x, M, out);        // Q8 row scales are applied in the large-tile epilogue only
     if (!fast_get(s)) return -1;
     const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
     EncSmall *q = small_get(s, NB);

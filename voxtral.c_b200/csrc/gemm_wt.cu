@@ -50,6 +50,7 @@ struct KParams {
     const uint8_t *wt, *at;                                 // tiled operands (see gemm_wt.h); null: tensor maps
     float *out_f32; long ldo; long split_stride;            // mode 0: out_f32[s*split_stride + b*ldo + n]
     uint16_t *out_bf16; long ldb; long lo_off;              // mode 1: rows (2i, 2i+1) = (gate, up)
+    const float *row_scale;                                 // Q8: scale of output feature n, or null
 };
 
 template <int NB>
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
             const int as = n & 1;
             const unsigned aph = (unsigned)(n >> 1) & 1u;
             const int row = tile * BMW + q * 32 + lane;     // output feature of this thread
+            const float rsc = p.row_scale ? __ldg(p.row_scale + row) : 1.0f;
             mb_wait(&tfull[as], aph);
             tc_fence_after();
             #pragma unroll 1
@@ -177,6 +179,10 @@ __global__ void __launch_bounds__(NT, 1) gemm_wt_kernel(const __grid_constant__ 
                     tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * C::ACC_COLS + NB + cc * 32), r2);
                     #pragma unroll
                     for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) + __uint_as_float(r2[c]));
+                }
+                if (p.row_scale) {
+                    #pragma unroll
+                    for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) * rsc);
                 }
                 if (p.mode == 0) {
                     float *o = p.out_f32 + (size_t)sp * p.split_stride + row;
@@ -271,6 +277,7 @@ int gemm_wt_prepare(WtOp *op, int NB, int B, int N, int K, int split, const uint
     op->mode = WT_OUT_F32; op->out_f32 = nullptr; op->ldo = 0; op->split_stride = 0;
     op->out_bf16 = nullptr; op->ldb = 0; op->lo_off = 0;
     op->w_tiled = nullptr; op->act_tiled = nullptr;
+    op->row_scale = nullptr;
     return 0;
 }
 
@@ -280,6 +287,7 @@ int gemm_wt_launch(cudaStream_t st, const WtOp *op) {
     p.mode = op->mode; p.out_f32 = op->out_f32; p.ldo = op->ldo; p.split_stride = op->split_stride;
     p.out_bf16 = op->out_bf16; p.ldb = op->ldb; p.lo_off = op->lo_off;
     p.wt = (const uint8_t *)op->w_tiled; p.at = (const uint8_t *)op->act_tiled;
+    p.row_scale = op->row_scale;
     if ((p.wt == nullptr) != (p.at == nullptr)) { vox_set_error("gemm_wt: tiled weights need tiled activations"); return -1; }
     if ((p.mode == WT_OUT_F32 && !p.out_f32) || (p.mode == WT_OUT_SWIGLU_BF16X2 && (!p.out_bf16 || p.ksplit != 1))) {
         vox_set_error("gemm_wt: epilogue not set");

@@ -20,6 +20,9 @@ struct WtOp {
     // SWIZZLE_128B K-major image), so one 1-D bulk copy replaces 128 row requests.  act_tiled: per k-block a
     // contiguous [hi: NB rows x 128 B | lo: NB rows x 128 B] block in the same swizzle (wt_act_offset()).
     const uint16_t *w_tiled, *act_tiled;
+    // Q8 weights: W holds the int8 values as bf16, the product (each K-range partial) is multiplied by row_scale[n];
+    // null = plain bf16 weights
+    const float *row_scale;
 };
 
 // byte offset of element (row b, column c) of the hi half inside a tiled activation buffer; lo = + NB * 128
