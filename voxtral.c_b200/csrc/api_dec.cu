@@ -95,6 +95,7 @@ extern "C" void vox_cuda_state_free(vox_cuda_state_t *s) {
     batch_free(s);
     enc_state_free(s);
     dec_mega_free(s);
+    dec_prefill_wt_free(s);
     void *ptrs[] = {s->kv_k, s->kv_v, s->d_params, s->d_x, s->d_q, s->d_attn, s->d_h, s->d_logits,
                     s->d_embed_in, s->d_rope, s->d_attn_part, s->d_blockmax, s->d_tokens,
                     s->adapter_buf, s->pf_buf, s->d_alt, s->d_alt_cand, s->kv_k16, s->kv_v16};
@@ -398,6 +399,13 @@ static int prefill_f32_mode(void) {
     return m;
 }
 
+// VOX_CUDA_PREFILL_TC=1 keeps the prompt rows on the large-tile GEMM (gemm_tc.cu; A/B runs: 5.05 ms per 38-row prompt)
+static int prefill_wt_mode(void) {
+    static int m = -1;
+    if (m < 0) { const char *env = getenv("VOX_CUDA_PREFILL_TC"); m = (env && atoi(env)) ? 0 : 1; }
+    return m;
+}
+
 static int ensure_pf(vox_cuda_state *s) {
     const size_t per_row = (size_t)(2 * DEC_DIM + DEC_QKV + DEC_QDIM + 2 * DEC_HIDDEN + DEC_HIDDEN) * 4;
     const size_t need = per_row * PF_ROWS;
@@ -442,6 +450,12 @@ int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase,
         float *x = x_dev + (size_t)r0 * DEC_DIM;
         const int pos0 = *pos;
         const int first_valid = pos0 - *n_valid;
+        if (tcm && prefill_wt_mode()) {                     // default: skinny swap-AB GEMM with K-range splits (dec_prefill.cu)
+            if (dec_prefill_block_wt(s, x, M, kbase, vbase, kv_layer, mask, pos0, first_valid)) return -1;
+            *pos += M;
+            *n_valid = *n_valid + M > DEC_WINDOW ? DEC_WINDOW : *n_valid + M;
+            continue;
+        }
         for (int l = 0; l < m->n_dec; l++) {
             const DecLayerDev &L = m->dec[l];
             float *kc = kbase + l * kv_layer, *vc = vbase + l * kv_layer;

@@ -106,6 +106,7 @@ struct vox_cuda_state {
     int use_graph_steps;         // 1: legacy kernel-per-op CUDA graph (VOX_CUDA_DEC_GRAPH=1), 0: megakernel
     // prefill scratch (allocated on demand)
     float *pf_buf; size_t pf_bytes;
+    void *pf_wt;                 // PfWt*, dec_prefill.cu (skinny-GEMM prefill: prepared products + row buffers, on first use)
     // ---- encoder ----
     void *enc_priv;              // EncState*, see enc_host.cu
     void *batch;                 // BatchBuf*, api_batch.cu (resident PCM / mel of the whole-clip entry point)
@@ -130,6 +131,10 @@ int dec_mega_attn_part_floats(void);
 // api_dec.cu: prompt prefill into an arbitrary K/V ring (used by the state itself and by stream groups)
 int dec_prefill_into(vox_cuda_state *s, float *x_dev, int seq_len, float *kbase, float *vbase, size_t kv_layer,
                      int mask, int *pos, int *n_valid);
+// dec_prefill.cu: one block of <= 64 prompt rows on the skinny swap-AB GEMM (x = residual stream, in place)
+int dec_prefill_block_wt(vox_cuda_state *s, float *x, int M, float *kbase, float *vbase, size_t kv_layer, int mask, int pos0,
+                         int first_valid);
+void dec_prefill_wt_free(vox_cuda_state *s);
 // api_batch.cu: PCM -> mel -> conv stem -> encoder -> adapter rows in s->adapter_buf (resets the state)
 int batch_encode_clip(vox_cuda_state *s, const float *pcm, int n_samples, int n_frames);
 
