@@ -177,9 +177,8 @@ int dec_prefill_block_wt(vox_cuda_state *s, float *x, int M, float *kbase, float
         CUDA_TRY(launch_pdl(pf_qkv_rope_kernel, dim3(M, DEC_QKV / 1024), 256, 0, st, (const float *)q->part, KS_QKV,
                                  (long)M * DEC_QKV, q->qkv, (const float *)m->inv_freq_dec, pos0, mask, kc, vc));
         LAUNCHED();
-        if (rows_attention(st, DEC_HD, q->qkv, DEC_QKV, kc, vc, DEC_KVDIM, mask, DEC_HEADS, DEC_HEADS / DEC_KVH, M, pos0,
-                           first_valid, DEC_WINDOW, q->att, DEC_QDIM)) return -1;
-        if (f32_to_bf16_rows(st, q->att, DEC_QDIM, q->att_t, 2 * DEC_QDIM, M, DEC_QDIM, 1)) return -1;
+        if (rows_attention_split128(st, q->qkv, DEC_QKV, kc, vc, DEC_KVDIM, mask, DEC_HEADS, DEC_HEADS / DEC_KVH, M, pos0,
+                                    first_valid, DEC_WINDOW, q->att_t, 2 * DEC_QDIM, DEC_QDIM)) return -1;
         if (gemm_wt_launch(st, &o[1])) return -1;
         CUDA_TRY(launch_pdl(pf_resid_norm_kernel<KS_WO>, M, NT_ROW, 0, st, x, (const float *)q->part, (long)M * DEC_DIM, L.ffn_norm,
                                  (const float *)(m->ada_scale + (size_t)l * DEC_DIM), q->xn_t));

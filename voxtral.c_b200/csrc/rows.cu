@@ -127,7 +127,10 @@ template <int HD>
 __global__ void __launch_bounds__(128) rows_attention_kernel(
     const float *__restrict__ q, long ldq, const float *__restrict__ kc,
     const float *__restrict__ vc, int kv_dim, int ring_mask, int heads_per_kv,
-    int q_pos0, int first_valid, int window, float scale, float *__restrict__ out, long ldo) {
+    int q_pos0, int first_valid, int window, float scale, float *__restrict__ out, long ldo,
+    uint16_t *__restrict__ out_b, long ldb, long lo_off) {
+    tcx::pdl_launch_dependents();   // no-ops under a plain launch
+    tcx::pdl_wait();
     constexpr int DPL = HD / 32;  // dims per lane in the PV phase
     const int row = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -177,9 +180,22 @@ __global__ void __launch_bounds__(128) rows_attention_kernel(
         m = mn;
     }
     const float inv = l > 0.f ? 1.0f / l : 0.f;
-    float *o = out + (size_t)row * ldo + head * HD + lane * DPL;
-    #pragma unroll
-    for (int d = 0; d < DPL; d++) o[d] = acc[d] * inv;
+    if (out) {
+        float *o = out + (size_t)row * ldo + head * HD + lane * DPL;
+        #pragma unroll
+        for (int d = 0; d < DPL; d++) o[d] = acc[d] * inv;
+    }
+    if (out_b) {   // split-bf16 row (hi at column c, rounding residual at lo_off + c): the next product's A operand
+        uint16_t *o = out_b + (size_t)row * ldb + head * HD + lane * DPL;
+        #pragma unroll
+        for (int d = 0; d < DPL; d += 2) {
+            const float y0 = acc[d] * inv, y1 = acc[d + 1] * inv;
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(y0, y1);
+            *reinterpret_cast<__nv_bfloat162 *>(o + d) = hi;
+            *reinterpret_cast<__nv_bfloat162 *>(o + lo_off + d) =
+                __floats2bfloat162_rn(y0 - __bfloat162float(hi.x), y1 - __bfloat162float(hi.y));
+        }
+    }
 }
 
 int rows_attention(cudaStream_t st, int head_dim, const float *q, long ldq, const float *kc,
@@ -190,13 +206,25 @@ int rows_attention(cudaStream_t st, int head_dim, const float *q, long ldq, cons
     dim3 grid(rows, n_heads / 4);
     if (head_dim == 64)
         rows_attention_kernel<64><<<grid, 128, 0, st>>>(q, ldq, kc, vc, kv_dim, ring_mask, heads_per_kv,
-                                                        q_pos0, first_valid, window, scale, out, ldo);
+                                                        q_pos0, first_valid, window, scale, out, ldo, nullptr, 0L, 0L);
     else if (head_dim == 128)
         rows_attention_kernel<128><<<grid, 128, 0, st>>>(q, ldq, kc, vc, kv_dim, ring_mask, heads_per_kv,
-                                                         q_pos0, first_valid, window, scale, out, ldo);
+                                                         q_pos0, first_valid, window, scale, out, ldo, nullptr, 0L, 0L);
     else { vox_set_error("rows_attention: head_dim %d unsupported", head_dim); return -1; }
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// head_dim 128, output as a split-bf16 row, launched with programmatic dependent launch (decoder prefill, dec_prefill.cu)
+int rows_attention_split128(cudaStream_t st, const float *q, long ldq, const float *kc, const float *vc, int kv_dim,
+                            int ring_mask, int n_heads, int heads_per_kv, int rows, int q_pos0, int first_valid, int window,
+                            uint16_t *out_b, long ldb, long lo_off) {
+    if (rows <= 0) return 0;
+    const float scale = 1.0f / sqrtf(128.0f);
+    CUDA_TRY(launch_pdl(rows_attention_kernel<128>, dim3(rows, n_heads / 4), 128, 0, st, q, ldq, kc, vc, kv_dim, ring_mask,
+                        heads_per_kv, q_pos0, first_valid, window, scale, (float *)nullptr, 0L, out_b, ldb, lo_off));
+    LAUNCHED();
     return 0;
 }
 

@@ -12,6 +12,9 @@ int rows_rope_kv_dev(cudaStream_t st, float *qkv, int rows, int q_dim, int kv_di
 int rows_attention(cudaStream_t st, int head_dim, const float *q, long ldq, const float *kc,
                    const float *vc, int kv_dim, int ring_mask, int n_heads, int heads_per_kv,
                    int rows, int q_pos0, int first_valid, int window, float *out, long ldo);
+int rows_attention_split128(cudaStream_t st, const float *q, long ldq, const float *kc, const float *vc, int kv_dim,
+                            int ring_mask, int n_heads, int heads_per_kv, int rows, int q_pos0, int first_valid, int window,
+                            uint16_t *out_b, long ldb, long lo_off);
 int rows_swiglu(cudaStream_t st, const float *gu, float *h, int rows, int hidden);
 int rows_rmsnorm_bf16(cudaStream_t st, const float *x, long ldx, const float *w, const float *ada, uint16_t *out,
                       long ldo, int rows, int dim, int split);
