@@ -93,6 +93,39 @@ def test_decoder_prefill_and_steps(full_env):
         e.L.vox_cuda_state_free(st)
 
 
+def test_decoder_prefill_two_blocks(full_env):
+    """a 100-row prefill = two blocks (64 + 36 rows) of the skinny-GEMM path (csrc/dec_prefill.cu): the second block's
+    causal attention reads the first block's K/V rows from the ring.  K/V rows of the first and last layer and the
+    logits of the following step against vox_decoder_prefill / vox_decoder_forward of the reference."""
+    e = full_env
+    rng = np.random.default_rng(11)
+    n = 100
+    emb = (0.5 * rng.standard_normal((n, 3072))).astype(np.float32)
+    e.ref.set("kv_cache_len", 0); e.ref.set("kv_pos_offset", 0)
+    e.ref.prefill(emb)
+    kref, vref = e.ref.kv_views()
+    st = e.L.vox_cuda_state_create(e.model)
+    assert st, e.vc.last_error()
+    try:
+        assert e.L.vox_cuda_decoder_prefill(st, e.vc.fptr(emb), n) == 0, e.vc.last_error()
+        assert e.L.vox_cuda_decoder_position(st) == n
+        k = np.empty((n, 1024), np.float32); v = np.empty((n, 1024), np.float32)
+        for layer in (0, 25):
+            assert e.L.vox_cuda_decoder_kv_read(st, layer, 0, n, e.vc.fptr(k), e.vc.fptr(v)) == 0
+            dk, dv = np.abs(k - kref[layer, :n]).max(), np.abs(v - vref[layer, :n]).max()
+            print(f"layer {layer}: 100-row prefill max|dK| {dk:.2e} max|dV| {dv:.2e}")
+            assert dk < 2e-2 and dv < 2e-2
+        x = (0.5 * rng.standard_normal(3072)).astype(np.float32)
+        tok_r, logits_r = e.ref.decoder_forward(x)
+        logits_c = np.empty(131072, np.float32)
+        tok_c = e.L.vox_cuda_decoder_step(st, e.vc.fptr(x), e.vc.fptr(logits_c))
+        d = float(np.abs(logits_c - logits_r).max())
+        print(f"step after the 100-row prompt: ref {tok_r} cuda {tok_c} max|dlogit| {d:.3e}")
+        assert d < 2e-2 and tok_c == tok_r
+    finally:
+        e.L.vox_cuda_state_free(st)
+
+
 def test_encoder_stem_layers_adapter(full_env):
     e = full_env
     x = synth_audio(16000 * 2, seed=3)

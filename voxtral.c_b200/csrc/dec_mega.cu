@@ -37,6 +37,9 @@ namespace mk {
 #ifndef MK_Q8_TPW
 #define MK_Q8_TPW 0                         // Q8, K = 3072 / 4096 phases: 1 = tile-per-warp consumer (consume_q8_w), 0 = K-split (consume_q8)
 #endif
+#ifndef MK_Q8_GROWS
+#define MK_Q8_GROWS 16                      // Q8 K-split consumer: rows per CTA barrier + epilogue (16 / 32 rows: 1.16 / 1.26 ms per token)
+#endif
 #ifndef MK_NSTAGE
 #define MK_NSTAGE 6                         // ring depth: 4 / 6 / 8 stages measured 1.434 / 1.427 / 1.470 ms per token
 #endif
@@ -84,11 +87,12 @@ struct Smem {
 // Q8 weights (vox_cuda_model_create_q8): the activation vector of a phase as four planes of unsigned 8-bit digits
 // (see prep_digits) and the int32 partial sums of a row group.  Only the Q8 instantiations allocate this part.
 constexpr int QDIG = 4;                     // digit planes: 32-bit offset-binary fixed point
+constexpr int QGROWS = MK_Q8_GROWS;         // rows per sync group of the Q8 K-split consumer (<= 32: one epilogue lane per row)
 constexpr int QROWS = 896;                  // rows of one phase per CTA: ceil(131072 / 148) = 886 with 148 CTAs (checked at launch)
 constexpr int QPLANE = KMAX + 64;           // plane pitch in bytes (+64: the four planes start in different banks)
 struct SmemQ : Smem {
     alignas(16) unsigned char dig[QDIG][QPLANE];
-    int partq[2][QDIG][CW][GROWS];           // [buffer][digit plane][warp][row of the group]
+    int partq[2][QDIG][CW][QGROWS];          // [buffer][digit plane][warp][row of the group]
     float redm[CW];
     // scale and row sum of the rows this CTA owns in the current phase (<= 886: the vocabulary), staged with cp.async at the
     // start of the phase so that no epilogue waits for an L2 round trip
@@ -470,7 +474,7 @@ __device__ __forceinline__ void consume(Smem &sm, unsigned &g0, int &pbuf, int R
 // in 64-bit integers - the only rounding of the whole dot product is X itself (2^-30 of the vector's maximum; the
 // reference's sequential fp32 sum carries more).  ~30 instructions per thread per 24 KB tile instead of ~180 for
 // an unpack + FFMA loop over twice the weights of a bf16 tile.
-template <int K> struct GroupTilesQ { static constexpr int v = (K == 9216) ? 8 : 2; };
+template <int K> struct GroupTilesQ { static constexpr int v = QGROWS / TileRows<K, 1>::v; };   // 2 / 2 / 8 tiles at 16 rows
 
 __device__ __forceinline__ void imma_u8s8(int (&d)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
     const uint32_t z = 0u;               // A rows 8..15 are not used
@@ -644,7 +648,7 @@ __device__ __forceinline__ void consume_q8(SmemQ &sm, unsigned &g0, int &pbuf, i
                                            const uint4 (&dg)[K / 512], float unit_scale, const float *__restrict__ scale,
                                            const int *__restrict__ rowsum, unsigned *err, long long &t_wait, Epi epi) {
     constexpr int TR = TileRows<K, 1>::v, GT = GroupTilesQ<K>::v, SP = K / 512;
-    static_assert(GT * TR <= GROWS && TR <= 8, "");
+    static_assert(GT * TR <= QGROWS && QGROWS <= 32 && TR <= 8, "");
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, rq = lane >> 2, cq = lane & 3;
     int r0, r1;
     cta_rows(R, unit, c, G, r0, r1);
