@@ -32,12 +32,12 @@ for rep in range(3):
     vc.check(L.vox_cuda_decoder_set_position(st, start, min(start, 8192)), "setpos")
     toks = np.empty(steps, np.int32)
     ms = L.vox_cuda_bench_decoder_steps(st, 32, 0, steps, vc.iptr(toks))
-    prof = (C.c_double * 7)()
+    prof = (C.c_double * 8)()
     line = f"rep {rep}: {ms:.4f} ms/step  ({WEIGHT_BYTES / ms / 1e6:.0f} GB/s)  uniq tokens {len(set(toks.tolist()))}"
     if L.vox_cuda_debug_mega_profile(st, prof) == 0 and prof[0] > 0:
         t = prof[0]
         line += (f" | cycles/step {t / steps:.0f}: wait-tiles {100 * prof[1] / t:.1f}% grid-sync {100 * prof[2] / t:.1f}% "
-                 f"(spin {100 * prof[5] / t:.1f}% atom-rtt {100 * prof[6] / t:.1f}%) attention {100 * prof[3] / t:.1f}% prologue {100 * prof[4] / t:.1f}% "
+                 f"(spin {100 * prof[5] / t:.1f}% atom-rtt {100 * prof[6] / t:.1f}%) attention {100 * prof[3] / t:.1f}% prologue {100 * prof[4] / t:.1f}% (Q8 digit prep {100 * prof[7] / t:.1f}%) "
                  f"compute+other {100 * (t - prof[1] - prof[2] - prof[3] - prof[4]) / t:.1f}%")
     print(line, flush=True)
 

@@ -988,13 +988,13 @@ __device__ __forceinline__ float norm_slice_max(SmemQ &sm, float (&xr)[DEC_DIM /
     #pragma unroll
     for (int j = 0; j < DEC_DIM / 1024; j++) {
         wv[j] = *reinterpret_cast<const float4 *>(nw + j * 1024 + col0);
+        float4 pw = wv[j];                 // w (1 + ada): for the maximum only - the norm below multiplies in the reference's order
         if (ada) {
             av[j] = *reinterpret_cast<const float4 *>(ada + j * 1024 + col0);
-            wv[j].x *= (1.0f + av[j].x); wv[j].y *= (1.0f + av[j].y); wv[j].z *= (1.0f + av[j].z); wv[j].w *= (1.0f + av[j].w);
+            pw.x *= (1.0f + av[j].x); pw.y *= (1.0f + av[j].y); pw.z *= (1.0f + av[j].z); pw.w *= (1.0f + av[j].w);
         }
-        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j] * wv[j].x)), fabsf(xr[4 * j + 1] * wv[j].y));
-        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j + 2] * wv[j].z)), fabsf(xr[4 * j + 3] * wv[j].w));
-        if (ada) wv[j] = *reinterpret_cast<const float4 *>(nw + j * 1024 + col0);      // the norm below multiplies in the reference's order
+        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j] * pw.x)), fabsf(xr[4 * j + 1] * pw.y));
+        mraw = fmaxf(fmaxf(mraw, fabsf(xr[4 * j + 2] * pw.z)), fabsf(xr[4 * j + 3] * pw.w));
     }
     ss = warp_sum(ss);
     #pragma unroll
@@ -1078,7 +1078,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
     unsigned gt = 0;                              // global index of the next phase's first tile
     int pbuf = 0;
     unsigned bar_target = P.bar_base;
-    long long t_wait = 0, t_grid = 0, t_attn = 0, t_pro = 0, t_own = 0, t_atom = 0;
+    long long t_wait = 0, t_grid = 0, t_attn = 0, t_pro = 0, t_own = 0, t_atom = 0, t_prep = 0;
     const long long t_start = clock64();
 #define MK_GRID_SYNC()                                              \
     do {                                                            \
@@ -1183,7 +1183,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
+                    { const long long tq_ = clock64(); prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn); t_prep += clock64() - tq_; }
                     t_pro += clock64() - tp;
                     if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, DEC_QKV, 2, c, G, us, L.s_wqkv, L.qs_wqkv, P.err, epi_qkv);
                     else consume_q8<DEC_DIM, true>(smq, gt, pbuf, DEC_QKV, 2, c, G, dg, us, L.s_wqkv, L.qs_wqkv, P.err, t_wait, epi_qkv);
@@ -1222,7 +1222,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_QDIM / 512];
                     float us;
-                    prep_digits<DEC_QDIM, !MK_Q8_TPW>(smq, xr, col0, dg, us);
+                    { const long long tq_ = clock64(); prep_digits<DEC_QDIM, !MK_Q8_TPW>(smq, xr, col0, dg, us); t_prep += clock64() - tq_; }
                     t_pro += clock64() - tp;
                     if constexpr (MK_Q8_TPW) consume_q8_w<DEC_QDIM, false>(smq, gt, DEC_DIM, 1, c, G, us, L.s_wo, L.qs_wo, P.err, epi_res);
                     else consume_q8<DEC_QDIM, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_wo, L.qs_wo, P.err, t_wait, epi_res);
@@ -1236,8 +1236,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             {
                 const long long tp = clock64();
                 float xr[DEC_DIM / 256];
-                if constexpr (Q8) stage_row_consts(smq, L.s_w13, L.qs_w13, 2 * DEC_HIDDEN, 2, c, G);
                 const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
+                if constexpr (Q8) stage_row_consts(smq, L.s_w13, L.qs_w13, 2 * DEC_HIDDEN, 2, c, G);
                 float mxn = -1.f;
                 if constexpr (Q8) mxn = norm_slice_max(smq, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
                 else norm_slice(sm, xr, ss, L.ffn_norm, P.ada_scale + (size_t)l * DEC_DIM, col0);
@@ -1245,7 +1245,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_DIM / 512];
                     float us;
-                    prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
+                    { const long long tq_ = clock64(); prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn); t_prep += clock64() - tq_; }
                     t_pro += clock64() - tp;
                     if constexpr (MK_Q8_TPW) consume_q8_w<DEC_DIM, true>(smq, gt, 2 * DEC_HIDDEN, 2, c, G, us, L.s_w13, L.qs_w13, P.err, epi_glu);
                     else consume_q8<DEC_DIM, true>(smq, gt, pbuf, 2 * DEC_HIDDEN, 2, c, G, dg, us, L.s_w13, L.qs_w13, P.err, t_wait, epi_glu);
@@ -1266,7 +1266,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
                 if constexpr (Q8) {
                     uint4 dg[DEC_HIDDEN / 512];
                     float us;
-                    prep_digits<DEC_HIDDEN, true>(smq, xr, col0, dg, us);
+                    { const long long tq_ = clock64(); prep_digits<DEC_HIDDEN, true>(smq, xr, col0, dg, us); t_prep += clock64() - tq_; }
                     t_pro += clock64() - tp;
                     consume_q8<DEC_HIDDEN, false>(smq, gt, pbuf, DEC_DIM, 1, c, G, dg, us, L.s_w2, L.qs_w2, P.err, t_wait, epi_res);
                 } else {
@@ -1280,8 +1280,8 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         {
             const long long tp = clock64();
             float xr[DEC_DIM / 256];
-            if constexpr (Q8) stage_row_consts(smq, P.s_tok_emb, P.qs_tok_emb, VOCAB, 1, c, G);
             const float ss = load_slice<DEC_DIM>(P.x, col0, xr);
+            if constexpr (Q8) stage_row_consts(smq, P.s_tok_emb, P.qs_tok_emb, VOCAB, 1, c, G);
             float mxn = -1.f;
             if constexpr (Q8) mxn = norm_slice_max(smq, xr, ss, P.dec_norm, nullptr, col0);
             else norm_slice(sm, xr, ss, P.dec_norm, nullptr, col0);
@@ -1297,7 +1297,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
             if constexpr (Q8) {
                 uint4 dg[DEC_DIM / 512];
                 float us;
-                prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn);
+                { const long long tq_ = clock64(); prep_digits<DEC_DIM, !MK_Q8_TPW>(smq, xr, col0, dg, us, mxn); t_prep += clock64() - tq_; }
                 t_pro += clock64() - tp;
                 if constexpr (MK_Q8_TPW) {
                     if (P.alt_on) consume_q8_w<DEC_DIM, false>(smq, gt, VOCAB, 1, c, G, us, P.s_tok_emb, P.qs_tok_emb, P.err, epi_alt);
@@ -1397,7 +1397,7 @@ __global__ void __launch_bounds__(NT, 1) dec_mega_kernel(const Params P) {
         unsigned long long *o = P.prof + (size_t)c * 32;
         o[0] = (unsigned long long)(clock64() - t_start);
         o[1] = (unsigned long long)t_wait; o[2] = (unsigned long long)t_grid;
-        o[3] = (unsigned long long)t_attn; o[4] = (unsigned long long)t_pro; o[5] = (unsigned long long)t_own; o[6] = (unsigned long long)t_atom;
+        o[3] = (unsigned long long)t_attn; o[4] = (unsigned long long)t_pro; o[5] = (unsigned long long)t_own; o[6] = (unsigned long long)t_atom; o[7] = (unsigned long long)t_prep;   // Q8: digit conversion share of the prologues
     }
 }
 
@@ -1512,14 +1512,14 @@ int dec_mega_launch(vox_cuda_state *s, int n_steps) {
 int dec_mega_attn_part_floats(void) { return mk::MAX_SPLITS * DEC_HEADS * mk::PART_LD; }
 
 // Debug: cycle counters of the last launch, averaged over CTAs:
-// out[0..4] = total, waiting for weight tiles, grid barriers, attention, prologues.
+// out[0..7] = total, waiting for weight tiles, grid barriers, attention, prologues, barrier spin, atomic round trip, Q8 digit prep.
 extern "C" int vox_cuda_debug_mega_profile(vox_cuda_state_t *s, double *out) {
     MegaHost *h = s ? (MegaHost *)s->mega : nullptr;
     if (!h || !h->d_prof) return -1;
     const int n = h->grid * 32;
     unsigned long long *buf = (unsigned long long *)malloc((size_t)n * 8);
     if (cudaMemcpy(buf, h->d_prof, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) { free(buf); return -1; }
-    for (int k = 0; k < 7; k++) {
+    for (int k = 0; k < 8; k++) {
         double a = 0;
         for (int c = 0; c < h->grid; c++) a += (double)buf[c * 32 + k];
         out[k] = a / h->grid;
