@@ -199,10 +199,38 @@ def test_q8_fp16_kv_and_alternatives(q8_env):
         e.L.vox_cuda_state_free(st)
 
 
+def test_q8_stream_group_equals_single_stream(q8_env):
+    """a Q8 model behind a stream group (lock-step decode on the swap-AB GEMM, row scale in its epilogue, embedding rows
+    = int8 row * scale): three clips of different lengths, every stream's ids = the single-stream Q8 run; fp32 and fp16 rings"""
+    import bench
+    e = q8_env
+    clips = [bench.frame_buffer(bench.synth_clip(sec, seed)) for sec, seed in ((2.0, 5), (3.1, 11), (2.4, 12))]
+    want = [_transcribe(e, bench.synth_clip(sec, seed)).tolist() for sec, seed in ((2.0, 5), (3.1, 11), (2.4, 12))]
+    for bits in (32, 16):
+        g = e.L.vox_cuda_group_create_ex(e.model, 3, 128, bits)
+        assert g, e.vc.last_error()
+        try:
+            for i, (buf, nf) in enumerate(clips):
+                assert e.L.vox_cuda_group_encode(g, i, e.vc.fptr(buf), len(buf), nf) == len(want[i]) + 38, e.vc.last_error()
+            toks = np.full((3, 64), -7, np.int32)
+            counts = np.zeros(3, np.int32)
+            steps = e.L.vox_cuda_group_decode(g, 39, e.vc.iptr(toks), 64, e.vc.iptr(counts), None)
+            assert steps == max(len(w) for w in want), (steps, e.vc.last_error())
+            same = [toks[i, :counts[i]].tolist() == want[i] for i in range(3)]
+            print(f"Q8 stream group, {bits}-bit K/V: streams equal to single-stream ids: {same}")
+            if bits == 32:
+                assert all(same)
+            else:                                             # fp16 rings: a flip may only come late (free-running)
+                for i in range(3):
+                    got = toks[i, :counts[i]]
+                    nz = np.nonzero(got != np.array(want[i]))[0]
+                    assert len(nz) == 0 or nz[0] >= 10
+        finally:
+            e.L.vox_cuda_group_free(g)
+
+
 def test_q8_refused_where_not_built(q8_env):
     e = q8_env
-    assert not e.L.vox_cuda_group_create(e.model, 4, 64)
-    assert "Q8" in e.vc.last_error()
     assert not e.L.vox_cuda_tp_create_local(e.model, 2)
     assert "Q8" in e.vc.last_error()
 

@@ -236,9 +236,10 @@ void layout_q8(vox_cuda_model *m, const vox_cuda_weights_t *w, const vox_cuda_we
     }
     m->dec_norm = (const float *)u.put(w->dec_norm, DEC_DIM * 4);
     {
-        Q8Mat t = q.begin(VOCAB, DEC_DIM, true, false);
+        // the bf16 image (805 MB) serves the stream groups' logits product and embedding rows (api_group.cu)
+        Q8Mat t = q.begin(VOCAB, DEC_DIM, true, true);
         q.part(t, qw->tok_embeddings, VOCAB, 0, 1); q.finish(t);
-        m->tok_emb = nullptr; m->q_tok_emb = t.q; m->s_tok_emb = t.s; m->qs_tok_emb = t.qs;
+        m->tok_emb = t.bf; m->q_tok_emb = t.q; m->s_tok_emb = t.s; m->qs_tok_emb = t.qs;
     }
     for (int l = 0; l < m->n_enc; l++) {
         const vox_cuda_enc_layer_w_t &s = w->enc[l];

@@ -35,12 +35,12 @@ namespace {
 __global__ void __launch_bounds__(256) group_norm_kernel(
     float *__restrict__ x, int mode, const float *__restrict__ part, int n_split, long split_stride,
     const float *__restrict__ adapter, long adapter_stride, const uint16_t *__restrict__ tok_emb,
-    const Slot *__restrict__ slots, const float *__restrict__ w, const float *__restrict__ ada,
+    const float *__restrict__ tok_scale, const Slot *__restrict__ slots, const float *__restrict__ w, const float *__restrict__ ada,
     uint16_t *__restrict__ out) {
     __shared__ float red[8];
     tcx::pdl_launch_dependents();
     tcx::pdl_wait();
-    norm_row(blockIdx.x, threadIdx.x, x, mode, part, n_split, split_stride, adapter, adapter_stride, tok_emb, slots, w, ada,
+    norm_row(blockIdx.x, threadIdx.x, x, mode, part, n_split, split_stride, adapter, adapter_stride, tok_emb, tok_scale, slots, w, ada,
              out, red, SyncThreads());
 }
 
@@ -78,12 +78,16 @@ __global__ void __launch_bounds__(256) group_kv_round_kernel(const float *__rest
 }
 
 __global__ void __launch_bounds__(256) group_embed_rows_kernel(const int *__restrict__ tokens, const float *__restrict__ adapter,
-                                                               const uint16_t *__restrict__ tok_emb, float *__restrict__ x) {
+                                                               const uint16_t *__restrict__ tok_emb, const float *__restrict__ tok_scale,
+                                                               float *__restrict__ x) {
     const int r = blockIdx.x;
     const float *a = adapter + (size_t)r * DEC_DIM;
     const uint16_t *e = tok_emb + (size_t)tokens[r] * DEC_DIM;
-    for (int i = threadIdx.x; i < DEC_DIM; i += 256)
-        x[(size_t)r * DEC_DIM + i] = a[i] + __uint_as_float(((uint32_t)e[i]) << 16);
+    const float es = tok_scale ? tok_scale[tokens[r]] : 1.0f;        // Q8 model: int-valued row * row scale
+    for (int i = threadIdx.x; i < DEC_DIM; i += 256) {
+        const float ev = __uint_as_float(((uint32_t)e[i]) << 16);
+        x[(size_t)r * DEC_DIM + i] = a[i] + (tok_scale ? ev * es : ev);
+    }
 }
 
 }  // namespace
@@ -119,7 +123,6 @@ extern "C" vox_cuda_group_t *vox_cuda_group_create_ex(vox_cuda_model_t *m, int n
         vox_set_error("group_create: need 1..%d streams, max_positions >= 2, kv_bits 32 or 16", MAX_STREAMS);
         return nullptr;
     }
-    if (m->q8) { vox_set_error("group_create: stream groups do not take a Q8 model (single-stream decoder only)"); return nullptr; }
     vox_cuda_group *g = (vox_cuda_group *)calloc(1, sizeof(vox_cuda_group));
     if (!g) return nullptr;
     g->m = m; g->B = n_streams; g->max_pos = max_positions; g->kv16 = kv_bits == 16;
@@ -159,10 +162,13 @@ extern "C" vox_cuda_group_t *vox_cuda_group_create_ex(vox_cuda_model_t *m, int n
         g->op_wo[l].out_f32 = g->part; g->op_wo[l].ldo = DEC_DIM; g->op_wo[l].split_stride = (long)B * DEC_DIM;
         g->op_w13[l].mode = WT_OUT_SWIGLU_BF16X2; g->op_w13[l].out_bf16 = g->hh_b; g->op_w13[l].ldb = 2 * DEC_HIDDEN; g->op_w13[l].lo_off = DEC_HIDDEN;
         g->op_w2[l].out_f32 = g->part; g->op_w2[l].ldo = DEC_DIM; g->op_w2[l].split_stride = (long)B * DEC_DIM;
+        // Q8 model: the weights are the int8 values as bf16, the row scale goes into the GEMM epilogue (null otherwise)
+        g->op_qkv[l].row_scale = L.s_wqkv; g->op_wo[l].row_scale = L.s_wo; g->op_w13[l].row_scale = L.s_w13; g->op_w2[l].row_scale = L.s_w2;
     }
     if (ok) {
         ok = !gemm_wt_prepare(&g->op_logits, g->NB, g->B, VOCAB, DEC_DIM, 1, g->xn_b, 2 * DEC_DIM, m->tok_emb, 1);
         g->op_logits.out_f32 = g->logits; g->op_logits.ldo = VOCAB; g->op_logits.split_stride = 0;
+        g->op_logits.row_scale = m->s_tok_emb;
     }
     if (!ok) { vox_cuda_group_free(g); return nullptr; }
     if (!g->kv16) group_mega_init(g);   // persistent step kernel, opt-in (VOX_CUDA_GROUP_MEGA=1, fp32 rings only); default: kernel per op + PDL
@@ -201,10 +207,10 @@ static int group_step(vox_cuda_group *g, int step) {
     for (int l = 0; l < m->n_dec; l++) {
         const DecLayerDev &L = m->dec[l];
         if (l == 0)
-            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 0, nullptr, 0, 0L, g->adapter, astride, m->tok_emb, g->d_slots,
+            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 0, nullptr, 0, 0L, g->adapter, astride, m->tok_emb, (const float *)(m->q8 ? m->s_tok_emb : nullptr), g->d_slots,
                                 L.attn_norm, nullptr, g->xn_b));
         else
-            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+            CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, (const float *)nullptr, g->d_slots,
                                 L.attn_norm, nullptr, g->xn_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_qkv[l])) return -1;
@@ -218,13 +224,13 @@ static int group_step(vox_cuda_group *g, int step) {
                                 g->kv_v + l * g->kv_layer, g->kv_stream, g->mask, g->att_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_wo[l])) return -1;
-        CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_WO, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+        CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_WO, (long)B * DEC_DIM, nullptr, 0L, nullptr, (const float *)nullptr, g->d_slots,
                             L.ffn_norm, m->ada_scale + (size_t)l * DEC_DIM, g->xn_b));
         LAUNCHED();
         if (gemm_wt_launch(st, &g->op_w13[l])) return -1;
         if (gemm_wt_launch(st, &g->op_w2[l])) return -1;
     }
-    CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, g->d_slots,
+    CUDA_TRY(launch_pdl(group_norm_kernel, B, 256, 0, st, g->x, 1, g->part, KS_W2, (long)B * DEC_DIM, nullptr, 0L, nullptr, (const float *)nullptr, g->d_slots,
                         m->dec_norm, nullptr, g->xn_b));
     LAUNCHED();
     if (gemm_wt_launch(st, &g->op_logits)) return -1;
@@ -282,7 +288,7 @@ extern "C" int vox_cuda_group_decode(vox_cuda_group_t *g, int prompt_len, int *t
             }
             continue;
         }
-        group_embed_rows_kernel<<<n_pre, 256, 0, st>>>(g->pf_tok, g->adapter + (size_t)b * g->max_pos * DEC_DIM, m->tok_emb, g->pf_x);
+        group_embed_rows_kernel<<<n_pre, 256, 0, st>>>(g->pf_tok, g->adapter + (size_t)b * g->max_pos * DEC_DIM, m->tok_emb, m->q8 ? m->s_tok_emb : nullptr, g->pf_x);
         LAUNCHED();
         int pos = 0, n_valid = 0;
         if (g->kv16) {

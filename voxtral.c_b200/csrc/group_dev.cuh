@@ -29,6 +29,7 @@ template <class Sync>
 __device__ __forceinline__ void norm_row(
     int b, int tid, float *__restrict__ x, int mode, const float *__restrict__ part, int n_split, long split_stride,
     const float *__restrict__ adapter, long adapter_stride, const uint16_t *__restrict__ tok_emb,
+    const float *__restrict__ tok_scale /* Q8 model: row scales of the int-valued embedding rows, else null */,
     const Slot *__restrict__ slots, const float *__restrict__ w, const float *__restrict__ ada,
     uint16_t *__restrict__ out, float *red /* smem [8] */, Sync sync) {
     float *xr = x + (size_t)b * DEC_DIM;
@@ -38,13 +39,19 @@ __device__ __forceinline__ void norm_row(
         *reinterpret_cast<int4 *>(&sl) = __ldcg(reinterpret_cast<const int4 *>(slots + b));
         const float *a = adapter + (size_t)b * adapter_stride + (size_t)sl.aidx * DEC_DIM;
         const uint16_t *e = tok_emb + (size_t)sl.prev * DEC_DIM;
+        const float es = tok_scale ? tok_scale[sl.prev] : 1.0f;      // q * scale (tok_embed_q8_to_f32, voxtral.c:443-452)
         #pragma unroll
         for (int j = 0; j < 3; j++) {
             const int col = j * 1024 + tid * 4;
             const float4 av = *reinterpret_cast<const float4 *>(a + col);
             const uint2 ev = *reinterpret_cast<const uint2 *>(e + col);
-            v[4 * j] = av.x + bf16_lo(ev.x); v[4 * j + 1] = av.y + bf16_hi(ev.x);
-            v[4 * j + 2] = av.z + bf16_lo(ev.y); v[4 * j + 3] = av.w + bf16_hi(ev.y);
+            if (tok_scale) {
+                v[4 * j] = av.x + bf16_lo(ev.x) * es; v[4 * j + 1] = av.y + bf16_hi(ev.x) * es;
+                v[4 * j + 2] = av.z + bf16_lo(ev.y) * es; v[4 * j + 3] = av.w + bf16_hi(ev.y) * es;
+            } else {
+                v[4 * j] = av.x + bf16_lo(ev.x); v[4 * j + 1] = av.y + bf16_hi(ev.x);
+                v[4 * j + 2] = av.z + bf16_lo(ev.y); v[4 * j + 3] = av.w + bf16_hi(ev.y);
+            }
         }
     } else {
         #pragma unroll

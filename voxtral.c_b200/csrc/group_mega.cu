@@ -292,10 +292,10 @@ __global__ void __launch_bounds__(NT, 1) group_mega_kernel(const MParams P) {
                 GM_T0();
                 if (b_own < P.B) {
                     if (l == 0)
-                        norm_row(b_own, wtid, P.x, 0, nullptr, 0, 0L, P.adapter, P.adapter_stride, P.tok_emb, P.slots,
+                        norm_row(b_own, wtid, P.x, 0, nullptr, 0, 0L, P.adapter, P.adapter_stride, P.tok_emb, nullptr, P.slots,
                                  T.attn_norm[l], nullptr, P.xn_b, mi.red, wsync);
                     else
-                        norm_row(b_own, wtid, P.x, 1, P.part, KS_W2, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, P.slots,
+                        norm_row(b_own, wtid, P.x, 1, P.part, KS_W2, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, nullptr, P.slots,
                                  T.attn_norm[l], nullptr, P.xn_b, mi.red, wsync);
                 }
                 GM_ACC(t_n);
@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(NT, 1) group_mega_kernel(const MParams P) {
                 // N2
                 GM_T0();
                 if (b_own < P.B)
-                    norm_row(b_own, wtid, P.x, 1, P.part, KS_WO, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, P.slots,
+                    norm_row(b_own, wtid, P.x, 1, P.part, KS_WO, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, nullptr, P.slots,
                              T.ffn_norm[l], P.ada_scale + (size_t)l * DEC_DIM, P.xn_b, mi.red, wsync);
                 GM_ACC(t_n);
                 GM_BAR();
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(NT, 1) group_mega_kernel(const MParams P) {
             }
             GM_T0();
             if (b_own < P.B)
-                norm_row(b_own, wtid, P.x, 1, P.part, KS_W2, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, P.slots,
+                norm_row(b_own, wtid, P.x, 1, P.part, KS_W2, (long)P.B * DEC_DIM, nullptr, 0L, nullptr, nullptr, P.slots,
                          P.dec_norm, nullptr, P.xn_b, mi.red, wsync);
             GM_ACC(t_n);
             GM_BAR();
@@ -385,6 +385,7 @@ int group_mega_init(vox_cuda_group *g) {
     // the 185 grid barriers cost what the PDL launches cost), so the per-op path is the default.
     const char *env = getenv("VOX_CUDA_GROUP_MEGA");
     if (!env || !atoi(env)) return -1;
+    if (g->m->q8) return -1;                     // the persistent step kernel has no row-scale epilogue: Q8 groups run per op
     int dev = 0, sms = 0, coop = 0, occ = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

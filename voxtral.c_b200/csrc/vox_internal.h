@@ -56,7 +56,7 @@ struct vox_cuda_model {
     size_t arena_bytes;
     DecLayerDev dec[VOX_CUDA_DEC_LAYERS];
     EncLayerDev enc[VOX_CUDA_ENC_LAYERS];
-    const uint16_t *tok_emb;   // [131072,3072] (null for a Q8 model)
+    const uint16_t *tok_emb;   // [131072,3072] (Q8 model: the int8 values as bf16, to be scaled by s_tok_emb)
     int q8;                    // 1: created by vox_cuda_model_create_q8
     const int8_t *q_tok_emb;   // [131072,3072] int8
     const float *s_tok_emb;    // [131072]
