@@ -24,7 +24,7 @@ constexpr int NT_ROW = DEC_DIM / 4;                          // 768 threads: one
 struct PfWt {
     uint16_t *xn_t, *att_t, *hh_t;                           // split-bf16 rows [64][2*3072], [64][2*4096], [64][2*9216]
     float *part;                                             // K-range partials
-    float *qkv, *att;                                        // [64][6144] (q rotated in place), [64][4096]
+    float *qkv;                                              // [64][6144] fp32: q (rotated) for the attention; k / v go to the ring
     WtOp *ops;                                               // [n_dec][4]
 };
 
@@ -114,11 +114,11 @@ PfWt *pf_get(vox_cuda_state *s) {
     if (!q) return nullptr;
     const size_t part_f = (size_t)KS_QKV * PW_NB * DEC_QKV > (size_t)KS_W2 * PW_NB * DEC_DIM ? (size_t)KS_QKV * PW_NB * DEC_QKV
                                                                                            : (size_t)KS_W2 * PW_NB * DEC_DIM;
-    const size_t bytes[6] = {(size_t)PW_NB * 2 * DEC_DIM * 2, (size_t)PW_NB * 2 * DEC_QDIM * 2, (size_t)PW_NB * 2 * DEC_HIDDEN * 2,
-                             part_f * 4, (size_t)PW_NB * DEC_QKV * 4, (size_t)PW_NB * DEC_QDIM * 4};
-    void **ptrs[6] = {(void **)&q->xn_t, (void **)&q->att_t, (void **)&q->hh_t, (void **)&q->part, (void **)&q->qkv, (void **)&q->att};
+    const size_t bytes[5] = {(size_t)PW_NB * 2 * DEC_DIM * 2, (size_t)PW_NB * 2 * DEC_QDIM * 2, (size_t)PW_NB * 2 * DEC_HIDDEN * 2,
+                             part_f * 4, (size_t)PW_NB * DEC_QKV * 4};
+    void **ptrs[5] = {(void **)&q->xn_t, (void **)&q->att_t, (void **)&q->hh_t, (void **)&q->part, (void **)&q->qkv};
     bool ok = true;
-    for (int i = 0; i < 6 && ok; i++)
+    for (int i = 0; i < 5 && ok; i++)
         ok = cudaMalloc(ptrs[i], bytes[i]) == cudaSuccess && cudaMemsetAsync(*ptrs[i], 0, bytes[i], s->stream) == cudaSuccess;
     q->ops = ok ? (WtOp *)aligned_alloc(64, sizeof(WtOp) * 4 * m->n_dec) : nullptr;
     ok = ok && q->ops;
@@ -138,7 +138,7 @@ PfWt *pf_get(vox_cuda_state *s) {
     }
     if (!ok) {
         vox_set_error("prefill (skinny GEMM path): setup failed");
-        cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part); cudaFree(q->qkv); cudaFree(q->att);
+        cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part); cudaFree(q->qkv);
         free(q->ops); free(q);
         return nullptr;
     }
@@ -151,7 +151,7 @@ PfWt *pf_get(vox_cuda_state *s) {
 void dec_prefill_wt_free(vox_cuda_state *s) {
     PfWt *q = (PfWt *)s->pf_wt;
     if (!q) return;
-    cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part); cudaFree(q->qkv); cudaFree(q->att);
+    cudaFree(q->xn_t); cudaFree(q->att_t); cudaFree(q->hh_t); cudaFree(q->part); cudaFree(q->qkv);
     free(q->ops); free(q);
     s->pf_wt = nullptr;
 }
