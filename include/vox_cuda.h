@@ -368,6 +368,11 @@ vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int world);
 /* all `world` ranks on THIS device, run kernel by kernel in lock step: checks the shard
  * arithmetic and the exchange protocol on one GPU (not a fast path) */
 vox_cuda_tp_t *vox_cuda_tp_create_local(vox_cuda_model_t *m, int world);
+/* kv_bits 32 = the two calls above; 16 = this rank's K/V rings in fp16 (the reference's GPU default
+ * "fp16 KV", voxtral.c:189-190; same rounding rule and the same prompt-prefill limits as vox_cuda_state_create_ex).
+ * No counterpart call in the reference (it has no multi-device code). */
+vox_cuda_tp_t *vox_cuda_tp_create_ex(vox_cuda_model_t *m, int rank, int world, int kv_bits);
+vox_cuda_tp_t *vox_cuda_tp_create_local_ex(vox_cuda_model_t *m, int world, int kv_bits);
 int  vox_cuda_tp_export(vox_cuda_tp_t *tp, void *handle_out /* VOX_CUDA_TP_HANDLE_BYTES */);
 int  vox_cuda_tp_connect(vox_cuda_tp_t *tp, const void *handles /* world x VOX_CUDA_TP_HANDLE_BYTES, rank order */);
 vox_cuda_state_t *vox_cuda_tp_state(vox_cuda_tp_t *tp);

@@ -67,6 +67,40 @@ def test_tp_lockstep_ids_equal_single_stream(full_env, world):
         e.L.vox_cuda_tp_free(tp)
 
 
+@pytest.mark.parametrize("world", [2, 4])
+def test_tp_fp16_kv_rings(full_env, world):
+    """SURVEY 8(f2) for the tensor-parallel decoder: vox_cuda_tp_create_local_ex(model, world, 16) - every rank's K/V rows
+    rounded to fp16 when appended.  Stated as a tolerance against the fp32-ring tensor-parallel run on the same clip (the
+    fp32 BLAS oracle cannot pin a 16-bit cache bit for bit): last-step logits within KV16_LOGIT_TOL, ids equal up to the
+    first step whose margin is within reach of that difference (free-running afterwards)."""
+    from test_gpu_kv16 import KV16_LOGIT_TOL
+    e = full_env
+    buf, nf = _clip(2.0, 5)
+    out = []
+    for bits in (32, 16):
+        tp = e.L.vox_cuda_tp_create_local_ex(e.model, world, bits)
+        assert tp, e.vc.last_error()
+        try:
+            assert e.L.vox_cuda_state_kv_bits(e.L.vox_cuda_tp_state(tp)) == bits
+            toks = np.empty(nf // 8 + 8, np.int32)
+            n = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+            assert n > 0, e.vc.last_error()
+            logits = np.empty(131072, np.float32)
+            assert e.L.vox_cuda_decoder_read_logits(e.L.vox_cuda_tp_state(tp), e.vc.fptr(logits)) == 0
+            out.append((toks[:n].copy(), logits))
+        finally:
+            e.L.vox_cuda_tp_free(tp)
+    (t32, l32), (t16, l16) = out
+    assert len(t32) == len(t16)
+    nz = np.nonzero(t32 != t16)[0]
+    d = float(np.abs(l32 - l16).max())
+    print(f"TP x{world}: fp16 vs fp32 K/V rings: {len(t32) - len(nz)} of {len(t32)} ids equal, last-step max|dlogit| {d:.2e}")
+    if len(nz) == 0:
+        assert d < KV16_LOGIT_TOL
+    else:
+        assert nz[0] >= 10
+
+
 def test_tp_argument_errors(full_env):
     e = full_env
     assert not e.L.vox_cuda_tp_create_local(e.model, 3)

@@ -171,11 +171,11 @@ constexpr int FULL_NW = 2, FULL_NCH = DEC_DIM / 256;      // K = 3072 kernels: 2
 // T1: this rank's rows of wq|wk|wv on rmsnorm(x); RoPE; q -> q_out, K/V -> ring slot
 // (voxtral_decoder.c:710-725).  Buffers keep GLOBAL row / head indices; a rank touches its slice only.
 // ---------------------------------------------------------------------------
-template <bool REDUCE>
+template <bool REDUCE, class KV>
 __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     TpDev td, int a_idx, const DecStepParams *__restrict__ p, const float *__restrict__ x_in,
     float *__restrict__ x_out, const float *__restrict__ attn_norm, const uint16_t *__restrict__ wqkv,
-    const float *__restrict__ rope, float *__restrict__ q_out, float *__restrict__ kc, float *__restrict__ vc, int cs) {
+    const float *__restrict__ rope, float *__restrict__ q_out, KV *__restrict__ kc, KV *__restrict__ vc, int cs) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float4 xs[DEC_DIM / 4];               // cluster gather buffer (cs > 1)
     __shared__ float red[TP_WARPS];
@@ -209,11 +209,9 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
                 const float r0 = v0 * c - v1 * s, r1 = v0 * s + v1 * c;
                 v0 = r0; v1 = r1;
             }
-            float *dst;
-            if (row < DEC_QDIM) dst = q_out + row;
-            else if (row < DEC_QDIM + DEC_KVDIM) dst = kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM);
-            else dst = vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM);
-            *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
+            if (row < DEC_QDIM) *reinterpret_cast<float2 *>(q_out + row) = make_float2(v0, v1);
+            else if (row < DEC_QDIM + DEC_KVDIM) tp_st_kv2(kc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM), v0, v1);
+            else tp_st_kv2(vc + (size_t)slot * DEC_KVDIM + (row - DEC_QDIM - DEC_KVDIM), v0, v1);
         }
     }
 }
@@ -225,9 +223,10 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
 // 8 x 4 scores are reduced across lanes by a transposed butterfly) - the scheme of the single-stream
 // kernel (dec_mega.cu) and of group_dev.cuh.  The CTA that arrives last for a kv head merges the splits.
 // ---------------------------------------------------------------------------
+template <class KV>
 __global__ void __launch_bounds__(TP_THREADS) tp_attn_kernel(
-    TpDev td, const DecStepParams *__restrict__ p, const float *__restrict__ q, const float *__restrict__ kc,
-    const float *__restrict__ vc, float *__restrict__ part, float *__restrict__ attn_out) {
+    TpDev td, const DecStepParams *__restrict__ p, const float *__restrict__ q, const KV *__restrict__ kc,
+    const KV *__restrict__ vc, float *__restrict__ part, float *__restrict__ attn_out) {
     __shared__ __align__(16) TpAttnSmem sm;
     tcx::pdl_wait();
     tcx::pdl_launch_dependents();
@@ -469,11 +468,12 @@ static int tp_rank_init(vox_cuda_tp *tp, TpRank &R, int rank) {
     return 0;
 }
 
-static vox_cuda_tp *tp_alloc(vox_cuda_model *m, int world) {
+static vox_cuda_tp *tp_alloc(vox_cuda_model *m, int world, int kv_bits = 32) {
     if (!m || !tp_valid_world(world)) { vox_set_error("tp: world size must be 1, 2, 4 or 8"); return nullptr; }
+    if (kv_bits != 32 && kv_bits != 16) { vox_set_error("tp: kv_bits must be 32 or 16"); return nullptr; }
     vox_cuda_tp *tp = (vox_cuda_tp *)calloc(1, sizeof(vox_cuda_tp));
     tp->m = m; tp->world = world;
-    tp->s = vox_cuda_state_create(m);
+    tp->s = vox_cuda_state_create_ex(m, kv_bits);
     if (!tp->s) { free(tp); return nullptr; }
     // key splits: enough CTAs to pull a long context at HBM speed, few enough that the merge stays short
     const int kh = DEC_KVH / world;
@@ -499,8 +499,12 @@ extern "C" void vox_cuda_tp_free(vox_cuda_tp_t *tp) {
 
 // One rank of a world of `world` processes (one per GPU).  Peers are attached with export / connect.
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int world) {
+    return vox_cuda_tp_create_ex(m, rank, world, 32);
+}
+
+extern "C" vox_cuda_tp_t *vox_cuda_tp_create_ex(vox_cuda_model_t *m, int rank, int world, int kv_bits) {
     if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
-    vox_cuda_tp *tp = tp_alloc(m, world);
+    vox_cuda_tp *tp = tp_alloc(m, world, kv_bits);
     if (!tp) return nullptr;
     if (rank < 0 || rank >= world) { vox_set_error("tp: rank %d outside world %d", rank, world); vox_cuda_tp_free(tp); return nullptr; }
     tp->n_local = 1;
@@ -511,7 +515,7 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
         // (profiles/r01_j_tp_decode.md): 1.067 vs 1.077 ms per token at 2 GPUs, 0.810 vs 0.868 at 4 - a grid barrier
         // costs more than a PDL kernel boundary whose successor already runs beside its predecessor.
         const char *env = getenv("VOX_CUDA_TP_MEGA");
-        if (env && atoi(env) != 0) tp->mega = tp_mega_create(m, world);
+        if (env && atoi(env) != 0 && !tp->s->kv16) tp->mega = tp_mega_create(m, world);   // the persistent engine reads fp32 rings only
     }
     return tp;
 }
@@ -520,8 +524,12 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
 // arithmetic, the exchange windows and the sequence numbers are those of the multi-GPU run, so one GPU is
 // enough to check them (tests/test_gpu_tp.py).  Not a fast path: every kernel is launched `world` times.
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create_local(vox_cuda_model_t *m, int world) {
+    return vox_cuda_tp_create_local_ex(m, world, 32);
+}
+
+extern "C" vox_cuda_tp_t *vox_cuda_tp_create_local_ex(vox_cuda_model_t *m, int world, int kv_bits) {
     if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
-    vox_cuda_tp *tp = tp_alloc(m, world);
+    vox_cuda_tp *tp = tp_alloc(m, world, kv_bits);
     if (!tp) return nullptr;
     for (int i = 0; i < world; i++) {
         if (tp_rank_init(tp, tp->r[i], i)) { tp->n_local = i + 1; vox_cuda_tp_free(tp); return nullptr; }
@@ -655,25 +663,38 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
     for (int l = 0; l < L; l++) {
         const DecLayerDev &W = m->dec[l];
         float *kc = s->kv_k + l * kv_layer, *vc = s->kv_v + l * kv_layer;
+        __half *kc16 = (__half *)s->kv_k16 + l * kv_layer, *vc16 = (__half *)s->kv_v16 + l * kv_layer;   // fp16 rings (kv16 states)
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
             const int a = 2 * l - 1;              // consumes the w2 exchange of the previous layer
             const DecStepParams *pp = R.d_params;
-            if (l == 0)
-                CUDA_TRY(launch_pdl(tp_qkv_kernel<false>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
-                                    (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, 1));
-            else {
+            if (l == 0) {
+                if (s->kv16)
+                    CUDA_TRY(launch_pdl(tp_qkv_kernel<false, __half>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
+                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, 1));
+                else
+                    CUDA_TRY(launch_pdl(tp_qkv_kernel<false, float>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
+                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, 1));
+            } else {
                 int g = tp_grid(DEC_QKV / G);
                 const int cs = tp_cluster_size(G, g);
                 g -= g % cs;
-                CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
-                                       R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, cs));
+                if (s->kv16)
+                    CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true, __half>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
+                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, cs));
+                else
+                    CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true, float>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
+                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, cs));
             }
         }
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
-            CUDA_TRY(launch_pdl(tp_attn_kernel, dim3(DEC_KVH / G, tp->att_splits), TP_THREADS, 0, st, R.dev, (const DecStepParams *)R.d_params,
-                                (const float *)s->d_q, (const float *)kc, (const float *)vc, tp->attn_part, s->d_attn));
+            if (s->kv16)
+                CUDA_TRY(launch_pdl(tp_attn_kernel<__half>, dim3(DEC_KVH / G, tp->att_splits), TP_THREADS, 0, st, R.dev, (const DecStepParams *)R.d_params,
+                                    (const float *)s->d_q, (const __half *)kc16, (const __half *)vc16, tp->attn_part, s->d_attn));
+            else
+                CUDA_TRY(launch_pdl(tp_attn_kernel<float>, dim3(DEC_KVH / G, tp->att_splits), TP_THREADS, 0, st, R.dev, (const DecStepParams *)R.d_params,
+                                    (const float *)s->d_q, (const float *)kc, (const float *)vc, tp->attn_part, s->d_attn));
         }
         for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM));
         for (int i = 0; i < NL; i++) {

@@ -1,6 +1,7 @@
 // dec_tp_dev.cuh - device side of the tensor-parallel decoder shared by the kernel-per-op step (dec_tp.cu) and
 // the persistent step kernel (dec_tp_mega.cu): exchange window layout and words, row-batch GEMV, attention task.
 #pragma once
+#include <cuda_fp16.h>
 #include "vox_internal.h"
 #include "tc_ptx.cuh"
 
@@ -114,9 +115,22 @@ struct __align__(16) TpAttnSmem {
 
 // One (local kv head lk, key split) task of the attention on 256 threads: see tp_attn_kernel in dec_tp.cu.
 // q is read through L2 (another CTA of a persistent kernel may have written it).  Ends with the block in sync.
+// K/V ring element: float, or __half (vox_cuda_tp_create_ex(.., 16): rows rounded once when appended, widened when read -
+// the arrangement of vox_cuda_state_create_ex, dec_mega.cu)
+__device__ __forceinline__ float4 tp_ld_kv4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ float4 tp_ld_kv4(const __half *p) {
+    const uint2 u = __ldcg(reinterpret_cast<const uint2 *>(p));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void tp_st_kv2(float *p, float a, float b) { *reinterpret_cast<float2 *>(p) = make_float2(a, b); }
+__device__ __forceinline__ void tp_st_kv2(__half *p, float a, float b) { *reinterpret_cast<__half2 *>(p) = __floats2half2_rn(a, b); }
+
+template <class KV>
 __device__ __forceinline__ void tp_attn_task(const TpDev &td, int lk, int split, int ns, int pos, int n_valid,
-                                             const float *__restrict__ q, const float *__restrict__ kc,
-                                             const float *__restrict__ vc, float *__restrict__ part,
+                                             const float *__restrict__ q, const KV *__restrict__ kc,
+                                             const KV *__restrict__ vc, float *__restrict__ part,
                                              float *__restrict__ attn_out, TpAttnSmem &sm) {
     float (*qs)[DEC_HD] = sm.qs;
     float (*wsm)[4][DEC_HD + 4] = sm.wsm;
@@ -150,8 +164,8 @@ __device__ __forceinline__ void tp_attn_task(const TpDev &td, int lk, int split,
         #pragma unroll
         for (int i = 0; i < 8; i++) {
             const int slot = (first + j0 + min(i, nv - 1)) & (DEC_WINDOW - 1);   // clamped: always a valid row
-            kf[i] = __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)slot * DEC_KVDIM + hoff));
-            vf[i] = __ldcg(reinterpret_cast<const float4 *>(vc + (size_t)slot * DEC_KVDIM + hoff));
+            kf[i] = tp_ld_kv4(kc + (size_t)slot * DEC_KVDIM + hoff);
+            vf[i] = tp_ld_kv4(vc + (size_t)slot * DEC_KVDIM + hoff);
         }
         float v[32];
         #pragma unroll

@@ -126,6 +126,8 @@ SIGNATURES = {
     "vox_cuda_window_rms": (C.c_int, [f32p, C.c_int, C.c_int, f32p]),
     "vox_cuda_tp_create": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_tp_create_local": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "vox_cuda_tp_create_ex": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "vox_cuda_tp_create_local_ex": (C.c_void_p, [C.c_void_p, C.c_int, C.c_int]),
     "vox_cuda_tp_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vox_cuda_tp_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
     "vox_cuda_tp_state": (C.c_void_p, [C.c_void_p]),
