@@ -118,10 +118,9 @@ vox_cuda_model_t *vox_cuda_model_create(const vox_cuda_weights_t *w);
  * path: y = (sum_k q[n][k] * x[k]) * scale[n] with the sum exact to fp32 class (voxtral_kernels.c:277-310 for
  * M = 1; for M > 1 the reference widens q * scale to fp32 and calls sgemm, :322-336 - the same product up to
  * one fp32 rounding per weight).  The single-stream decoder streams the int8 rows (half the bytes per token);
- * encoder, adapter, prompt prefill and the stream groups' lock-step decode run on the tcgen05 GEMMs with the
- * scale in the epilogue (their weights are the int8 values held as bf16: no byte saving there).  The
- * tensor-parallel decoder refuses a Q8 model (vox_cuda_tp_create* return NULL with an error - not a
- * fallback), as do the legacy graph engine and the fp32 debug modes. */
+ * encoder, adapter, prompt prefill, the stream groups' lock-step decode and the tensor-parallel decoder run on
+ * the int8 values held as bf16 with the scale applied to each product (no byte saving there).  Only the legacy
+ * graph engine and the fp32 debug modes refuse a Q8 model (an error - not a fallback). */
 vox_cuda_model_t *vox_cuda_model_create_q8(const vox_cuda_weights_t *w, const vox_cuda_weights_q8_t *q);
 int  vox_cuda_model_is_q8(const vox_cuda_model_t *m);
 /* vox_set_delay recomputes ada_scale on the host (voxtral.c:1681-1687). */

@@ -229,10 +229,30 @@ def test_q8_stream_group_equals_single_stream(q8_env):
             e.L.vox_cuda_group_free(g)
 
 
-def test_q8_refused_where_not_built(q8_env):
+@pytest.mark.parametrize("world,bits", [(2, 32), (4, 16)])
+def test_q8_tensor_parallel_lockstep(q8_env, world, bits):
+    """a Q8 model behind the tensor-parallel decoder (all ranks on this GPU in lock step, vox_cuda_tp_create_local_ex): row
+    scales applied in every shard's GEMV, embedding row = int8 row * scale; ids = the single-stream Q8 ids of the clip"""
+    import bench
     e = q8_env
-    assert not e.L.vox_cuda_tp_create_local(e.model, 2)
-    assert "Q8" in e.vc.last_error()
+    x = bench.synth_clip(2.0, 5)
+    want = _transcribe(e, x).tolist()
+    buf, nf = bench.frame_buffer(x)
+    tp = e.L.vox_cuda_tp_create_local_ex(e.model, world, bits)
+    assert tp, e.vc.last_error()
+    try:
+        toks = np.empty(nf // 8 + 8, np.int32)
+        n = e.L.vox_cuda_tp_transcribe(tp, e.vc.fptr(buf), len(buf), nf, 39, e.vc.iptr(toks), len(toks), None)
+        assert n == len(want), e.vc.last_error()
+        got = toks[:n].tolist()
+        print(f"Q8, TP x{world}, {bits}-bit K/V: {sum(a == b for a, b in zip(got, want))} of {n} ids equal the single-stream Q8 ids")
+        if bits == 32:
+            assert got == want
+        else:
+            nz = [i for i, (a, b) in enumerate(zip(got, want)) if a != b]
+            assert not nz or nz[0] >= 10
+    finally:
+        e.L.vox_cuda_tp_free(tp)
 
 
 def test_q8_dropin_cli(q8_env, tmp_path):

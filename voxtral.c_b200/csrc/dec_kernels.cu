@@ -88,7 +88,7 @@ __device__ __forceinline__ void load_x_norm(XSmem<K> &xs, const float *__restric
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) dec_embed_kernel(
     const DecStepParams *__restrict__ p, const float *__restrict__ embed_in,
-    const float *__restrict__ adapter, const uint16_t *__restrict__ tok_emb,
+    const float *__restrict__ adapter, const uint16_t *__restrict__ tok_emb, const float *__restrict__ tok_scale,
     const float *__restrict__ inv_freq, float *__restrict__ x, float *__restrict__ rope) {
     const int t = threadIdx.x;
     if (p->use_host_embed) {
@@ -96,8 +96,14 @@ __global__ void __launch_bounds__(256) dec_embed_kernel(
     } else {
         const float *a = adapter + (size_t)p->adapter_index * DEC_DIM;
         const uint16_t *e = tok_emb + (size_t)p->prev_token * DEC_DIM;
-        for (int i = t; i < DEC_DIM; i += 256)
-            x[i] = a[i] + __uint_as_float(((uint32_t)e[i]) << 16);
+        if (tok_scale) {                  // Q8 model: int-valued row * row scale (tok_embed_q8_to_f32, voxtral.c:443-452)
+            const float es = tok_scale[p->prev_token];
+            for (int i = t; i < DEC_DIM; i += 256)
+                x[i] = a[i] + __uint_as_float(((uint32_t)e[i]) << 16) * es;
+        } else {
+            for (int i = t; i < DEC_DIM; i += 256)
+                x[i] = a[i] + __uint_as_float(((uint32_t)e[i]) << 16);
+        }
     }
     if (t < DEC_HD / 2) {
         const float angle = (float)p->pos * inv_freq[t];
@@ -423,8 +429,8 @@ __global__ void __launch_bounds__(1024) dec_argmax_final_kernel(
 // the attention of a contiguous range of kv heads (a rank's shard).
 // ---------------------------------------------------------------------------
 void dec_launch_embed(cudaStream_t st, const DecStepParams *p, const float *embed_in, const float *adapter,
-                      const uint16_t *tok_emb, const float *inv_freq, float *x, float *rope) {
-    dec_embed_kernel<<<1, 256, 0, st>>>(p, embed_in, adapter, tok_emb, inv_freq, x, rope);
+                      const uint16_t *tok_emb, const float *tok_scale, const float *inv_freq, float *x, float *rope) {
+    dec_embed_kernel<<<1, 256, 0, st>>>(p, embed_in, adapter, tok_emb, tok_scale, inv_freq, x, rope);
     LAUNCHED();
 }
 
@@ -441,7 +447,7 @@ void dec_launch_attn(cudaStream_t st, const DecStepParams *p, const float *q, co
 int dec_launch_step(vox_cuda_state *s, cudaStream_t st) {
     vox_cuda_model *m = s->m;
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
-    dec_embed_kernel<<<1, 256, 0, st>>>(s->d_params, s->d_embed_in, s->adapter_buf, m->tok_emb,
+    dec_embed_kernel<<<1, 256, 0, st>>>(s->d_params, s->d_embed_in, s->adapter_buf, m->tok_emb, (const float *)nullptr,
                                         m->inv_freq_dec, s->d_x, s->d_rope);
     LAUNCHED();
     static bool attr_set = false;

@@ -175,7 +175,8 @@ template <bool REDUCE, class KV>
 __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
     TpDev td, int a_idx, const DecStepParams *__restrict__ p, const float *__restrict__ x_in,
     float *__restrict__ x_out, const float *__restrict__ attn_norm, const uint16_t *__restrict__ wqkv,
-    const float *__restrict__ rope, float *__restrict__ q_out, KV *__restrict__ kc, KV *__restrict__ vc, int cs) {
+    const float *__restrict__ rope, float *__restrict__ q_out, KV *__restrict__ kc, KV *__restrict__ vc, int cs,
+    const float *__restrict__ row_scale /* Q8 model: scale of matrix row n (the weights are the int8 values as bf16), else null */) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float4 xs[DEC_DIM / 4];               // cluster gather buffer (cs > 1)
     __shared__ float red[TP_WARPS];
@@ -203,6 +204,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_qkv_kernel(
         if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, wqkv + (size_t)grow_of(b) * DEC_DIM, DEC_DIM, DEC_DIM);
         if (lane == 0) {
             float v0 = acc[0], v1 = acc[1];
+            if (row_scale) { v0 *= row_scale[row]; v1 *= row_scale[row + 1]; }
             if (row < DEC_QDIM + DEC_KVDIM) {     // interleaved-pair rotation, voxtral_kernels.c:631-655
                 const int d = (row & (DEC_HD - 1)) >> 1;
                 const float c = rope[2 * d], s = rope[2 * d + 1];
@@ -241,7 +243,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_attn_kernel(
 // ---------------------------------------------------------------------------
 template <int NW, int NCH>
 __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
-    TpDev td, int a_idx, const float *__restrict__ v, const uint16_t *__restrict__ W, int K) {
+    TpDev td, int a_idx, const float *__restrict__ v, const uint16_t *__restrict__ W, int K, const float *__restrict__ row_scale) {
     extern __shared__ __align__(16) unsigned char tp_smem[];
     const int ks = K / td.world;
     float4 *xA = reinterpret_cast<float4 *>(tp_smem);
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
         if (b < nbatch) tp_wload<NW, NCH>(w, Ws + (size_t)b * NW * K, (size_t)K, ks);
         if (dst) {                              // lane p sends the sums to rank p: value and flag in one 8-byte word
             #pragma unroll
-            for (int r = 0; r < NW; r++) st_ll(dst + row0 + r, __float_as_uint(acc[r]), seq);
+            for (int r = 0; r < NW; r++) st_ll(dst + row0 + r, __float_as_uint(row_scale ? acc[r] * row_scale[row0 + r] : acc[r]), seq);
         }
     }
 }
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_gemv_partial_kernel(
 __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
     TpDev td, int a_idx, const float *__restrict__ x_in, float *__restrict__ x_out,
     const float *__restrict__ ffn_norm, const float *__restrict__ ada, const uint16_t *__restrict__ w13,
-    float *__restrict__ h, int cs) {
+    float *__restrict__ h, int cs, const float *__restrict__ row_scale) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float4 xs[DEC_DIM / 4];
     __shared__ float red[TP_WARPS];
@@ -300,7 +302,10 @@ __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
         const int row = row_base + b * FULL_NW;
         b += nwarps;
         if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, w13 + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
-        if (lane == 0) h[row >> 1] = silu(acc[0]) * acc[1];
+        if (lane == 0) {
+            if (row_scale) { acc[0] *= row_scale[row]; acc[1] *= row_scale[row + 1]; }
+            h[row >> 1] = silu(acc[0]) * acc[1];
+        }
     }
 }
 
@@ -309,7 +314,8 @@ __global__ void __launch_bounds__(TP_THREADS) tp_ffn_kernel(
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
     TpDev td, int a_idx, const float *__restrict__ x_in, const float *__restrict__ norm,
-    const uint16_t *__restrict__ tok_emb, float *__restrict__ logits, float *__restrict__ blockmax, int cs) {
+    const uint16_t *__restrict__ tok_emb, float *__restrict__ logits, float *__restrict__ blockmax, int cs,
+    const float *__restrict__ row_scale) {
     __shared__ float4 xA[DEC_DIM / 8], xB[DEC_DIM / 8];
     __shared__ float4 xs[DEC_DIM / 4];
     __shared__ float red[TP_WARPS];
@@ -331,6 +337,7 @@ __global__ void __launch_bounds__(TP_THREADS) tp_logits_kernel(
         b += nwarps;
         if (b < nbatch) tp_wload<FULL_NW, FULL_NCH>(w, tok_emb + (size_t)(row_base + b * FULL_NW) * DEC_DIM, DEC_DIM, DEC_DIM);
         if (lane == 0) {
+            if (row_scale) { acc[0] *= row_scale[row]; acc[1] *= row_scale[row + 1]; }
             *reinterpret_cast<float2 *>(logits + row) = make_float2(acc[0], acc[1]);
             tp_argmax_merge(bv, bi, acc[0], row);
             tp_argmax_merge(bv, bi, acc[1], row + 1);
@@ -503,7 +510,6 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create(vox_cuda_model_t *m, int rank, int 
 }
 
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create_ex(vox_cuda_model_t *m, int rank, int world, int kv_bits) {
-    if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
     vox_cuda_tp *tp = tp_alloc(m, world, kv_bits);
     if (!tp) return nullptr;
     if (rank < 0 || rank >= world) { vox_set_error("tp: rank %d outside world %d", rank, world); vox_cuda_tp_free(tp); return nullptr; }
@@ -515,7 +521,7 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create_ex(vox_cuda_model_t *m, int rank, i
         // (profiles/r01_j_tp_decode.md): 1.067 vs 1.077 ms per token at 2 GPUs, 0.810 vs 0.868 at 4 - a grid barrier
         // costs more than a PDL kernel boundary whose successor already runs beside its predecessor.
         const char *env = getenv("VOX_CUDA_TP_MEGA");
-        if (env && atoi(env) != 0 && !tp->s->kv16) tp->mega = tp_mega_create(m, world);   // the persistent engine reads fp32 rings only
+        if (env && atoi(env) != 0 && !tp->s->kv16 && !m->q8) tp->mega = tp_mega_create(m, world);   // the persistent engine: fp32 rings, bf16 models
     }
     return tp;
 }
@@ -528,7 +534,6 @@ extern "C" vox_cuda_tp_t *vox_cuda_tp_create_local(vox_cuda_model_t *m, int worl
 }
 
 extern "C" vox_cuda_tp_t *vox_cuda_tp_create_local_ex(vox_cuda_model_t *m, int world, int kv_bits) {
-    if (m && m->q8) { vox_set_error("tp: the tensor-parallel decoder does not take a Q8 model"); return nullptr; }
     vox_cuda_tp *tp = tp_alloc(m, world, kv_bits);
     if (!tp) return nullptr;
     for (int i = 0; i < world; i++) {
@@ -590,7 +595,7 @@ static inline int tp_step_kernels(const vox_cuda_tp *tp) { return 1 + 5 * tp->m-
 
 // wo / w2 slices: (rows per warp, 256-column chunks) so that a lane has 32-40 loads of 16 B in flight
 template <int NW, int NCH>
-static cudaError_t tp_launch_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K) {
+static cudaError_t tp_launch_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K, const float *row_scale) {
     const int ks = K / td.world;
     const size_t smem = (size_t)ks * 4;
     static bool attr = false;
@@ -600,21 +605,21 @@ static cudaError_t tp_launch_partial(cudaStream_t st, const TpDev &td, int a_idx
     }
     int grid = (DEC_DIM / NW + TP_WARPS - 1) / TP_WARPS;
     if (grid > 148) grid = 148;     // 170-240 registers per thread: one CTA per SM, warps loop over row batches
-    return launch_pdl(tp_gemv_partial_kernel<NW, NCH>, grid, TP_THREADS, smem, st, td, a_idx, v, W, K);
+    return launch_pdl(tp_gemv_partial_kernel<NW, NCH>, grid, TP_THREADS, smem, st, td, a_idx, v, W, K, row_scale);
 }
 
-static cudaError_t tp_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K) {
+static cudaError_t tp_partial(cudaStream_t st, const TpDev &td, int a_idx, const float *v, const uint16_t *W, int K, const float *row_scale) {
     const int G = td.world;
     if (K == DEC_QDIM) {
-        if (G == 1) return tp_launch_partial<2, 16>(st, td, a_idx, v, W, K);
-        if (G == 2) return tp_launch_partial<4, 8>(st, td, a_idx, v, W, K);
-        if (G == 4) return tp_launch_partial<8, 4>(st, td, a_idx, v, W, K);
-        return tp_launch_partial<8, 2>(st, td, a_idx, v, W, K);
+        if (G == 1) return tp_launch_partial<2, 16>(st, td, a_idx, v, W, K, row_scale);
+        if (G == 2) return tp_launch_partial<4, 8>(st, td, a_idx, v, W, K, row_scale);
+        if (G == 4) return tp_launch_partial<8, 4>(st, td, a_idx, v, W, K, row_scale);
+        return tp_launch_partial<8, 2>(st, td, a_idx, v, W, K, row_scale);
     }
-    if (G == 1) return tp_launch_partial<1, 36>(st, td, a_idx, v, W, K);
-    if (G == 2) return tp_launch_partial<2, 18>(st, td, a_idx, v, W, K);
-    if (G == 4) return tp_launch_partial<4, 9>(st, td, a_idx, v, W, K);
-    return tp_launch_partial<8, 5>(st, td, a_idx, v, W, K);
+    if (G == 1) return tp_launch_partial<1, 36>(st, td, a_idx, v, W, K, row_scale);
+    if (G == 2) return tp_launch_partial<2, 18>(st, td, a_idx, v, W, K, row_scale);
+    if (G == 4) return tp_launch_partial<4, 9>(st, td, a_idx, v, W, K, row_scale);
+    return tp_launch_partial<8, 5>(st, td, a_idx, v, W, K, row_scale);
 }
 
 // PDL launch of an exchange consumer, as clusters of TP_CS CTAs when the cluster gather is on (cs > 1)
@@ -658,7 +663,7 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
     const size_t kv_layer = (size_t)DEC_WINDOW * DEC_KVDIM;
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
-        dec_launch_embed(st, R.d_params, s->d_embed_in, s->adapter_buf, m->tok_emb, m->inv_freq_dec, R.xbuf, s->d_rope);
+        dec_launch_embed(st, R.d_params, s->d_embed_in, s->adapter_buf, m->tok_emb, m->q8 ? m->s_tok_emb : nullptr, m->inv_freq_dec, R.xbuf, s->d_rope);
     }
     for (int l = 0; l < L; l++) {
         const DecLayerDev &W = m->dec[l];
@@ -671,20 +676,20 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
             if (l == 0) {
                 if (s->kv16)
                     CUDA_TRY(launch_pdl(tp_qkv_kernel<false, __half>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
-                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, 1));
+                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, 1, W.s_wqkv));
                 else
                     CUDA_TRY(launch_pdl(tp_qkv_kernel<false, float>, tp_grid(DEC_QKV / G), TP_THREADS, 0, st, R.dev, a, pp, (const float *)R.xbuf,
-                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, 1));
+                                        (float *)nullptr, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, 1, W.s_wqkv));
             } else {
                 int g = tp_grid(DEC_QKV / G);
                 const int cs = tp_cluster_size(G, g);
                 g -= g % cs;
                 if (s->kv16)
                     CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true, __half>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
-                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, cs));
+                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc16, vc16, cs, W.s_wqkv));
                 else
                     CUDA_TRY(launch_pdl_cs(tp_qkv_kernel<true, float>, g, cs, st, R.dev, a, pp, (const float *)(R.xbuf + DEC_DIM),
-                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, cs));
+                                           R.xbuf, W.attn_norm, W.wqkv, (const float *)s->d_rope, s->d_q, kc, vc, cs, W.s_wqkv));
             }
         }
         for (int i = 0; i < NL; i++) {
@@ -696,16 +701,16 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
                 CUDA_TRY(launch_pdl(tp_attn_kernel<float>, dim3(DEC_KVH / G, tp->att_splits), TP_THREADS, 0, st, R.dev, (const DecStepParams *)R.d_params,
                                     (const float *)s->d_q, (const float *)kc, (const float *)vc, tp->attn_part, s->d_attn));
         }
-        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM));
+        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l, s->d_attn, W.wo, DEC_QDIM, W.s_wo));
         for (int i = 0; i < NL; i++) {
             TpRank &R = tp->r[i];
             int g = tp_grid(2 * DEC_HIDDEN / G);
             const int cs = tp_cluster_size(G, g);
             g -= g % cs;
             CUDA_TRY(launch_pdl_cs(tp_ffn_kernel, g, cs, st, R.dev, 2 * l, (const float *)R.xbuf, R.xbuf + DEC_DIM,
-                                   W.ffn_norm, (const float *)(m->ada_scale + (size_t)l * DEC_DIM), W.w13, s->d_h, cs));
+                                   W.ffn_norm, (const float *)(m->ada_scale + (size_t)l * DEC_DIM), W.w13, s->d_h, cs, W.s_w13));
         }
-        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN));
+        for (int i = 0; i < NL; i++) CUDA_TRY(tp_partial(st, tp->r[i].dev, 2 * l + 1, s->d_h, W.w2, DEC_HIDDEN, W.s_w2));
     }
     int nblk = (VOCAB / G / FULL_NW + TP_WARPS - 1) / TP_WARPS;      // 100-400 MB: bandwidth-bound, one CTA per SM
     if (nblk > 148) nblk = 148;
@@ -714,7 +719,7 @@ static int tp_enqueue_step(vox_cuda_tp *tp, cudaStream_t st) {
     for (int i = 0; i < NL; i++) {
         TpRank &R = tp->r[i];
         CUDA_TRY(launch_pdl_cs(tp_logits_kernel, nblk, lcs, st, R.dev, 2 * L - 1, (const float *)(R.xbuf + DEC_DIM), m->dec_norm,
-                               m->tok_emb, s->d_logits, R.blockmax, lcs));
+                               m->tok_emb, s->d_logits, R.blockmax, lcs, (const float *)(m->q8 ? m->s_tok_emb : nullptr)));
     }
     for (int i = 0; i < NL; i++) tp_argmax_pub_kernel<<<1, 1024, 0, st>>>(tp->r[i].dev, tp->r[i].blockmax, nblk);
     for (int i = 0; i < NL; i++) tp_argmax_fin_kernel<<<1, 32, 0, st>>>(tp->r[i].dev, tp->r[i].d_params, tp->r[i].d_tokens);

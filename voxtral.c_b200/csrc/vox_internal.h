@@ -142,7 +142,7 @@ int batch_encode_clip(vox_cuda_state *s, const float *pcm, int n_samples, int n_
 int dec_launch_step(vox_cuda_state *s, cudaStream_t st);
 int dec_prefill(vox_cuda_state *s, const float *d_x_in, int seq_len);
 void dec_launch_embed(cudaStream_t st, const DecStepParams *p, const float *embed_in, const float *adapter,
-                      const uint16_t *tok_emb, const float *inv_freq, float *x, float *rope);
+                      const uint16_t *tok_emb, const float *tok_scale, const float *inv_freq, float *x, float *rope);
 void dec_launch_attn(cudaStream_t st, const DecStepParams *p, const float *q, const float *kc, const float *vc,
                      float *part, float *attn, int kvh0, int n_kvh);
 
