@@ -66,3 +66,49 @@ def test_q8_weight_table_layout_matches_c():
         pytest.skip("oracle/_ref not built")
     L = C.CDLL(rh.REF_SO)
     assert L.refshim_sizeof_weights_q8() == C.sizeof(vc.WeightsQ8)
+
+
+def test_q8_oracle_restatement_against_reference():
+    """oracle/vox_oracle.py quantize_q8 / linear_q8 pinned to the compiled reference: vox_linear_nobias_q8 and
+    vox_linear_q8 of libvoxref.so (/root/reference/voxtral_kernels.c:312-364) on random inputs, one row (the fused
+    matvec) and several rows (widen + sgemm); and the quantiser against the file gen_model --q8 wrote"""
+    import pytest
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "oracle"))
+    import vox_oracle as vo
+    if not rh.have_ref():
+        pytest.skip("oracle/_ref not built")
+    L = C.CDLL(rh.REF_SO)
+    f32p, i8p = C.POINTER(C.c_float), C.POINTER(C.c_int8)
+    L.vox_linear_nobias_q8.argtypes = [f32p, f32p, i8p, f32p, C.c_int, C.c_int, C.c_int]
+    L.vox_linear_q8.argtypes = [f32p, f32p, i8p, f32p, f32p, C.c_int, C.c_int, C.c_int]
+    rng = np.random.default_rng(3)
+    for rows, k, n in ((1, 3072, 64), (5, 1280, 96)):
+        w = (0.05 * rng.standard_normal((n, k))).astype(np.float32)
+        q, sc = vo.quantize_q8(w)
+        assert q.dtype == np.int8 and int(np.abs(q.astype(np.int32)).max(axis=1).min()) == 127
+        x = rng.standard_normal((rows, k)).astype(np.float32)
+        b = rng.standard_normal(n).astype(np.float32)
+        y = np.empty((rows, n), np.float32)
+        L.vox_linear_nobias_q8(y.ctypes.data_as(f32p), x.ctypes.data_as(f32p), q.ctypes.data_as(i8p), sc.ctypes.data_as(f32p), rows, k, n)
+        want = vo.linear_q8(x, q, sc)
+        assert np.abs(y - want).max() < 2e-5 * max(1.0, float(np.abs(want).max()))
+        L.vox_linear_q8(y.ctypes.data_as(f32p), x.ctypes.data_as(f32p), q.ctypes.data_as(i8p), sc.ctypes.data_as(f32p), b.ctypes.data_as(f32p), rows, k, n)
+        assert np.abs(y - vo.linear_q8(x, q, sc, b)).max() < 2e-5 * max(1.0, float(np.abs(want).max()))
+
+
+def test_q8_oracle_quantiser_equals_the_file(tmp_path_factory):
+    """vo.quantize_q8 on the bf16 tensor == the (int8, scale) pair gen_model --q8 wrote for it (itself = quantize.py)"""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "oracle"))
+    import hostmodel
+    import vox_oracle as vo
+    dq = _small_q8_dir(tmp_path_factory)
+    db = str(tmp_path_factory.mktemp("bfchk"))
+    subprocess.check_call([rh.ensure_gen_model(), db, "--enc-layers", "1", "--dec-layers", "1", "--no-tokenizer"], stderr=subprocess.DEVNULL)
+    hq, hb = hostmodel.HostModel(dq), hostmodel.HostModel(db)
+    for name, shape in (("layers.0.attention.wk.weight", (1024, 3072)), ("layers.0.ada_rms_norm_t_cond.2.weight", (3072, 32))):
+        w = hostmodel.bf16_to_f32(hb.u16(name)).reshape(shape)
+        q, sc = vo.quantize_q8(w)
+        fq, fs = hq.q8_parts(name)
+        assert np.array_equal(q, fq) and np.array_equal(sc.view(np.uint32), fs.view(np.uint32)), name
