@@ -138,7 +138,7 @@ vox_cuda_state_t *vox_cuda_state_create(vox_cuda_model_t *m);
  * (0.87 instead of 1.74 GB at the full 8192-key window).  Not bit-comparable with the fp32 BLAS oracle: the
  * tests state the logit tolerance (tests/test_gpu_kv16.py).  Prompt prefill: at most 128 rows at position 0.
  * vox_cuda_decoder_kv_read / _write keep fp32 host rows and convert.  Default engine only (not the legacy
- * graph decoder, not the tensor-parallel decoder). */
+ * graph decoder); the tensor-parallel decoder takes its own kv_bits (vox_cuda_tp_create_ex). */
 vox_cuda_state_t *vox_cuda_state_create_ex(vox_cuda_model_t *m, int kv_bits);
 int  vox_cuda_state_kv_bits(const vox_cuda_state_t *s);
 void vox_cuda_state_free(vox_cuda_state_t *s);
