@@ -258,34 +258,38 @@ def run_cuda(args, rank, world):
     # quantize.py); ids compared with the reference's own Q8 CPU path (tests/golden/ids_clip60_q8.npz) ----
     q8_leg = None
     if rank == 0 and not args.no_extra and not args.no_q8:
-        hq = hostmodel.HostModel(rh.model_dir(extra=("--q8",)))
-        mq = vc.check(hq.create_model(L), "model_create_q8")
-        sq = vc.check(L.vox_cuda_state_create(mq), "state_create")
-        tq = np.empty(max_tok, np.int32)
+        try:
+            hq = hostmodel.HostModel(rh.model_dir(extra=("--q8",)))
+            mq = vc.check(hq.create_model(L), "model_create_q8")
+            sq = vc.check(L.vox_cuda_state_create(mq), "state_create")
+            tq = np.empty(max_tok, np.int32)
 
-        def one_q8():
-            return vc.check(L.vox_cuda_transcribe(sq, vc.fptr(pinned), len(buf), nf, PROMPT_LEN, vc.iptr(tq), max_tok, None), "transcribe")
+            def one_q8():
+                return vc.check(L.vox_cuda_transcribe(sq, vc.fptr(pinned), len(buf), nf, PROMPT_LEN, vc.iptr(tq), max_tok, None), "transcribe")
 
-        nq = one_q8()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
             nq = one_q8()
-        tq_s = (time.perf_counter() - t0) / args.steps
-        ids_q8 = tq[:nq].copy()
-        vc.check(L.vox_cuda_decoder_set_position(sq, 38, 38), "set_position")
-        ms_q8 = float(L.vox_cuda_bench_decoder_steps(sq, 32, 38, nq, None))
-        gq = os.path.join(ROOT, "tests", "golden", "ids_clip60_q8.npz")
-        par = None
-        if args.clip_seconds == CLIP_SECONDS and os.path.exists(gq):
-            wq = np.load(gq)["ids"]
-            par = bool(len(wq) == nq and np.array_equal(wq, ids_q8))
-        q8_leg = {"e2e": {"value": args.clip_seconds / tq_s, "unit": UNIT, "ms_per_step": 1e3 * tq_s},
-                  "ms_per_token": ms_q8, "bytes_per_token": Q8_BYTES_PER_TOKEN,
-                  "hbm_gbs": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9, "frac": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9 / peak_hbm(),
-                  "parity_ids": par, "ids_equal_bf16_run": int((ids_q8 == toks_e2e[:nq]).sum()) if nq == n_tok else None,
-                  "api": "vox_cuda_model_create_q8 + vox_cuda_transcribe(host PCM) -> ids; reference = its Q8 CPU path"}
-        L.vox_cuda_state_free(sq)
-        L.vox_cuda_model_free(mq)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                nq = one_q8()
+            tq_s = (time.perf_counter() - t0) / args.steps
+            ids_q8 = tq[:nq].copy()
+            vc.check(L.vox_cuda_decoder_set_position(sq, 38, 38), "set_position")
+            ms_q8 = float(L.vox_cuda_bench_decoder_steps(sq, 32, 38, nq, None))
+            gq = os.path.join(ROOT, "tests", "golden", "ids_clip60_q8.npz")
+            par = None
+            if args.clip_seconds == CLIP_SECONDS and os.path.exists(gq):
+                wq = np.load(gq)["ids"]
+                par = bool(len(wq) == nq and np.array_equal(wq, ids_q8))
+            q8_leg = {"e2e": {"value": args.clip_seconds / tq_s, "unit": UNIT, "ms_per_step": 1e3 * tq_s},
+                      "ms_per_token": ms_q8, "bytes_per_token": Q8_BYTES_PER_TOKEN,
+                      "hbm_gbs": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9, "frac": Q8_BYTES_PER_TOKEN / (ms_q8 * 1e-3) / 1e9 / peak_hbm(),
+                      "parity_ids": par, "ids_equal_bf16_run": int((ids_q8 == toks_e2e[:nq]).sum()) if nq == n_tok else None,
+                      "api": "vox_cuda_model_create_q8 + vox_cuda_transcribe(host PCM) -> ids; reference = its Q8 CPU path"}
+            L.vox_cuda_state_free(sq)
+            L.vox_cuda_model_free(mq)
+        except Exception as ex:      # a second checkpoint is a lot to ask of a box: the headline line must survive without it
+            q8_leg = {"error": str(ex)[:200]}
+
     # ---- config 5 leg: S independent clips per GPU through a stream group (lock-step decode, one pass
     # over the weights per step); host PCM in, token ids out, inside the timed region ----
     multi = None
