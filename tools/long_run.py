@@ -1,13 +1,13 @@
 #!/usr/bin/env python3
 """BASELINE config 4 (GPU): a 30-minute synthetic clip through the streaming calls - the mel is
-fed to vox_cuda_encode_chunk in 2048-frame chunks, the decoder catches up after every chunk
+fed to vox_cuda_encode_chunk in chunks of 6656 frames (the library's largest one-pass chunk; argv[2] changes it), the decoder catches up after every chunk
 (vox_cuda_decoder_run) and consumed adapter rows are dropped (vox_cuda_adapter_discard_before), the
 way stream_run_encoder / stream_run_decoder do (/root/reference/voxtral.c:826-1145).  22 511 decode
 steps; the K/V ring (8192 positions) wraps at step 8154 and the reference's compaction points
 (9216, then every 1062 steps, voxtral_decoder.c:354-385) are passed 13 times.
 Reports total time, ms/step per 2048-step bucket (context growth then the full-window plateau)
 and checks causality: the ids of the first 60 s equal those of a run that only saw the first 90 s.
-usage: long_run.py [seconds]"""
+usage: long_run.py [seconds] [mel frames per encoder call]"""
 import ctypes as C
 import os
 import sys
@@ -25,6 +25,7 @@ import hostmodel  # noqa: E402
 import bench  # noqa: E402
 
 secs = float(sys.argv[1]) if len(sys.argv) > 1 else 1800.0
+CHUNK = int(sys.argv[2]) if len(sys.argv) > 2 else 6656
 L = vc.lib()
 assert L.vox_cuda_init() == 1, vc.last_error()
 hm = hostmodel.HostModel(rh.model_dir())
@@ -38,7 +39,8 @@ def clip(seconds):
     return np.concatenate(parts)[: int(16000 * seconds)]
 
 
-def run(x, chunk=2048):
+def run(x, chunk=None):
+    chunk = chunk or CHUNK
     buf, nf = bench.frame_buffer(x)
     mel = np.empty((nf, 128), np.float32)
     t0 = time.perf_counter()
